@@ -1,0 +1,12 @@
+"""frn_b200 -- B200-native (sm_100a) implementation of FRN's cross-modal fusion block.
+
+Drop-in replacements for retinanet/fusion.py, retinanet/Attention.py and
+retinanet/AdaIN.py of JinkaiLiu/FRN; see DESIGN.md and INTEGRATION.md.
+"""
+from .modules import AdaIN_block, CrossAttentionBlock, REFusion, c2_xavier_fill, fusion_parameters
+from .patch import patch_reference
+from .dist import allreduce_fusion_grads, shard_batch
+
+__all__ = ["AdaIN_block", "CrossAttentionBlock", "REFusion", "c2_xavier_fill", "fusion_parameters",
+           "patch_reference", "allreduce_fusion_grads", "shard_batch"]
+__version__ = "0.1.0"

@@ -1,0 +1,90 @@
+"""ctypes binding of libfrn_b200.so (the C ABI declared in include/frn_b200.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` / ``make -C frn_b200/csrc``.
+There is NO fallback: if the shared object is missing, importing succeeds (so that
+CPU-only tooling can still import the package) but the first call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfrn_b200.so")
+
+c_float_p = C.c_void_p  # raw device pointers travel as integers
+
+
+class CabParams(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in
+                ("g_w", "g_b", "theta_w", "theta_b", "phi_w", "phi_b", "W_w", "W_b")]
+
+
+class RefusionParams(C.Structure):
+    _fields_ = [("conv0_rgb_w", C.c_void_p), ("conv0_rgb_b", C.c_void_p),
+                ("conv0_evt_w", C.c_void_p), ("conv0_evt_b", C.c_void_p),
+                ("rgb_ca", CabParams), ("event_ca", CabParams)]
+
+
+# name -> (restype, argtypes); mirrors include/frn_b200.h one to one
+_SIGNATURES = {
+    "frn_abi_version": (C.c_int, []),
+    "frn_error_string": (C.c_char_p, [C.c_int]),
+    "frn_kernel_inventory": (C.c_char_p, []),
+    "frn_launch_count": (C.c_ulonglong, []),
+    "frn_mean_std": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
+                               C.c_void_p, C.c_void_p]),
+    "frn_adain_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_void_p]),
+    "frn_adain_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_size_t]),
+    "frn_adain_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_cab_saved_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_cab_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_cab_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                  C.POINTER(CabParams), C.c_void_p, C.c_long, C.c_void_p, C.c_size_t,
+                                  C.c_void_p, C.c_size_t]),
+    "frn_cab_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                   C.POINTER(CabParams), C.c_void_p, C.c_void_p, C.c_long, C.c_void_p,
+                                   C.c_void_p, C.c_int, C.POINTER(CabParams), C.c_void_p, C.c_size_t]),
+    "frn_refusion_saved_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_refusion_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_refusion_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.POINTER(RefusionParams), C.c_void_p, C.c_void_p, C.c_size_t,
+                                       C.c_void_p, C.c_size_t]),
+    "frn_refusion_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                        C.POINTER(RefusionParams), C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.POINTER(RefusionParams), C.c_void_p, C.c_size_t]),
+}
+
+EXPORTS = tuple(_SIGNATURES)
+_lib = None
+
+
+class FrnError(RuntimeError):
+    pass
+
+
+def load():
+    """Load the shared object (once) and set the prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FrnError(
+            f"frn_b200: {LIB_PATH} is missing -- build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` or `make -C frn_b200/csrc`. There is no PyTorch/CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here == header/library drift
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str):
+    if code != 0:
+        msg = load().frn_error_string(code).decode()
+        raise FrnError(f"frn_b200.{what} failed: {msg} (code {code})")

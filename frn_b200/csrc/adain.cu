@@ -1,0 +1,348 @@
+// HBM-bound kernels of the fusion block: instance statistics and the AdaIN
+// affine (retinanet/AdaIN.py:7-26), the multiplicative gate of REFusion
+// (retinanet/fusion.py:26-28) and their gradients.
+//
+// Every kernel walks rows of N = H*W contiguous floats (one (sample, channel)
+// pair per row, NCHW).  A row is owned by one warp (N < 1024) or one 256-thread
+// CTA (N >= 1024); loads are 128-bit when N % 4 == 0 (rows then start 16-byte
+// aligned), scalar otherwise (DDD17: N = 5655, 1452, 374, 99).  Variances are
+// two-pass (mean first, then sum of squared deviations; the second pass hits
+// L1/L2) because the near-constant maps produced by RGB blanking
+// (retinanet/model.py:279-280) break the E[x^2]-E[x]^2 form in fp32.
+#include <type_traits>
+#include "common.cuh"
+
+namespace frn {
+namespace {
+
+template <int W> struct Vec;
+template <> struct Vec<1> {
+  float v[1];
+  __device__ __forceinline__ void load(const float* p) { v[0] = __ldg(p); }
+  __device__ __forceinline__ void load_rw(const float* p) { v[0] = *p; }
+  __device__ __forceinline__ void store(float* p) const { *p = v[0]; }
+};
+template <> struct Vec<4> {
+  float v[4];
+  __device__ __forceinline__ void load(const float* p) {
+    float4 t = __ldg(reinterpret_cast<const float4*>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  __device__ __forceinline__ void load_rw(const float* p) {
+    float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  __device__ __forceinline__ void store(float* p) const {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+
+template <int GS>
+__device__ __forceinline__ float group_sum(float v, float* red) {
+  if (GS == 32) return warp_sum(v);
+  return block_sum(v, red);
+}
+
+// Row owned by this thread group, or -1.  GS == 32: 8 rows per 256-thread CTA.
+template <int GS>
+__device__ __forceinline__ long my_row(long rows, int& lane) {
+  if (GS == 32) {
+    lane = threadIdx.x & 31;
+    long r = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    return r < rows ? r : -1;
+  }
+  lane = threadIdx.x;
+  return blockIdx.x;
+}
+
+#define ROW_KERNEL_PROLOGUE()                 \
+  __shared__ float red[33];                   \
+  (void)red;                                  \
+  int lane;                                   \
+  long row = my_row<GS>(rows, lane);          \
+  if (row < 0) return;
+
+// ---- calc_mean_std -----------------------------------------------------------
+template <int GS, int W>
+__global__ void __launch_bounds__(256) row_mean_std_kernel(long rows, int N, const float* __restrict__ x,
+                                                           float eps, float* __restrict__ mean,
+                                                           float* __restrict__ sd) {
+  ROW_KERNEL_PROLOGUE();
+  const float* xr = x + row * N;
+  float s = 0.f;
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> a; a.load(xr + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) s += a.v[q];
+  }
+  float mu = group_sum<GS>(s, red) / (float)N;
+  float ss = 0.f;
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> a; a.load(xr + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) { float dlt = a.v[q] - mu; ss = fmaf(dlt, dlt, ss); }
+  }
+  ss = group_sum<GS>(ss, red);
+  if (lane == 0) {
+    mean[row] = mu;
+    sd[row] = sqrtf(ss / (float)(N - 1) + eps);
+  }
+}
+
+// ---- gate + statistics of both gated maps ------------------------------------
+template <int GS, int W>
+__global__ void __launch_bounds__(256) gate_stats_kernel(long rows, int N, const float* __restrict__ r0,
+                                                         const float* __restrict__ e0,
+                                                         float* __restrict__ r1, float* __restrict__ e1,
+                                                         float eps, float* __restrict__ mu_r,
+                                                         float* __restrict__ sd_r,
+                                                         float* __restrict__ mu_e,
+                                                         float* __restrict__ sd_e) {
+  ROW_KERNEL_PROLOGUE();
+  const long o = row * N;
+  float sr = 0.f, se = 0.f;
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> a, b, x, y;
+    a.load(r0 + o + n); b.load(e0 + o + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) {
+      float m = a.v[q] * b.v[q];
+      x.v[q] = a.v[q] + m; y.v[q] = b.v[q] + m;
+      sr += x.v[q]; se += y.v[q];
+    }
+    x.store(r1 + o + n); y.store(e1 + o + n);
+  }
+  float mr = group_sum<GS>(sr, red) / (float)N;
+  float me = group_sum<GS>(se, red) / (float)N;
+  float qr = 0.f, qe = 0.f;
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> a, b;
+    a.load(r0 + o + n); b.load(e0 + o + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) {
+      float m = a.v[q] * b.v[q];
+      float dx = (a.v[q] + m) - mr, dy = (b.v[q] + m) - me;
+      qr = fmaf(dx, dx, qr); qe = fmaf(dy, dy, qe);
+    }
+  }
+  qr = group_sum<GS>(qr, red);
+  qe = group_sum<GS>(qe, red);
+  if (lane == 0) {
+    mu_r[row] = mr; sd_r[row] = sqrtf(qr / (float)(N - 1) + eps);
+    mu_e[row] = me; sd_e[row] = sqrtf(qe / (float)(N - 1) + eps);
+  }
+}
+
+// ---- AdaIN apply --------------------------------------------------------------
+template <int GS, int W>
+__global__ void __launch_bounds__(256) adain_apply_kernel(long rows, int C, int N, const float* __restrict__ x,
+                                                          const float* __restrict__ mu_x,
+                                                          const float* __restrict__ sd_x,
+                                                          const float* __restrict__ mu_t,
+                                                          const float* __restrict__ sd_t,
+                                                          float* __restrict__ out, long ob) {
+  ROW_KERNEL_PROLOGUE();
+  const float* xr = x + row * N;
+  float* orow = out + (row / C) * ob + (row % C) * (long)N;
+  float mx = mu_x[row], a = sd_t[row] / sd_x[row], mt = mu_t[row];
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v; v.load(xr + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) v.v[q] = fmaf(v.v[q] - mx, a, mt);
+    v.store(orow + n);
+  }
+}
+
+// ---- AdaIN backward -------------------------------------------------------------
+template <int GS, int W>
+__global__ void __launch_bounds__(256) adain_bwd_reduce_kernel(long rows, int C, int N,
+                                                               const float* __restrict__ g, long gb,
+                                                               const float* __restrict__ x,
+                                                               const float* __restrict__ mu_x,
+                                                               const float* __restrict__ sd_x,
+                                                               float* __restrict__ g1,
+                                                               float* __restrict__ g2) {
+  ROW_KERNEL_PROLOGUE();
+  const float* xr = x + row * N;
+  const float* gr = g + (row / C) * gb + (row % C) * (long)N;
+  float mx = mu_x[row];
+  float s1 = 0.f, s2 = 0.f;
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v, gg; v.load(xr + n); gg.load(gr + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) { s1 += gg.v[q]; s2 = fmaf(gg.v[q], v.v[q] - mx, s2); }
+  }
+  s1 = group_sum<GS>(s1, red);
+  s2 = group_sum<GS>(s2, red);
+  if (lane == 0) { g1[row] = s1; g2[row] = s2 / sd_x[row]; }
+}
+
+template <int GS, int W>
+__global__ void __launch_bounds__(256) adain_bwd_content_kernel(
+    long rows, int C, int N, const float* __restrict__ g, long gb, const float* __restrict__ x,
+    const float* __restrict__ mu_x, const float* __restrict__ sd_x, const float* __restrict__ sd_t,
+    const float* __restrict__ g1, const float* __restrict__ g2, float* __restrict__ dx, int accumulate) {
+  ROW_KERNEL_PROLOGUE();
+  const float* xr = x + row * N;
+  const float* gr = g + (row / C) * gb + (row % C) * (long)N;
+  float* dr = dx + row * N;
+  float mx = mu_x[row], isx = 1.f / sd_x[row];
+  float k = sd_t[row] * isx;
+  float c1 = g1[row] / (float)N, c2 = g2[row] * isx / (float)(N - 1);
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v, gg, o; v.load(xr + n); gg.load(gr + n);
+    if (accumulate) o.load_rw(dr + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) {
+      float r = k * (gg.v[q] - c1 - (v.v[q] - mx) * c2);
+      o.v[q] = accumulate ? o.v[q] + r : r;
+    }
+    o.store(dr + n);
+  }
+}
+
+template <int GS, int W>
+__global__ void __launch_bounds__(256) adain_bwd_style_kernel(long rows, int N, const float* __restrict__ t,
+                                                              const float* __restrict__ mu_t,
+                                                              const float* __restrict__ sd_t,
+                                                              const float* __restrict__ g1,
+                                                              const float* __restrict__ g2,
+                                                              float* __restrict__ dstyle) {
+  ROW_KERNEL_PROLOGUE();
+  const float* tr = t + row * N;
+  float* dr = dstyle + row * N;
+  float mt = mu_t[row];
+  float al = g1[row] / (float)N, be = g2[row] / ((float)(N - 1) * sd_t[row]);
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v; v.load(tr + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) v.v[q] = fmaf(be, v.v[q] - mt, al);
+    v.store(dr + n);
+  }
+}
+
+template <int GS, int W>
+__global__ void __launch_bounds__(256) center_rows_kernel(long rows, int N, const float* __restrict__ y,
+                                                          const float* __restrict__ mean,
+                                                          float* __restrict__ yc) {
+  ROW_KERNEL_PROLOGUE();
+  float mu = mean[row];
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v; v.load(y + row * N + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) v.v[q] -= mu;
+    v.store(yc + row * N + n);
+  }
+}
+
+template <int GS, int W>
+__global__ void __launch_bounds__(256) add_row_bias_kernel(long rows, int N, const float* __restrict__ u,
+                                                           float* __restrict__ x) {
+  ROW_KERNEL_PROLOGUE();
+  float b = u[row];
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v; v.load_rw(x + row * N + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) v.v[q] += b;
+    v.store(x + row * N + n);
+  }
+}
+
+template <int GS, int W>
+__global__ void __launch_bounds__(256) row_dot_kernel(long rows, int N, const float* __restrict__ x,
+                                                      const float* __restrict__ y, float* __restrict__ out) {
+  ROW_KERNEL_PROLOGUE();
+  float s = 0.f;
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> a, b; a.load(x + row * N + n); b.load(y + row * N + n);
+#pragma unroll
+    for (int q = 0; q < W; q++) s = fmaf(a.v[q], b.v[q], s);
+  }
+  s = group_sum<GS>(s, red);
+  if (lane == 0) out[row] = s;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// Dispatch on row length (warp- or CTA-per-row) and vector width.
+#define LAUNCH_ROWS(KERNEL, rows, N, vec, ...)                                            \
+  do {                                                                                    \
+    if ((N) >= 1024) {                                                                    \
+      if (vec) KERNEL<256, 4><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);             \
+      else KERNEL<256, 1><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);                 \
+    } else {                                                                              \
+      unsigned nb = (unsigned)(((rows) + 7) / 8);                                         \
+      if (vec) KERNEL<32, 4><<<nb, 256, 0, st>>>(__VA_ARGS__);                            \
+      else KERNEL<32, 1><<<nb, 256, 0, st>>>(__VA_ARGS__);                                \
+    }                                                                                     \
+    FRN_LAUNCH_CHECK();                                                                   \
+  } while (0)
+
+}  // namespace
+
+int row_mean_std(cudaStream_t st, long rows, int N, const float* x, float eps, float* mean, float* sd) {
+  bool vec = (N % 4 == 0) && aligned16(x);
+  LAUNCH_ROWS(row_mean_std_kernel, rows, N, vec, rows, N, x, eps, mean, sd);
+  return FRN_OK;
+}
+
+int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* e0, float* r1, float* e1,
+               float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e) {
+  bool vec = (N % 4 == 0) && aligned16(r0) && aligned16(e0) && aligned16(r1) && aligned16(e1);
+  LAUNCH_ROWS(gate_stats_kernel, rows, N, vec, rows, N, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e);
+  return FRN_OK;
+}
+
+int adain_apply(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x, const float* sd_x,
+                const float* mu_t, const float* sd_t, float* out, long ob) {
+  long rows = (long)B * C;
+  bool vec = (N % 4 == 0) && (ob % 4 == 0) && aligned16(x) && aligned16(out);
+  LAUNCH_ROWS(adain_apply_kernel, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
+  return FRN_OK;
+}
+
+int adain_bwd_reduce(cudaStream_t st, int B, int C, int N, const float* g, long gb, const float* x,
+                     const float* mu_x, const float* sd_x, float* g1, float* g2) {
+  long rows = (long)B * C;
+  bool vec = (N % 4 == 0) && (gb % 4 == 0) && aligned16(x) && aligned16(g);
+  LAUNCH_ROWS(adain_bwd_reduce_kernel, rows, N, vec, rows, C, N, g, gb, x, mu_x, sd_x, g1, g2);
+  return FRN_OK;
+}
+
+int adain_bwd_content(cudaStream_t st, int B, int C, int N, const float* g, long gb, const float* x,
+                      const float* mu_x, const float* sd_x, const float* sd_t, const float* g1,
+                      const float* g2, float* dx, int accumulate) {
+  long rows = (long)B * C;
+  bool vec = (N % 4 == 0) && (gb % 4 == 0) && aligned16(x) && aligned16(g) && aligned16(dx);
+  LAUNCH_ROWS(adain_bwd_content_kernel, rows, N, vec, rows, C, N, g, gb, x, mu_x, sd_x, sd_t, g1, g2, dx,
+              accumulate);
+  return FRN_OK;
+}
+
+int adain_bwd_style(cudaStream_t st, int B, int C, int N, const float* t, const float* mu_t,
+                    const float* sd_t, const float* g1, const float* g2, float* dstyle) {
+  long rows = (long)B * C;
+  bool vec = (N % 4 == 0) && aligned16(t) && aligned16(dstyle);
+  LAUNCH_ROWS(adain_bwd_style_kernel, rows, N, vec, rows, N, t, mu_t, sd_t, g1, g2, dstyle);
+  return FRN_OK;
+}
+
+int center_rows(cudaStream_t st, long rows, int N, const float* y, const float* mean, float* yc) {
+  bool vec = (N % 4 == 0) && aligned16(y) && aligned16(yc);
+  LAUNCH_ROWS(center_rows_kernel, rows, N, vec, rows, N, y, mean, yc);
+  return FRN_OK;
+}
+
+int add_row_bias(cudaStream_t st, long rows, int N, const float* u, float* x) {
+  bool vec = (N % 4 == 0) && aligned16(x);
+  LAUNCH_ROWS(add_row_bias_kernel, rows, N, vec, rows, N, u, x);
+  return FRN_OK;
+}
+
+int row_dot(cudaStream_t st, long rows, int N, const float* x, const float* y, float* out) {
+  bool vec = (N % 4 == 0) && aligned16(x) && aligned16(y);
+  LAUNCH_ROWS(row_dot_kernel, rows, N, vec, rows, N, x, y, out);
+  return FRN_OK;
+}
+
+}  // namespace frn

@@ -1,0 +1,167 @@
+// Shared helpers for the FRN fusion-block kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <atomic>
+#include "../../include/frn_b200.h"
+
+namespace frn {
+
+extern std::atomic<unsigned long long> g_launches;
+
+#define FRN_LAUNCH_CHECK()                                   \
+  do {                                                       \
+    frn::g_launches.fetch_add(1, std::memory_order_relaxed); \
+    cudaError_t e__ = cudaGetLastError();                    \
+    if (e__ != cudaSuccess) return (int)e__;                 \
+  } while (0)
+
+#define FRN_TRY(expr)            \
+  do {                           \
+    int rc__ = (expr);           \
+    if (rc__ != FRN_OK) return rc__; \
+  } while (0)
+
+static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
+static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024; result valid in every thread.
+// `red` must hold 33 floats.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();  // protect `red` from a previous use
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    float t = lane < nw ? red[lane] : 0.f;
+    t = warp_sum(t);
+    if (lane == 0) red[32] = t;
+  }
+  __syncthreads();
+  return red[32];
+}
+
+// Bump allocator over a caller-provided buffer.
+struct Arena {
+  char* base;
+  size_t off, cap, peak;
+  bool ok;
+  bool dry;   // only count bytes
+  Arena(void* p, size_t bytes, bool dry_ = false)
+      : base((char*)p), off(0), cap(bytes), peak(0), ok(true), dry(dry_) {}
+  template <typename T>
+  T* take(size_t count) {
+    size_t bytes = align_up(count * sizeof(T));
+    size_t at = off;
+    off += bytes;
+    if (off > peak) peak = off;
+    if (dry) return nullptr;
+    if (off > cap) { ok = false; return nullptr; }
+    return (T*)(base + at);
+  }
+  void release_to(size_t mark) { off = mark; }
+};
+
+// ---- GEMM (gemm.cu) -------------------------------------------------------
+// C[b][m][n] (+)= alpha * sum_k A[b][m][k] * B[b][k][n] + bias_m[m]
+// with arbitrary element strides.  reduce_batch: sums the product over the
+// batch into one C (weight gradients); then sCb is ignored.
+struct GemmDesc {
+  const float* A; const float* B; float* C;
+  int M, N, K, batch;
+  long sAm, sAk, sAb;
+  long sBk, sBn, sBb;
+  long sCm, sCn, sCb;
+  const float* bias_m;   // length M (+ b*bias_bs) or nullptr
+  long bias_bs;          // batch stride of bias_m (0: shared)
+  float alpha;
+  int accumulate;        // C += result
+  int reduce_batch;
+};
+enum { GEMM_EPI_STORE = 0, GEMM_EPI_ROWSUMSQ = 1 };
+
+size_t gemm_workspace_bytes(const GemmDesc& d);
+// ws: split-K partials (only used when reduce_batch); may be null if bytes == 0.
+int gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);
+// out_partial[(b*M + m) * nparts + part] = sum over the tile's columns of (A*B)^2; returns nparts.
+int gemm_rowsumsq_parts(int N);
+int gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
+
+// ---- attention (attention.cu) ----------------------------------------------
+// Qc, Kc: (B, d, N) channel-major.  Vp: (B, N, d) position-major.
+// Y: (B, N, d) row-major; lse: (B, N).
+int attn_forward(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc,
+                 const float* Vp, float* Y, float* lse);
+// Backward needs both orientations: *c = (B, d, N), *p = (B, N, d).
+// dQp must be zero-initialised by the caller (accumulated with atomics).
+int attn_backward(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Qp,
+                  const float* Kc, const float* Kp, const float* Vc, const float* dYc,
+                  const float* dYp, const float* lse, const float* delta, float* dQp,
+                  float* dKp, float* dVp);
+
+// ---- elementwise / reductions (adain.cu) ------------------------------------
+// mean/std over rows of length N: x is (rows, N) contiguous.
+int row_mean_std(cudaStream_t st, long rows, int N, const float* x, float eps, float* mean,
+                 float* sd);
+// r1 = r0 + r0*e0, e1 = e0 + r0*e0 fused with the row statistics of r1 and e1.
+int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* e0, float* r1,
+               float* e1, float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e);
+// out[b][c][n] = (x - mu_x)/sd_x * sd_t + mu_t   (out has batch stride ob)
+int adain_apply(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x,
+                const float* sd_x, const float* mu_t, const float* sd_t, float* out, long ob);
+// g1 = sum_n g, g2 = sum_n g * xhat per (b, c) row; g has batch stride gb.
+int adain_bwd_reduce(cudaStream_t st, int B, int C, int N, const float* g, long gb,
+                     const float* x, const float* mu_x, const float* sd_x, float* g1, float* g2);
+// dx (+)= (sd_t/sd_x) * (g - g1/N - xhat*g2/(N-1))
+int adain_bwd_content(cudaStream_t st, int B, int C, int N, const float* g, long gb,
+                      const float* x, const float* mu_x, const float* sd_x, const float* sd_t,
+                      const float* g1, const float* g2, float* dx, int accumulate);
+// dstyle = g1/N + g2*(t - mu_t)/((N-1)*sd_t)
+int adain_bwd_style(cudaStream_t st, int B, int C, int N, const float* t, const float* mu_t,
+                    const float* sd_t, const float* g1, const float* g2, float* dstyle);
+// alpha = g1/N, beta = g2/((N-1)*sd_t)
+int style_coeffs(cudaStream_t st, long rows, int N, const float* g1, const float* g2,
+                 const float* sd_t, float* alpha, float* beta);
+// sd_t = sqrt(sum(parts)/(N-1) + eps)
+int finish_style_std(cudaStream_t st, long rows, int nparts, int N, const float* parts, float eps,
+                     float* sd_t);
+// yc[r][n] = y[r][n] - mean[r]
+int center_rows(cudaStream_t st, long rows, int N, const float* y, const float* mean, float* yc);
+// out[r] = sum_n x[r][n]*y[r][n]   (rows of length N)
+int row_dot(cudaStream_t st, long rows, int N, const float* x, const float* y, float* out);
+// out[m] = sum_b sum_n x[b*sb + m*sm + n*sn]
+int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb, long sm, long sn,
+                  float* out);
+// gate backward: dr0 = dr1*(1+e0) + de1*e0 ; de0 = de1*(1+r0) + dr1*r0 (in place allowed)
+int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
+                  const float* de1, float* dr0, float* de0);
+// dst (B, cols, rows) = transpose of src (B, rows, cols)
+int transpose_batched(cudaStream_t st, int B, int rows, int cols, const float* src, float* dst);
+// scaled[b][c][k] = beta[b][c] * w[c][k]
+int scale_rows(cudaStream_t st, int B, int C, int K, const float* w, const float* beta,
+               float* scaled);
+// dst[b][k][n] = u[b][k] + src[b][k][n]   (in place)
+int add_row_bias(cudaStream_t st, long rows, int N, const float* u, float* x);
+// dW[c][k] (+)= sum_b alpha[b][c] * N * ybar[b][k]
+int outer_accumulate(cudaStream_t st, int B, int C, int K, const float* alpha, const float* ybar,
+                     float scale, float* dW);
+// materialised attention helpers (rows of length N, one CTA per row)
+int softmax_rows(cudaStream_t st, long rows, int N, float* S, float* lse);        // in place
+int exp_sub_lse(cudaStream_t st, long rows, int N, float* S, const float* lse);   // in place
+int ds_from_p(cudaStream_t st, long rows, int N, const float* P, float* dP, const float* delta);
+int fill_zero(cudaStream_t st, float* p, size_t count);
+int scale_sum_batch(cudaStream_t st, int B, int C, const float* alpha, float scale, float* out);
+
+}  // namespace frn

@@ -1,0 +1,561 @@
+// Host-side orchestration of the fusion block and the C ABI (include/frn_b200.h).
+//
+//   cab_forward / cab_backward        CrossAttentionBlock   retinanet/Attention.py:21-36
+//   refusion_forward / _backward      REFusion              retinanet/fusion.py:20-36
+//   frn_adain_* / frn_mean_std        AdaIN_block           retinanet/AdaIN.py:7-26
+//
+// Every function only enqueues kernels on the caller's stream.  Scratch comes
+// from a bump arena over the caller's workspace; the *_workspace_bytes()
+// queries run the same code in "dry" mode (no launches) so the sizes can never
+// drift from the real allocation sequence.
+#include <algorithm>
+#include "common.cuh"
+
+namespace frn {
+namespace {
+
+constexpr float kEps = 1e-5f;                        // AdaIN.py:7
+constexpr size_t kScoreBudget = 256ull << 20;        // bytes of N x N scores per chunk (d > 64 path)
+
+struct Ctx {
+  cudaStream_t st;
+  bool dry;
+  Arena ws;
+  size_t splitk_need;   // dry: max split-K partial bytes over all reduce GEMMs
+  void* splitk;
+  size_t splitk_cap;
+  Ctx(cudaStream_t s, void* p, size_t bytes, bool dry_)
+      : st(s), dry(dry_), ws(p, bytes, dry_), splitk_need(0), splitk(nullptr), splitk_cap(0) {}
+};
+
+#define RUN(c, expr)              \
+  do {                            \
+    if (!(c).dry) FRN_TRY(expr);  \
+  } while (0)
+
+int run_gemm(Ctx& c, const GemmDesc& d) {
+  if (c.dry) {
+    c.splitk_need = std::max(c.splitk_need, gemm_workspace_bytes(d));
+    return FRN_OK;
+  }
+  return gemm(c.st, d, c.splitk, c.splitk_cap);
+}
+
+GemmDesc desc(const float* A, const float* B, float* C, int M, int N, int K, int batch) {
+  GemmDesc d{};
+  d.A = A; d.B = B; d.C = C; d.M = M; d.N = N; d.K = K; d.batch = batch;
+  d.alpha = 1.f;
+  return d;
+}
+
+// out (batch, M, N) = W (M, K) @ x (batch, K, N) + bias
+int conv1x1(Ctx& c, const float* W, const float* bias, const float* x, float* out, int batch, int M,
+            int K, int N) {
+  GemmDesc d = desc(W, x, out, M, N, K, batch);
+  d.sAm = K; d.sAk = 1; d.sAb = 0;
+  d.sBk = N; d.sBn = 1; d.sBb = (long)K * N;
+  d.sCm = N; d.sCn = 1; d.sCb = (long)M * N;
+  d.bias_m = bias;
+  return run_gemm(c, d);
+}
+// dx (batch, K, N) (+)= W^T (K, M) @ dy (batch, M, N), dy element (m, n) at dy[m*sm + n*sn]
+int conv1x1_dgrad(Ctx& c, const float* W, const float* dy, long sm, long sn, long sb, float* dx,
+                  int batch, int M, int K, int N, int accumulate) {
+  GemmDesc d = desc(W, dy, dx, K, N, M, batch);
+  d.sAm = 1; d.sAk = K; d.sAb = 0;
+  d.sBk = sm; d.sBn = sn; d.sBb = sb;
+  d.sCm = N; d.sCn = 1; d.sCb = (long)K * N;
+  d.accumulate = accumulate;
+  return run_gemm(c, d);
+}
+// dW (M, K) = sum_b dy_b (M, N) @ x_b^T (N, K);  db (M) = sum_b sum_n dy_b
+int conv1x1_wgrad(Ctx& c, const float* dy, long sm, long sn, long sb, const float* x, float* dW,
+                  float* db, int batch, int M, int K, int N) {
+  GemmDesc d = desc(dy, x, dW, M, K, N, batch);
+  d.sAm = sm; d.sAk = sn; d.sAb = sb;
+  d.sBk = 1; d.sBn = N; d.sBb = (long)K * N;
+  d.sCm = K; d.sCn = 1;
+  d.reduce_batch = 1;
+  FRN_TRY(run_gemm(c, d));
+  if (db) RUN(c, batch_row_sum(c.st, batch, M, N, dy, sb, sm, sn, db));
+  return FRN_OK;
+}
+
+// ---- state kept by CrossAttentionBlock.forward for its backward ----------------
+struct CabSaved {
+  float *Qc, *Kc, *Vc;      // (B, d, N) phi(x1), theta(x1), g(x0)       Attention.py:24-27
+  float *Y;                 // (B, N, d) softmax(QK) V, row-major         Attention.py:32
+  float *lse;               // (B, N)    row log-sum-exp of QK
+  float *ybar;              // (B, d)    row means of Y viewed as (d, N)
+  float *mu_x, *sd_x;       // (B*C)     content statistics of x0        AdaIN.py:23
+  float *mu_t, *sd_t;       // (B*C)     style statistics of W(y)        AdaIN.py:22
+  size_t bytes;
+};
+
+CabSaved cab_saved_layout(void* base, int B, int C, int N) {
+  int d = C / 8;
+  Arena a(base, ~(size_t)0 >> 1, base == nullptr);
+  CabSaved s;
+  s.Qc = a.take<float>((size_t)B * d * N);
+  s.Kc = a.take<float>((size_t)B * d * N);
+  s.Vc = a.take<float>((size_t)B * d * N);
+  s.Y = a.take<float>((size_t)B * N * d);
+  s.lse = a.take<float>((size_t)B * N);
+  s.ybar = a.take<float>((size_t)B * d);
+  s.mu_x = a.take<float>((size_t)B * C);
+  s.sd_x = a.take<float>((size_t)B * C);
+  s.mu_t = a.take<float>((size_t)B * C);
+  s.sd_t = a.take<float>((size_t)B * C);
+  s.bytes = a.off;
+  return s;
+}
+
+int chunk_for_scores(int B, int N, int mats) {
+  size_t per = (size_t)N * N * sizeof(float) * mats;
+  size_t ch = kScoreBudget / (per ? per : 1);
+  if (ch < 1) ch = 1;
+  if (ch > (size_t)B) ch = B;
+  return (int)ch;
+}
+
+// softmax(Q K) V for all samples.  d <= 64: fused streaming kernel; else GEMM + row softmax.
+int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
+  if (d <= 64) {
+    float* Vp = c.ws.take<float>((size_t)B * N * d);
+    RUN(c, transpose_batched(c.st, B, d, N, s.Vc, Vp));
+    RUN(c, attn_forward(c.st, B, N, d, s.Qc, s.Kc, Vp, s.Y, s.lse));
+    return FRN_OK;
+  }
+  int ch = chunk_for_scores(B, N, 1);
+  float* S = c.ws.take<float>((size_t)ch * N * N);
+  for (int b0 = 0; b0 < B; b0 += ch) {
+    int nb = std::min(ch, B - b0);
+    long o = (long)b0 * d * N;
+    GemmDesc g = desc(s.Qc + o, s.Kc + o, S, N, N, d, nb);      // S[i][j] = sum_c Q[c][i] K[c][j]
+    g.sAm = 1; g.sAk = N; g.sAb = (long)d * N;
+    g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
+    g.sCm = N; g.sCn = 1; g.sCb = (long)N * N;
+    FRN_TRY(run_gemm(c, g));
+    RUN(c, softmax_rows(c.st, (long)nb * N, N, S, s.lse + (long)b0 * N));
+    GemmDesc y = desc(S, s.Vc + o, s.Y + o, N, d, N, nb);       // Y[i][k] = sum_j P[i][j] V[k][j]
+    y.sAm = N; y.sAk = 1; y.sAb = (long)N * N;
+    y.sBk = 1; y.sBn = N; y.sBb = (long)d * N;
+    y.sCm = d; y.sCn = 1; y.sCb = (long)N * d;
+    FRN_TRY(run_gemm(c, y));
+  }
+  return FRN_OK;
+}
+
+// CrossAttentionBlock.forward([x0, x1]).  have_x_stats: s.mu_x / s.sd_x already hold the
+// statistics of x0 (REFusion computes them inside the gate kernel).
+int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, const frn_cab_params& p,
+                float* out, long ob, const CabSaved& s, bool have_x_stats) {
+  const int d = C / 8;
+  FRN_TRY(conv1x1(c, p.g_w, p.g_b, x0, s.Vc, B, d, C, N));        // Attention.py:24
+  FRN_TRY(conv1x1(c, p.theta_w, p.theta_b, x1, s.Kc, B, d, C, N));  // Attention.py:26
+  FRN_TRY(conv1x1(c, p.phi_w, p.phi_b, x1, s.Qc, B, d, C, N));      // Attention.py:27
+  size_t mark = c.ws.off;
+  FRN_TRY(attention_fwd(c, B, N, d, s));                          // Attention.py:29-32
+  c.ws.release_to(mark);
+
+  // Attention.py:32,34-35: Y (N, d) is reinterpreted as Y' (d, N); only the per-channel
+  // mean / variance of W Y' + b reach the output (AdaIN.py:22), so W_y is never stored:
+  //   mu_t = W ybar + b ;  var_t = rowsumsq(W (Y' - ybar)) / (N-1)
+  float* scratch = c.ws.take<float>((size_t)B * d);
+  float* Yc = c.ws.take<float>((size_t)B * d * N);
+  int nparts = gemm_rowsumsq_parts(N);
+  float* parts = c.ws.take<float>((size_t)B * C * nparts);
+  RUN(c, row_mean_std(c.st, (long)B * d, N, s.Y, kEps, s.ybar, scratch));
+  RUN(c, center_rows(c.st, (long)B * d, N, s.Y, s.ybar, Yc));
+  {
+    GemmDesc g = desc(p.W_w, Yc, nullptr, C, N, d, B);
+    g.sAm = d; g.sAk = 1; g.sAb = 0;
+    g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
+    RUN(c, gemm_rowsumsq(c.st, g, parts));
+    RUN(c, finish_style_std(c.st, (long)B * C, nparts, N, parts, kEps, s.sd_t));
+    GemmDesc m = desc(p.W_w, s.ybar, s.mu_t, C, B, d, 1);       // mu_t[b][c] = W[c] . ybar[b] + b_c
+    m.sAm = d; m.sAk = 1;
+    m.sBk = 1; m.sBn = d;
+    m.sCm = 1; m.sCn = C;
+    m.bias_m = p.W_b;
+    FRN_TRY(run_gemm(c, m));
+  }
+  if (!have_x_stats) RUN(c, row_mean_std(c.st, (long)B * C, N, x0, kEps, s.mu_x, s.sd_x));
+  RUN(c, adain_apply(c.st, B, C, N, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, out, ob));  // AdaIN.py:24-26
+  c.ws.release_to(mark);
+  return FRN_OK;
+}
+
+// Gradients of softmax(Q K) V wrt Q, K, V given dY; outputs position-major (B, N, d).
+int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* dYp, float* dQp,
+                  float* dKp, float* dVp) {
+  float* delta = c.ws.take<float>((size_t)B * N);
+  RUN(c, row_dot(c.st, (long)B * N, d, dYp, s.Y, delta));           // rowsum(dY * Y)
+  if (d <= 64) {
+    float* Qp = c.ws.take<float>((size_t)B * N * d);
+    float* Kp = c.ws.take<float>((size_t)B * N * d);
+    float* dYc = c.ws.take<float>((size_t)B * N * d);
+    RUN(c, transpose_batched(c.st, B, d, N, s.Qc, Qp));
+    RUN(c, transpose_batched(c.st, B, d, N, s.Kc, Kp));
+    RUN(c, transpose_batched(c.st, B, N, d, dYp, dYc));
+    RUN(c, fill_zero(c.st, dQp, (size_t)B * N * d));
+    RUN(c, attn_backward(c.st, B, N, d, s.Qc, Qp, s.Kc, Kp, s.Vc, dYc, dYp, s.lse, delta, dQp, dKp, dVp));
+    return FRN_OK;
+  }
+  int ch = chunk_for_scores(B, N, 2);
+  float* P = c.ws.take<float>((size_t)ch * N * N);
+  float* dS = c.ws.take<float>((size_t)ch * N * N);
+  const long dn = (long)d * N, nn = (long)N * N;
+  for (int b0 = 0; b0 < B; b0 += ch) {
+    int nb = std::min(ch, B - b0);
+    long o = (long)b0 * dn;
+    GemmDesc g = desc(s.Qc + o, s.Kc + o, P, N, N, d, nb);          // S = Q K
+    g.sAm = 1; g.sAk = N; g.sAb = dn;
+    g.sBk = N; g.sBn = 1; g.sBb = dn;
+    g.sCm = N; g.sCn = 1; g.sCb = nn;
+    FRN_TRY(run_gemm(c, g));
+    RUN(c, exp_sub_lse(c.st, (long)nb * N, N, P, s.lse + (long)b0 * N));   // P = exp(S - lse)
+    GemmDesc v = desc(P, dYp + o, dVp + o, N, d, N, nb);            // dV[j][k] = sum_i P[i][j] dY[i][k]
+    v.sAm = 1; v.sAk = N; v.sAb = nn;
+    v.sBk = d; v.sBn = 1; v.sBb = dn;
+    v.sCm = d; v.sCn = 1; v.sCb = dn;
+    FRN_TRY(run_gemm(c, v));
+    GemmDesc p = desc(dYp + o, s.Vc + o, dS, N, N, d, nb);          // dP[i][j] = sum_k dY[i][k] V[k][j]
+    p.sAm = d; p.sAk = 1; p.sAb = dn;
+    p.sBk = N; p.sBn = 1; p.sBb = dn;
+    p.sCm = N; p.sCn = 1; p.sCb = nn;
+    FRN_TRY(run_gemm(c, p));
+    RUN(c, ds_from_p(c.st, (long)nb * N, N, P, dS, delta + (long)b0 * N));  // dS = P (dP - delta)
+    GemmDesc q = desc(dS, s.Kc + o, dQp + o, N, d, N, nb);          // dQ[i][k] = sum_j dS[i][j] K[k][j]
+    q.sAm = N; q.sAk = 1; q.sAb = nn;
+    q.sBk = 1; q.sBn = N; q.sBb = dn;
+    q.sCm = d; q.sCn = 1; q.sCb = dn;
+    FRN_TRY(run_gemm(c, q));
+    GemmDesc k = desc(dS, s.Qc + o, dKp + o, N, d, N, nb);          // dK[j][k] = sum_i dS[i][j] Q[k][i]
+    k.sAm = 1; k.sAk = N; k.sAb = nn;
+    k.sBk = 1; k.sBn = N; k.sBb = dn;
+    k.sCm = d; k.sCn = 1; k.sCb = dn;
+    FRN_TRY(run_gemm(c, k));
+  }
+  return FRN_OK;
+}
+
+// Backward of CrossAttentionBlock.forward.  dx0 / dx1: overwritten unless
+// acc0 / acc1.  Parameter gradients are overwritten.
+int cab_backward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, const frn_cab_params& p,
+                 const CabSaved& s, const float* g, long gb, float* dx0, int acc0, float* dx1, int acc1,
+                 const frn_cab_grads& gr) {
+  const int d = C / 8;
+  const long rows = (long)B * C;
+  size_t mark = c.ws.off;
+  float* g1 = c.ws.take<float>(rows);
+  float* g2 = c.ws.take<float>(rows);
+  float* alpha = c.ws.take<float>(rows);
+  float* beta = c.ws.take<float>(rows);
+  // AdaIN backward (AdaIN.py:24-26): content path straight into dx0
+  RUN(c, adain_bwd_reduce(c.st, B, C, N, g, gb, x0, s.mu_x, s.sd_x, g1, g2));
+  RUN(c, adain_bwd_content(c.st, B, C, N, g, gb, x0, s.mu_x, s.sd_x, s.sd_t, g1, g2, dx0, acc0));
+  RUN(c, style_coeffs(c.st, rows, N, g1, g2, s.sd_t, alpha, beta));
+  // style path: dT[b][c][n] = alpha + beta * (W (Y' - ybar))[c][n]
+  float* dYp = c.ws.take<float>((size_t)B * N * d);     // gradient wrt Y (flat = Y' layout)
+  {
+    size_t m2 = c.ws.off;
+    float* Yc = c.ws.take<float>((size_t)B * d * N);
+    float* Wb = c.ws.take<float>((size_t)B * C * d);
+    float* dT = c.ws.take<float>((size_t)B * C * N);
+    RUN(c, center_rows(c.st, (long)B * d, N, s.Y, s.ybar, Yc));
+    RUN(c, scale_rows(c.st, B, C, d, p.W_w, beta, Wb));
+    GemmDesc t = desc(Wb, Yc, dT, C, N, d, B);
+    t.sAm = d; t.sAk = 1; t.sAb = (long)C * d;
+    t.sBk = N; t.sBn = 1; t.sBb = (long)d * N;
+    t.sCm = N; t.sCn = 1; t.sCb = (long)C * N;
+    t.bias_m = alpha; t.bias_bs = C;
+    FRN_TRY(run_gemm(c, t));
+    // W conv gradients (Attention.py:34): dW = sum_b dT Y'^T, db = sum_b N alpha
+    GemmDesc w = desc(dT, s.Y, gr.W_w, C, d, N, B);
+    w.sAm = N; w.sAk = 1; w.sAb = (long)C * N;
+    w.sBk = 1; w.sBn = N; w.sBb = (long)d * N;
+    w.sCm = d; w.sCn = 1;
+    w.reduce_batch = 1;
+    FRN_TRY(run_gemm(c, w));
+    RUN(c, scale_sum_batch(c.st, B, C, alpha, (float)N, gr.W_b));
+    // dY' = W^T dT, stored flat == dY (N, d)  (undoes the view of Attention.py:32)
+    FRN_TRY(conv1x1_dgrad(c, p.W_w, dT, N, 1, (long)C * N, dYp, B, C, d, N, 0));
+    c.ws.release_to(m2);
+  }
+  float* dQp = c.ws.take<float>((size_t)B * N * d);
+  float* dKp = c.ws.take<float>((size_t)B * N * d);
+  float* dVp = c.ws.take<float>((size_t)B * N * d);
+  {
+    size_t m2 = c.ws.off;
+    FRN_TRY(attention_bwd(c, B, N, d, s, dYp, dQp, dKp, dVp));
+    c.ws.release_to(m2);
+  }
+  // projections (Attention.py:24-27); position-major gradients: element (k, n) at [n*d + k]
+  const long nd = (long)N * d;
+  FRN_TRY(conv1x1_dgrad(c, p.g_w, dVp, 1, d, nd, dx0, B, d, C, N, 1));
+  FRN_TRY(conv1x1_dgrad(c, p.theta_w, dKp, 1, d, nd, dx1, B, d, C, N, acc1));
+  FRN_TRY(conv1x1_dgrad(c, p.phi_w, dQp, 1, d, nd, dx1, B, d, C, N, 1));
+  FRN_TRY(conv1x1_wgrad(c, dVp, 1, d, nd, x0, gr.g_w, gr.g_b, B, d, C, N));
+  FRN_TRY(conv1x1_wgrad(c, dKp, 1, d, nd, x1, gr.theta_w, gr.theta_b, B, d, C, N));
+  FRN_TRY(conv1x1_wgrad(c, dQp, 1, d, nd, x1, gr.phi_w, gr.phi_b, B, d, C, N));
+  c.ws.release_to(mark);
+  return FRN_OK;
+}
+
+// ---- REFusion ---------------------------------------------------------------
+struct FusionSaved {
+  float *R0, *E0;           // (B, C, N) conv0_rgb(a), conv0_evt(e)       fusion.py:23-24
+  float *R1, *E1;           // (B, C, N) gated maps                        fusion.py:27-28
+  CabSaved blkA, blkB;      // rgb_cross_attention, event_cross_attention  fusion.py:31-32
+  size_t bytes;
+};
+
+FusionSaved fusion_saved_layout(void* base, int B, int C, int N) {
+  Arena a(base, ~(size_t)0 >> 1, base == nullptr);
+  FusionSaved s;
+  size_t cn = (size_t)B * C * N;
+  s.R0 = a.take<float>(cn);
+  s.E0 = a.take<float>(cn);
+  s.R1 = a.take<float>(cn);
+  s.E1 = a.take<float>(cn);
+  size_t cab = cab_saved_layout(nullptr, B, C, N).bytes;
+  char* pa = a.take<char>(cab);
+  char* pb = a.take<char>(cab);
+  s.blkA = cab_saved_layout(pa, B, C, N);
+  s.blkB = cab_saved_layout(pb, B, C, N);
+  if (base == nullptr) { s.blkA.bytes = s.blkB.bytes = cab; }
+  s.bytes = a.off;
+  return s;
+}
+
+int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e,
+                     const frn_refusion_params& p, float* out, const FusionSaved& s) {
+  FRN_TRY(conv1x1(c, p.conv0_rgb_w, p.conv0_rgb_b, a, s.R0, B, C, C, N));   // fusion.py:23
+  FRN_TRY(conv1x1(c, p.conv0_evt_w, p.conv0_evt_b, e, s.E0, B, C, C, N));   // fusion.py:24
+  // fusion.py:26-28 fused with the content statistics both AdaINs need (AdaIN.py:23)
+  RUN(c, gate_stats(c.st, (long)B * C, N, s.R0, s.E0, s.R1, s.E1, kEps, s.blkA.mu_x, s.blkA.sd_x,
+                    s.blkB.mu_x, s.blkB.sd_x));
+  const long ob = 2L * C * N;
+  FRN_TRY(cab_forward(c, B, C, N, s.R1, s.E1, p.rgb_ca, out, ob, s.blkA, true));                 // fusion.py:31
+  FRN_TRY(cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out + (long)C * N, ob, s.blkB, true));  // fusion.py:32,34
+  return FRN_OK;
+}
+
+int refusion_backward(Ctx& c, int B, int C, int N, const float* a, const float* e,
+                      const frn_refusion_params& p, const FusionSaved& s, const float* dout, float* da,
+                      float* de, const frn_refusion_grads& g) {
+  const size_t cn = (size_t)B * C * N;
+  const long ob = 2L * C * N, cnl = (long)C * N;
+  float* dR1 = c.ws.take<float>(cn);
+  float* dE1 = c.ws.take<float>(cn);
+  FRN_TRY(cab_backward(c, B, C, N, s.R1, s.E1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, dE1, 0, g.rgb_ca));
+  FRN_TRY(cab_backward(c, B, C, N, s.E1, s.R1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 1, dR1, 1, g.event_ca));
+  RUN(c, gate_backward(c.st, (long)cn, s.R0, s.E0, dR1, dE1, dR1, dE1));     // fusion.py:26-28
+  FRN_TRY(conv1x1_dgrad(c, p.conv0_rgb_w, dR1, N, 1, cnl, da, B, C, C, N, 0));
+  FRN_TRY(conv1x1_dgrad(c, p.conv0_evt_w, dE1, N, 1, cnl, de, B, C, C, N, 0));
+  FRN_TRY(conv1x1_wgrad(c, dR1, N, 1, cnl, a, g.conv0_rgb_w, g.conv0_rgb_b, B, C, C, N));
+  FRN_TRY(conv1x1_wgrad(c, dE1, N, 1, cnl, e, g.conv0_evt_w, g.conv0_evt_b, B, C, C, N));
+  return FRN_OK;
+}
+
+bool shape_ok(int B, int C, int N) { return B > 0 && C > 0 && N >= 2 && C % 8 == 0; }
+
+// Finish a Ctx for a real call: carve the split-K buffer whose size a dry pass determined.
+template <typename F>
+int with_ctx(void* stream, void* ws, size_t ws_bytes, F body) {
+  Ctx dry(nullptr, nullptr, 0, true);
+  FRN_TRY(body(dry));
+  size_t need = dry.ws.peak + align_up(dry.splitk_need);
+  if (need > 0 && (!ws || ws_bytes < need)) return FRN_ERR_WORKSPACE;
+  Ctx c((cudaStream_t)stream, ws, ws_bytes, false);
+  if (dry.splitk_need) {
+    c.splitk = c.ws.take<char>(dry.splitk_need);
+    c.splitk_cap = dry.splitk_need;
+  }
+  int rc = body(c);
+  if (rc == FRN_OK && !c.ws.ok) rc = FRN_ERR_WORKSPACE;
+  return rc;
+}
+template <typename F>
+size_t dry_bytes(F body) {
+  Ctx dry(nullptr, nullptr, 0, true);
+  if (body(dry) != FRN_OK) return 0;
+  return dry.ws.peak + align_up(dry.splitk_need) + 256;
+}
+
+}  // namespace
+}  // namespace frn
+
+// =============================================================================
+// C ABI
+// =============================================================================
+using namespace frn;
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+int frn_abi_version(void) { return FRN_B200_ABI_VERSION; }
+
+unsigned long long frn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+const char* frn_error_string(int code) {
+  switch (code) {
+    case FRN_OK: return "ok";
+    case FRN_ERR_BAD_SHAPE: return "bad shape (need B > 0, C > 0, C % 8 == 0, H*W >= 2)";
+    case FRN_ERR_NULL_POINTER: return "null pointer";
+    case FRN_ERR_WORKSPACE: return "workspace or saved buffer too small";
+    case FRN_ERR_UNSUPPORTED: return "unsupported configuration";
+    case FRN_ERR_NO_DEVICE: return "no CUDA device";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
+  }
+}
+
+const char* frn_kernel_inventory(void) {
+  return "sgemm_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
+         "gate_stats_kernel,adain_apply_kernel,adain_bwd_reduce_kernel,adain_bwd_content_kernel,"
+         "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
+         "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
+         "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
+         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel";
+}
+
+// ---- AdaIN -------------------------------------------------------------------
+int frn_mean_std(void* stream, int B, int C, int N, const float* feat, float eps, float* mean,
+                 float* std_out) {
+  if (B <= 0 || C <= 0 || N < 2) return FRN_ERR_BAD_SHAPE;
+  if (!feat || !mean || !std_out) return FRN_ERR_NULL_POINTER;
+  return row_mean_std((cudaStream_t)stream, (long)B * C, N, feat, eps, mean, std_out);
+}
+
+int frn_adain_forward(void* stream, int B, int C, int N, const float* content, const float* style,
+                      float* out, float* stats) {
+  if (B <= 0 || C <= 0 || N < 2) return FRN_ERR_BAD_SHAPE;
+  if (!content || !style || !out || !stats) return FRN_ERR_NULL_POINTER;
+  cudaStream_t st = (cudaStream_t)stream;
+  long rows = (long)B * C;
+  float *mu_c = stats, *sd_c = stats + rows, *mu_s = stats + 2 * rows, *sd_s = stats + 3 * rows;
+  FRN_TRY(row_mean_std(st, rows, N, style, kEps, mu_s, sd_s));      // AdaIN.py:22
+  FRN_TRY(row_mean_std(st, rows, N, content, kEps, mu_c, sd_c));    // AdaIN.py:23
+  return adain_apply(st, B, C, N, content, mu_c, sd_c, mu_s, sd_s, out, (long)C * N);  // AdaIN.py:24-26
+}
+
+size_t frn_adain_workspace_bytes(int B, int C, int N) {
+  (void)N;
+  if (B <= 0 || C <= 0) return 0;
+  return 2 * align_up((size_t)B * C * sizeof(float));
+}
+
+int frn_adain_backward(void* stream, int B, int C, int N, const float* content, const float* style,
+                       const float* stats, const float* dout, float* dcontent, float* dstyle, void* ws,
+                       size_t ws_bytes) {
+  if (B <= 0 || C <= 0 || N < 2) return FRN_ERR_BAD_SHAPE;
+  if (!content || !style || !stats || !dout || !dcontent || !dstyle) return FRN_ERR_NULL_POINTER;
+  if (!ws || ws_bytes < frn_adain_workspace_bytes(B, C, N)) return FRN_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  long rows = (long)B * C;
+  const float *mu_c = stats, *sd_c = stats + rows, *mu_s = stats + 2 * rows, *sd_s = stats + 3 * rows;
+  Arena a(ws, ws_bytes);
+  float* g1 = a.take<float>(rows);
+  float* g2 = a.take<float>(rows);
+  long cn = (long)C * N;
+  FRN_TRY(adain_bwd_reduce(st, B, C, N, dout, cn, content, mu_c, sd_c, g1, g2));
+  FRN_TRY(adain_bwd_content(st, B, C, N, dout, cn, content, mu_c, sd_c, sd_s, g1, g2, dcontent, 0));
+  return adain_bwd_style(st, B, C, N, style, mu_s, sd_s, g1, g2, dstyle);
+}
+
+// ---- CrossAttentionBlock -------------------------------------------------------
+size_t frn_cab_saved_bytes(int B, int C, int N) {
+  if (!shape_ok(B, C, N)) return 0;
+  return cab_saved_layout(nullptr, B, C, N).bytes;
+}
+
+size_t frn_cab_workspace_bytes(int B, int C, int N) {
+  if (!shape_ok(B, C, N)) return 0;
+  frn_cab_params p{};
+  frn_cab_grads g{};
+  CabSaved s = cab_saved_layout(nullptr, B, C, N);
+  size_t fwd = dry_bytes([&](Ctx& c) { return cab_forward(c, B, C, N, nullptr, nullptr, p, nullptr, 0, s, false); });
+  size_t bwd = dry_bytes([&](Ctx& c) {
+    return cab_backward(c, B, C, N, nullptr, nullptr, p, s, nullptr, 0, nullptr, 0, nullptr, 0, g);
+  });
+  // forward without a saved buffer keeps its state in the workspace
+  return std::max(fwd + align_up(s.bytes), bwd);
+}
+
+int frn_cab_forward(void* stream, int B, int C, int N, const float* x0, const float* x1,
+                    const frn_cab_params* p, float* out, long out_batch_stride, void* saved,
+                    size_t saved_bytes, void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N)) return FRN_ERR_BAD_SHAPE;
+  if (!x0 || !x1 || !p || !out) return FRN_ERR_NULL_POINTER;
+  size_t need_saved = cab_saved_layout(nullptr, B, C, N).bytes;
+  if (saved && saved_bytes < need_saved) return FRN_ERR_WORKSPACE;
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
+    void* sv = saved;
+    if (!sv) sv = c.ws.take<char>(need_saved);
+    CabSaved s = cab_saved_layout(c.dry ? nullptr : sv, B, C, N);
+    if (!c.dry && !sv) return (int)FRN_ERR_WORKSPACE;
+    return cab_forward(c, B, C, N, x0, x1, *p, out, out_batch_stride, s, false);
+  });
+}
+
+int frn_cab_backward(void* stream, int B, int C, int N, const float* x0, const float* x1,
+                     const frn_cab_params* p, const void* saved, const float* dout,
+                     long dout_batch_stride, float* dx0, float* dx1, int accumulate,
+                     const frn_cab_grads* grads, void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N)) return FRN_ERR_BAD_SHAPE;
+  if (!x0 || !x1 || !p || !saved || !dout || !dx0 || !dx1 || !grads) return FRN_ERR_NULL_POINTER;
+  CabSaved s = cab_saved_layout(const_cast<void*>(saved), B, C, N);
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
+    return cab_backward(c, B, C, N, x0, x1, *p, s, dout, dout_batch_stride, dx0, accumulate, dx1,
+                        accumulate, *grads);
+  });
+}
+
+// ---- REFusion --------------------------------------------------------------------
+size_t frn_refusion_saved_bytes(int B, int C, int N) {
+  if (!shape_ok(B, C, N)) return 0;
+  return fusion_saved_layout(nullptr, B, C, N).bytes;
+}
+
+size_t frn_refusion_workspace_bytes(int B, int C, int N) {
+  if (!shape_ok(B, C, N)) return 0;
+  frn_refusion_params p{};
+  frn_refusion_grads g{};
+  FusionSaved s = fusion_saved_layout(nullptr, B, C, N);
+  size_t fwd = dry_bytes([&](Ctx& c) { return refusion_forward(c, B, C, N, nullptr, nullptr, p, nullptr, s); });
+  size_t bwd = dry_bytes([&](Ctx& c) {
+    return refusion_backward(c, B, C, N, nullptr, nullptr, p, s, nullptr, nullptr, nullptr, g);
+  });
+  return std::max(fwd + align_up(s.bytes), bwd);
+}
+
+int frn_refusion_forward(void* stream, int B, int C, int N, const float* a, const float* e,
+                         const frn_refusion_params* p, float* out, void* saved, size_t saved_bytes,
+                         void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N)) return FRN_ERR_BAD_SHAPE;
+  if (!a || !e || !p || !out) return FRN_ERR_NULL_POINTER;
+  size_t need_saved = fusion_saved_layout(nullptr, B, C, N).bytes;
+  if (saved && saved_bytes < need_saved) return FRN_ERR_WORKSPACE;
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
+    void* sv = saved;
+    if (!sv) sv = c.ws.take<char>(need_saved);
+    if (!c.dry && !sv) return (int)FRN_ERR_WORKSPACE;
+    FusionSaved s = fusion_saved_layout(c.dry ? nullptr : sv, B, C, N);
+    return refusion_forward(c, B, C, N, a, e, *p, out, s);
+  });
+}
+
+int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, const float* e,
+                          const frn_refusion_params* p, const void* saved, const float* dout, float* da,
+                          float* de, const frn_refusion_grads* grads, void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N)) return FRN_ERR_BAD_SHAPE;
+  if (!a || !e || !p || !saved || !dout || !da || !de || !grads) return FRN_ERR_NULL_POINTER;
+  FusionSaved s = fusion_saved_layout(const_cast<void*>(saved), B, C, N);
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
+    return refusion_backward(c, B, C, N, a, e, *p, s, dout, da, de, *grads);
+  });
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

@@ -1,0 +1,261 @@
+// Small glue kernels: per-(sample, channel) coefficient math, bias-gradient
+// row sums, transposes, and the row softmax used by the materialised
+// attention path for d > 64 (retinanet/Attention.py:30).
+#include "common.cuh"
+
+namespace frn {
+namespace {
+
+constexpr float kLog2e = 1.4426950408889634f;
+
+__global__ void style_coeffs_kernel(long rows, int N, const float* __restrict__ g1,
+                                    const float* __restrict__ g2, const float* __restrict__ sd_t,
+                                    float* __restrict__ alpha, float* __restrict__ beta) {
+  long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (i >= rows) return;
+  alpha[i] = g1[i] / (float)N;
+  beta[i] = g2[i] / ((float)(N - 1) * sd_t[i]);
+}
+
+__global__ void finish_style_std_kernel(long rows, int nparts, int N, const float* __restrict__ parts,
+                                        float eps, float* __restrict__ sd_t) {
+  long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (i >= rows) return;
+  float s = 0.f;
+  for (int p = 0; p < nparts; p++) s += parts[i * nparts + p];
+  sd_t[i] = sqrtf(s / (float)(N - 1) + eps);
+}
+
+// out[m] = sum_b sum_n x[b*sb + m*sm + n*sn]; one CTA per m.
+__global__ void __launch_bounds__(256) batch_row_sum_kernel(int B, int M, int N, const float* __restrict__ x,
+                                                            long sb, long sm, long sn,
+                                                            float* __restrict__ out) {
+  __shared__ float red[33];
+  int m = blockIdx.x;
+  float s = 0.f;
+  for (int b = 0; b < B; b++) {
+    const float* p = x + b * sb + m * sm;
+    float t = 0.f;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) t += __ldg(p + n * sn);
+    s += t;
+  }
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) out[m] = s;
+}
+
+__global__ void gate_backward_kernel(long count, const float* __restrict__ r0, const float* __restrict__ e0,
+                                     const float* dr1, const float* de1,
+                                     float* dr0, float* de0) {  // dr0/de0 may alias dr1/de1
+  long stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < count; i += stride) {
+    float r = r0[i], e = e0[i], gr = dr1[i], ge = de1[i];
+    dr0[i] = fmaf(gr, 1.f + e, ge * e);
+    de0[i] = fmaf(ge, 1.f + r, gr * r);
+  }
+}
+__global__ void gate_backward_kernel4(long count4, const float4* __restrict__ r0,
+                                      const float4* __restrict__ e0, const float4* dr1,
+                                      const float4* de1, float4* dr0, float4* de0) {
+  long stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < count4; i += stride) {
+    float4 r = r0[i], e = e0[i], gr = dr1[i], ge = de1[i], a, b;
+    a.x = fmaf(gr.x, 1.f + e.x, ge.x * e.x); b.x = fmaf(ge.x, 1.f + r.x, gr.x * r.x);
+    a.y = fmaf(gr.y, 1.f + e.y, ge.y * e.y); b.y = fmaf(ge.y, 1.f + r.y, gr.y * r.y);
+    a.z = fmaf(gr.z, 1.f + e.z, ge.z * e.z); b.z = fmaf(ge.z, 1.f + r.z, gr.z * r.z);
+    a.w = fmaf(gr.w, 1.f + e.w, ge.w * e.w); b.w = fmaf(ge.w, 1.f + r.w, gr.w * r.w);
+    dr0[i] = a; de0[i] = b;
+  }
+}
+
+// dst (B, cols, rows) <- src (B, rows, cols), 32x32 tiles through smem.
+__global__ void transpose_kernel(int rows, int cols, const float* __restrict__ src, float* __restrict__ dst) {
+  __shared__ float tile[32][33];
+  long bo = (long)blockIdx.z * rows * cols;
+  int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    int r = r0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < rows && c < cols) ? src[bo + (long)r * cols + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < rows && c < cols) dst[bo + (long)c * rows + r] = tile[threadIdx.x][i];
+  }
+}
+
+__global__ void scale_rows_kernel(long total, int C, int K, const float* __restrict__ w,
+                                  const float* __restrict__ beta, float* __restrict__ scaled) {
+  long stride = (long)gridDim.x * blockDim.x;
+  long ck = (long)C * K;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    long b = i / ck, r = i % ck;
+    scaled[i] = beta[b * C + r / K] * w[r];
+  }
+}
+
+// dW[c][k] (+)= scale * sum_b alpha[b][c] * ybar[b][k]
+__global__ void outer_accumulate_kernel(int B, int C, int K, const float* __restrict__ alpha,
+                                        const float* __restrict__ ybar, float scale,
+                                        float* __restrict__ dW) {
+  long total = (long)C * K;
+  long stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    int c = (int)(i / K), k = (int)(i % K);
+    float s = 0.f;
+    for (int b = 0; b < B; b++) s = fmaf(alpha[(long)b * C + c], ybar[(long)b * K + k], s);
+    dW[i] += scale * s;
+  }
+}
+
+__global__ void fill_zero_kernel(float* __restrict__ p, size_t count) {
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += stride) p[i] = 0.f;
+}
+
+__global__ void scale_sum_batch_kernel(int B, int C, const float* __restrict__ alpha, float scale,
+                                       float* __restrict__ out) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f;
+  for (int b = 0; b < B; b++) s += alpha[(long)b * C + c];
+  out[c] = scale * s;
+}
+
+// ---- materialised attention helpers (one CTA per row of length N) -------------
+__global__ void __launch_bounds__(256) softmax_rows_kernel(int N, float* __restrict__ S, float* __restrict__ lse) {
+  __shared__ float red[33];
+  float* r = S + (long)blockIdx.x * N;
+  float mx = -INFINITY;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) mx = fmaxf(mx, r[n]);
+  mx = warp_max(mx);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : -INFINITY;
+    t = warp_max(t);
+    if (threadIdx.x == 0) red[32] = t;
+  }
+  __syncthreads();
+  mx = red[32];
+  float s = 0.f;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    float p = exp2f((r[n] - mx) * kLog2e);
+    r[n] = p;
+    s += p;
+  }
+  s = block_sum(s, red);
+  float inv = 1.f / s;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) r[n] *= inv;
+  if (threadIdx.x == 0) lse[blockIdx.x] = mx + logf(s);
+}
+
+__global__ void __launch_bounds__(256) exp_sub_lse_kernel(int N, float* __restrict__ S, const float* __restrict__ lse) {
+  float* r = S + (long)blockIdx.x * N;
+  float l = lse[blockIdx.x];
+  for (int n = threadIdx.x; n < N; n += blockDim.x) r[n] = exp2f((r[n] - l) * kLog2e);
+}
+
+__global__ void __launch_bounds__(256) ds_from_p_kernel(int N, const float* __restrict__ P, float* __restrict__ dP,
+                                                        const float* __restrict__ delta) {
+  const float* p = P + (long)blockIdx.x * N;
+  float* g = dP + (long)blockIdx.x * N;
+  float de = delta[blockIdx.x];
+  for (int n = threadIdx.x; n < N; n += blockDim.x) g[n] = p[n] * (g[n] - de);
+}
+
+inline int grid_for(long total, int block = 256) {
+  long g = (total + block - 1) / block;
+  if (g > 148L * 16) g = 148L * 16;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace
+
+std::atomic<unsigned long long> g_launches{0};
+
+int style_coeffs(cudaStream_t st, long rows, int N, const float* g1, const float* g2, const float* sd_t,
+                 float* alpha, float* beta) {
+  style_coeffs_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(rows, N, g1, g2, sd_t, alpha, beta);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int finish_style_std(cudaStream_t st, long rows, int nparts, int N, const float* parts, float eps, float* sd_t) {
+  finish_style_std_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(rows, nparts, N, parts, eps, sd_t);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb, long sm, long sn, float* out) {
+  batch_row_sum_kernel<<<M, 256, 0, st>>>(B, M, N, x, sb, sm, sn, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
+                  const float* de1, float* dr0, float* de0) {
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (count % 4 == 0 && al(r0) && al(e0) && al(dr1) && al(de1) && al(dr0) && al(de0)) {
+    gate_backward_kernel4<<<grid_for(count / 4), 256, 0, st>>>(
+        count / 4, (const float4*)r0, (const float4*)e0, (const float4*)dr1, (const float4*)de1,
+        (float4*)dr0, (float4*)de0);
+  } else {
+    gate_backward_kernel<<<grid_for(count), 256, 0, st>>>(count, r0, e0, dr1, de1, dr0, de0);
+  }
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int transpose_batched(cudaStream_t st, int B, int rows, int cols, const float* src, float* dst) {
+  dim3 grid(cdiv(cols, 32), cdiv(rows, 32), B), block(32, 8);
+  transpose_kernel<<<grid, block, 0, st>>>(rows, cols, src, dst);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int scale_rows(cudaStream_t st, int B, int C, int K, const float* w, const float* beta, float* scaled) {
+  long total = (long)B * C * K;
+  scale_rows_kernel<<<grid_for(total), 256, 0, st>>>(total, C, K, w, beta, scaled);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int outer_accumulate(cudaStream_t st, int B, int C, int K, const float* alpha, const float* ybar, float scale,
+                     float* dW) {
+  outer_accumulate_kernel<<<grid_for((long)C * K), 256, 0, st>>>(B, C, K, alpha, ybar, scale, dW);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int fill_zero(cudaStream_t st, float* p, size_t count) {
+  if (count == 0) return FRN_OK;
+  fill_zero_kernel<<<grid_for((long)count), 256, 0, st>>>(p, count);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int scale_sum_batch(cudaStream_t st, int B, int C, const float* alpha, float scale, float* out) {
+  scale_sum_batch_kernel<<<cdiv(C, 256), 256, 0, st>>>(B, C, alpha, scale, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int softmax_rows(cudaStream_t st, long rows, int N, float* S, float* lse) {
+  softmax_rows_kernel<<<(unsigned)rows, 256, 0, st>>>(N, S, lse);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+int exp_sub_lse(cudaStream_t st, long rows, int N, float* S, const float* lse) {
+  exp_sub_lse_kernel<<<(unsigned)rows, 256, 0, st>>>(N, S, lse);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+int ds_from_p(cudaStream_t st, long rows, int N, const float* P, float* dP, const float* delta) {
+  ds_from_p_kernel<<<(unsigned)rows, 256, 0, st>>>(N, P, dP, delta);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+}  // namespace frn

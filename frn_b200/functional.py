@@ -1,0 +1,217 @@
+"""torch.autograd.Functions over the C ABI (libfrn_b200.so).
+
+PyTorch is used for device memory (caching allocator), streams and autograd
+bookkeeping only; every arithmetic op of the fusion block runs in the
+hand-written sm_100a kernels.  CPU tensors are rejected: there is no fallback.
+
+Reference semantics:
+    adain / mean_std   retinanet/AdaIN.py:7-26
+    cross_attention    retinanet/Attention.py:21-36
+    refusion           retinanet/fusion.py:20-36
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+CAB_PARAM_ORDER = ("g_w", "g_b", "theta_w", "theta_b", "phi_w", "phi_b", "W_w", "W_b")
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _check_cuda(*tensors):
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("frn_b200: CUDA tensors required (there is no CPU fallback)")
+
+
+def _f32c(t):
+    return t.detach().to(torch.float32).contiguous()
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def _bytes(n, device):
+    return torch.empty(max(int(n), 16), dtype=torch.uint8, device=device)
+
+
+def _cab_struct(tensors):
+    s = _lib.CabParams()
+    for name, t in zip(CAB_PARAM_ORDER, tensors):
+        setattr(s, name, t.data_ptr())
+    return s
+
+
+def _fusion_struct(conv0, cab_a, cab_b):
+    s = _lib.RefusionParams()
+    s.conv0_rgb_w, s.conv0_rgb_b, s.conv0_evt_w, s.conv0_evt_b = (t.data_ptr() for t in conv0)
+    s.rgb_ca = _cab_struct(cab_a)
+    s.event_ca = _cab_struct(cab_b)
+    return s
+
+
+# --------------------------------------------------------------------------- AdaIN
+def mean_std(feat, eps=1e-5):
+    """AdaIN_block.calc_mean_std (AdaIN.py:7-15); not differentiable through this entry."""
+    _check_cuda(feat)
+    lib = _lib.load()
+    b, c = feat.shape[:2]
+    x = _f32c(feat).view(b, c, -1)
+    n = x.shape[2]
+    mean = torch.empty(b * c, dtype=torch.float32, device=x.device)
+    std = torch.empty_like(mean)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.frn_mean_std(_stream(), b, c, n, _ptr(x), eps, _ptr(mean), _ptr(std)), "mean_std")
+    return mean.view(b, c, 1, 1).to(feat.dtype), std.view(b, c, 1, 1).to(feat.dtype)
+
+
+class _AdaINFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, content, style):
+        _check_cuda(content, style)
+        lib = _lib.load()
+        b, c = content.shape[:2]
+        x, t = _f32c(content), _f32c(style)
+        n = x[0, 0].numel()
+        out = torch.empty_like(x)
+        stats = torch.empty(4 * b * c, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.frn_adain_forward(_stream(), b, c, n, _ptr(x), _ptr(t), _ptr(out), _ptr(stats)),
+                       "adain_forward")
+        ctx.save_for_backward(x, t, stats)
+        ctx.dims = (b, c, n)
+        ctx.in_dtypes = (content.dtype, style.dtype)
+        return out.to(content.dtype)
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.load()
+        x, t, stats = ctx.saved_tensors
+        b, c, n = ctx.dims
+        g = _f32c(dout)
+        dx, dt = torch.empty_like(x), torch.empty_like(t)
+        with torch.cuda.device(x.device):
+            ws_bytes = lib.frn_adain_workspace_bytes(b, c, n)
+            ws = _bytes(ws_bytes, x.device)
+            _lib.check(lib.frn_adain_backward(_stream(), b, c, n, _ptr(x), _ptr(t), _ptr(stats), _ptr(g),
+                                              _ptr(dx), _ptr(dt), _ptr(ws), ws_bytes), "adain_backward")
+        return dx.to(ctx.in_dtypes[0]), dt.to(ctx.in_dtypes[1])
+
+
+def adain(content, style):
+    return _AdaINFn.apply(content, style)
+
+
+# --------------------------------------------------------------------------- CrossAttentionBlock
+class _CabFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x0, x1, *params):
+        _check_cuda(x0, x1, *params)
+        lib = _lib.load()
+        b, c, h, w = x0.shape
+        n = h * w
+        a, e = _f32c(x0), _f32c(x1)
+        prm = [_f32c(p) for p in params]
+        out = torch.empty_like(a)
+        need_grad = any(ctx.needs_input_grad)
+        with torch.cuda.device(a.device):
+            ws_bytes = lib.frn_cab_workspace_bytes(b, c, n)
+            ws = _bytes(ws_bytes, a.device)
+            saved, saved_bytes = None, 0
+            if need_grad:
+                saved_bytes = lib.frn_cab_saved_bytes(b, c, n)
+                saved = _bytes(saved_bytes, a.device)
+            st = _cab_struct(prm)
+            _lib.check(lib.frn_cab_forward(_stream(), b, c, n, _ptr(a), _ptr(e), C.byref(st), _ptr(out), c * n,
+                                           _ptr(saved) if need_grad else None, saved_bytes, _ptr(ws), ws_bytes),
+                       "cab_forward")
+        if need_grad:
+            ctx.save_for_backward(a, e, saved, *prm)
+        ctx.dims = (b, c, n)
+        ctx.in_dtypes = (x0.dtype, x1.dtype) + tuple(p.dtype for p in params)
+        return out.to(x0.dtype)
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.load()
+        a, e, saved, *prm = ctx.saved_tensors
+        b, c, n = ctx.dims
+        g = _f32c(dout)
+        da, de = torch.empty_like(a), torch.empty_like(e)
+        grads = [torch.empty_like(p) for p in prm]
+        with torch.cuda.device(a.device):
+            ws_bytes = lib.frn_cab_workspace_bytes(b, c, n)
+            ws = _bytes(ws_bytes, a.device)
+            st, gst = _cab_struct(prm), _cab_struct(grads)
+            _lib.check(lib.frn_cab_backward(_stream(), b, c, n, _ptr(a), _ptr(e), C.byref(st), _ptr(saved),
+                                            _ptr(g), c * n, _ptr(da), _ptr(de), 0, C.byref(gst), _ptr(ws),
+                                            ws_bytes), "cab_backward")
+        dts = ctx.in_dtypes
+        return (da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
+
+
+def cross_attention(x0, x1, g_w, g_b, theta_w, theta_b, phi_w, phi_b, W_w, W_b):
+    return _CabFn.apply(x0, x1, g_w, g_b, theta_w, theta_b, phi_w, phi_b, W_w, W_b)
+
+
+# --------------------------------------------------------------------------- REFusion
+class _REFusionFn(torch.autograd.Function):
+    """params: conv0_rgb (w, b), conv0_evt (w, b), rgb_cross_attention (8), event_cross_attention (8)."""
+
+    @staticmethod
+    def forward(ctx, rgb, evt, *params):
+        _check_cuda(rgb, evt, *params)
+        lib = _lib.load()
+        b, c, h, w = rgb.shape
+        n = h * w
+        a, e = _f32c(rgb), _f32c(evt)
+        prm = [_f32c(p) for p in params]
+        out = torch.empty((b, 2 * c, h, w), dtype=torch.float32, device=a.device)
+        need_grad = any(ctx.needs_input_grad)
+        with torch.cuda.device(a.device):
+            ws_bytes = lib.frn_refusion_workspace_bytes(b, c, n)
+            ws = _bytes(ws_bytes, a.device)
+            saved, saved_bytes = None, 0
+            if need_grad:
+                saved_bytes = lib.frn_refusion_saved_bytes(b, c, n)
+                saved = _bytes(saved_bytes, a.device)
+            st = _fusion_struct(prm[0:4], prm[4:12], prm[12:20])
+            _lib.check(lib.frn_refusion_forward(_stream(), b, c, n, _ptr(a), _ptr(e), C.byref(st), _ptr(out),
+                                                _ptr(saved) if need_grad else None, saved_bytes, _ptr(ws),
+                                                ws_bytes), "refusion_forward")
+        if need_grad:
+            ctx.save_for_backward(a, e, saved, *prm)
+        ctx.dims = (b, c, n)
+        ctx.in_dtypes = (rgb.dtype, evt.dtype) + tuple(p.dtype for p in params)
+        return out.to(rgb.dtype)
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.load()
+        a, e, saved, *prm = ctx.saved_tensors
+        b, c, n = ctx.dims
+        g = _f32c(dout)
+        da, de = torch.empty_like(a), torch.empty_like(e)
+        grads = [torch.empty_like(p) for p in prm]
+        with torch.cuda.device(a.device):
+            ws_bytes = lib.frn_refusion_workspace_bytes(b, c, n)
+            ws = _bytes(ws_bytes, a.device)
+            st = _fusion_struct(prm[0:4], prm[4:12], prm[12:20])
+            gst = _fusion_struct(grads[0:4], grads[4:12], grads[12:20])
+            _lib.check(lib.frn_refusion_backward(_stream(), b, c, n, _ptr(a), _ptr(e), C.byref(st), _ptr(saved),
+                                                 _ptr(g), _ptr(da), _ptr(de), C.byref(gst), _ptr(ws), ws_bytes),
+                       "refusion_backward")
+        dts = ctx.in_dtypes
+        return (da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
+
+
+def refusion(rgb, evt, conv0, rgb_ca, event_ca):
+    """conv0: (rgb_w, rgb_b, evt_w, evt_b); rgb_ca / event_ca: 8 tensors in CAB_PARAM_ORDER."""
+    return _REFusionFn.apply(rgb, evt, *conv0, *rgb_ca, *event_ca)

@@ -1,0 +1,98 @@
+"""Drop-in nn.Modules with the reference's constructors, forward signatures and
+state-dict keys, backed by the sm_100a kernels.
+
+    AdaIN_block            retinanet/AdaIN.py:3-26
+    CrossAttentionBlock    retinanet/Attention.py:7-36
+    REFusion               retinanet/fusion.py:7-36
+
+The nn.Conv2d submodules are parameter containers only (their weights keep the
+reference's (out, in, 1, 1) shape so published checkpoints load unchanged,
+SURVEY.md section 5 "Checkpoint / resume"); their forward is never called.
+"""
+from __future__ import annotations
+
+import torch.nn as nn
+
+from . import functional as F
+
+
+def c2_xavier_fill(module: nn.Module) -> None:
+    """fvcore.nn.weight_init.c2_xavier_fill as used at Attention.py:16-17:
+    kaiming_uniform_(a=1) on the weight, zeros on the bias."""
+    nn.init.kaiming_uniform_(module.weight, a=1)
+    if module.bias is not None:
+        nn.init.constant_(module.bias, 0)
+
+
+class AdaIN_block(nn.Module):
+    def __init__(self):
+        super().__init__()
+
+    def calc_mean_std(self, feat, eps=1e-5):
+        size = feat.size()
+        assert (len(size) == 4)                                   # AdaIN.py:10
+        return F.mean_std(feat, eps)
+
+    def forward(self, rgb, evt):
+        assert (rgb.size()[:2] == evt.size()[:2])                 # AdaIN.py:20
+        assert len(rgb.size()) == 4 and len(evt.size()) == 4      # AdaIN.py:10 (via calc_mean_std)
+        return F.adain(rgb, evt)
+
+
+def _conv_params(conv):
+    return conv.weight, conv.bias
+
+
+class CrossAttentionBlock(nn.Module):
+    def __init__(self, in_channels):
+        super().__init__()
+        self.g = nn.Conv2d(in_channels, in_channels // 8, kernel_size=1, stride=1, padding=0)
+        self.theta = nn.Conv2d(in_channels, in_channels // 8, kernel_size=1, stride=1, padding=0)
+        self.phi = nn.Conv2d(in_channels, in_channels // 8, kernel_size=1, stride=1, padding=0)
+        self.W = nn.Conv2d(in_channels // 8, in_channels, kernel_size=1, stride=1, padding=0)
+        for layer in [self.g, self.theta, self.phi, self.W]:
+            c2_xavier_fill(layer)
+        self.adain = AdaIN_block()
+
+    def kernel_params(self):
+        """The 8 tensors in the order the C ABI's frn_cab_params expects."""
+        return (*_conv_params(self.g), *_conv_params(self.theta), *_conv_params(self.phi),
+                *_conv_params(self.W))
+
+    def forward(self, x):
+        x0, x1 = x[0], x[1]
+        assert len(x0.size()) == 4
+        assert x0.size() == x1.size()
+        return F.cross_attention(x0, x1, *self.kernel_params())
+
+
+class REFusion(nn.Module):
+    def __init__(self, in_planes, out_planes):
+        super().__init__()
+        # fusion.py:12-17 builds CrossAttentionBlock(in_planes) on conv0 outputs of out_planes
+        # channels: the reference constructs with any pair but its forward only works (and is only
+        # called, model.py:248-251) with in_planes == out_planes.  Same here: forward checks.
+        self.in_planes, self.out_planes = in_planes, out_planes
+        self.rgb_cross_attention = CrossAttentionBlock(in_planes)
+        self.event_cross_attention = CrossAttentionBlock(in_planes)
+        self.conv0_rgb = nn.Conv2d(in_planes, out_planes, kernel_size=1, stride=1, padding=0)
+        self.conv0_evt = nn.Conv2d(out_planes, out_planes, kernel_size=1, stride=1, padding=0)
+
+    def forward(self, rgb, evt):
+        assert len(rgb.size()) == 4
+        assert rgb.size() == evt.size()
+        if self.in_planes != self.out_planes or rgb.size(1) != self.in_planes:
+            raise RuntimeError("REFusion: expected in_planes == out_planes == input channels "
+                               f"(got {self.in_planes}, {self.out_planes}, {rgb.size(1)})")
+        conv0 = (*_conv_params(self.conv0_rgb), *_conv_params(self.conv0_evt))
+        return F.refusion(rgb, evt, conv0, self.rgb_cross_attention.kernel_params(),
+                          self.event_cross_attention.kernel_params())
+
+
+def fusion_parameters(model: nn.Module):
+    """Parameters that belong to REFusion modules of `model` (the allreduce set)."""
+    seen = []
+    for m in model.modules():
+        if isinstance(m, REFusion):
+            seen.extend(m.parameters())
+    return seen

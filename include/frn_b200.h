@@ -1,0 +1,151 @@
+/*
+ * frn_b200.h -- C ABI of the B200-native FRN fusion block.
+ *
+ * The reference (JinkaiLiu/FRN) is pure Python and has no FFI of its own; the
+ * entry points below are what a binding for its fusion path would call.  Each
+ * one names the reference interface it replaces (paths relative to the
+ * reference repository):
+ *
+ *   frn_mean_std            AdaIN_block.calc_mean_std      retinanet/AdaIN.py:7-15
+ *   frn_adain_forward/...   AdaIN_block.forward            retinanet/AdaIN.py:17-26
+ *   frn_cab_forward/...     CrossAttentionBlock.forward    retinanet/Attention.py:21-36
+ *   frn_refusion_forward/.. REFusion.forward               retinanet/fusion.py:20-36
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer on the current CUDA device unless the
+ *     parameter is documented otherwise.  Feature maps are NCHW-contiguous
+ *     (the layout retinanet/model.py:305-308 hands over), N = H*W.
+ *   - `stream` is a cudaStream_t passed as void*.  Calls only enqueue work;
+ *     they never synchronise, never allocate, and keep no global mutable
+ *     state (re-entrant: nn.DataParallel calls one thread per device).
+ *   - The caller owns every buffer, including `saved` (forward state kept for
+ *     backward) and `ws` (scratch, free to reuse after the call's work is
+ *     complete on `stream`).  Sizes come from the *_bytes() queries.
+ *   - Return value: FRN_OK (0) or a negative FRN_ERR_* code; CUDA launch
+ *     errors are returned as the positive cudaError_t value.  Nothing throws.
+ *   - dtype: FRN_F32 only for gradients and parameters.  Activations may be
+ *     FRN_F32 or FRN_BF16 where a `dtype` argument exists.
+ *   - Conv weights are the reference's (out, in, 1, 1) tensors viewed as
+ *     row-major (out, in) matrices; biases are (out).
+ */
+#ifndef FRN_B200_H_
+#define FRN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FRN_B200_ABI_VERSION 1
+
+enum {
+  FRN_OK = 0,
+  FRN_ERR_BAD_SHAPE = -1,      /* non-positive size, C % 8 != 0, N < 2 ...        */
+  FRN_ERR_NULL_POINTER = -2,
+  FRN_ERR_WORKSPACE = -3,      /* ws_bytes / saved_bytes smaller than required    */
+  FRN_ERR_UNSUPPORTED = -4,    /* C/8 > 256, unknown dtype ...                    */
+  FRN_ERR_NO_DEVICE = -5
+};
+
+enum { FRN_F32 = 0, FRN_BF16 = 1 };
+
+/* Parameters of one CrossAttentionBlock (retinanet/Attention.py:11-15). */
+typedef struct frn_cab_params {
+  const float* g_w;     const float* g_b;      /* (C/8, C), (C/8) */
+  const float* theta_w; const float* theta_b;  /* (C/8, C), (C/8) */
+  const float* phi_w;   const float* phi_b;    /* (C/8, C), (C/8) */
+  const float* W_w;     const float* W_b;      /* (C, C/8), (C)   */
+} frn_cab_params;
+
+typedef struct frn_cab_grads {
+  float* g_w;     float* g_b;
+  float* theta_w; float* theta_b;
+  float* phi_w;   float* phi_b;
+  float* W_w;     float* W_b;
+} frn_cab_grads;
+
+/* Parameters of one REFusion (retinanet/fusion.py:12-17). */
+typedef struct frn_refusion_params {
+  const float* conv0_rgb_w; const float* conv0_rgb_b;  /* (C, C), (C) */
+  const float* conv0_evt_w; const float* conv0_evt_b;  /* (C, C), (C) */
+  frn_cab_params rgb_ca;     /* rgb_cross_attention   */
+  frn_cab_params event_ca;   /* event_cross_attention */
+} frn_refusion_params;
+
+typedef struct frn_refusion_grads {
+  float* conv0_rgb_w; float* conv0_rgb_b;
+  float* conv0_evt_w; float* conv0_evt_b;
+  frn_cab_grads rgb_ca;
+  frn_cab_grads event_ca;
+} frn_refusion_grads;
+
+int frn_abi_version(void);
+const char* frn_error_string(int code);
+/* Comma-separated list of the kernels compiled into the library (for audits). */
+const char* frn_kernel_inventory(void);
+
+/* ---- AdaIN (retinanet/AdaIN.py) ------------------------------------------ */
+
+/* calc_mean_std: feat (B, C, N) -> mean, std each (B*C).  std = sqrt(unbiased
+ * variance + eps).  AdaIN.py:7-15. */
+int frn_mean_std(void* stream, int B, int C, int N, const float* feat, float eps,
+                 float* mean, float* std_out);
+
+/* AdaIN_block.forward(content, style) -> out (B, C, N).  stats (4*B*C floats:
+ * mu_c, sd_c, mu_s, sd_s) is kept for backward.  AdaIN.py:17-26. */
+int frn_adain_forward(void* stream, int B, int C, int N, const float* content,
+                      const float* style, float* out, float* stats);
+/* Gradients of AdaIN_block.forward wrt content and style. ws: frn_adain_workspace_bytes. */
+int frn_adain_backward(void* stream, int B, int C, int N, const float* content,
+                       const float* style, const float* stats, const float* dout,
+                       float* dcontent, float* dstyle, void* ws, size_t ws_bytes);
+size_t frn_adain_workspace_bytes(int B, int C, int N);
+
+/* ---- CrossAttentionBlock (retinanet/Attention.py) ------------------------- */
+
+size_t frn_cab_saved_bytes(int B, int C, int N);
+size_t frn_cab_workspace_bytes(int B, int C, int N);
+
+/* CrossAttentionBlock.forward([x0, x1]) -> out.  out has batch stride
+ * out_batch_stride elements (C*N for a stand-alone block, 2*C*N when writing
+ * one half of REFusion's concatenated output).  saved may be NULL for
+ * inference (then nothing is kept).  Attention.py:21-36. */
+int frn_cab_forward(void* stream, int B, int C, int N, const float* x0, const float* x1,
+                    const frn_cab_params* p, float* out, long out_batch_stride,
+                    void* saved, size_t saved_bytes, void* ws, size_t ws_bytes);
+
+/* dout has batch stride dout_batch_stride.  dx0 / dx1 are OVERWRITTEN when
+ * accumulate == 0 and added to when accumulate != 0.  Parameter gradients are
+ * overwritten (summed over the batch). */
+int frn_cab_backward(void* stream, int B, int C, int N, const float* x0, const float* x1,
+                     const frn_cab_params* p, const void* saved, const float* dout,
+                     long dout_batch_stride, float* dx0, float* dx1, int accumulate,
+                     const frn_cab_grads* grads, void* ws, size_t ws_bytes);
+
+/* ---- REFusion (retinanet/fusion.py) -------------------------------------- */
+
+size_t frn_refusion_saved_bytes(int B, int C, int N);
+size_t frn_refusion_workspace_bytes(int B, int C, int N);
+
+/* REFusion.forward(rgb=a, evt=e) -> out (B, 2C, N); channels [0, C) come from
+ * rgb_cross_attention([rgb1, evt1]), [C, 2C) from event_cross_attention
+ * ([evt1, rgb1]).  fusion.py:20-36.  saved may be NULL for inference. */
+int frn_refusion_forward(void* stream, int B, int C, int N, const float* a, const float* e,
+                         const frn_refusion_params* p, float* out,
+                         void* saved, size_t saved_bytes, void* ws, size_t ws_bytes);
+
+int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, const float* e,
+                          const frn_refusion_params* p, const void* saved, const float* dout,
+                          float* da, float* de, const frn_refusion_grads* grads,
+                          void* ws, size_t ws_bytes);
+
+/* Number of kernel launches issued by this library since load, on all threads
+ * (monotonic counter; bench.py reports the delta over the timed region). */
+unsigned long long frn_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* FRN_B200_H_ */
