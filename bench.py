@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py -- fusion-block fwd+bwd samples/s at DSEC 640x480 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+
+One "step" = REFusion forward + backward over all four FPN levels (C = 256/512/1024/2048 at
+120x160 / 60x80 / 30x40 / 15x20) for a batch of DSEC-shaped synthetic feature maps, i.e.
+BASELINE.json configs[1] ("full fusion stack across all FPN levels, batch=8, DSEC 640x480 synthetic
+features, fp32 on 1xB200").  N > 1: one process per GPU (torchrun), the batch is sharded by sample
+(weak scaling: 8 samples per GPU) and the fusion-parameter gradients are all-reduced over NCCL.
+
+Prints ONE JSON line (rank 0).  `value` is device-resident throughput, `e2e` includes the H2D copy
+of every step's inputs from pinned host memory and a D2H read of the step's gradient norm.
+`--impl reference` times the reference's own CPU arithmetic (oracle/fusion_torch.py: the same ATen
+call sequence as retinanet/fusion.py, since /root/reference does not exist on the GPU box).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+# DSEC 480x640 level shapes: (C, H, W)
+DSEC_LEVELS = [(256, 120, 160), (512, 60, 80), (1024, 30, 40), (2048, 15, 20)]
+SUM_NC = sum(c * h * w for c, h, w in DSEC_LEVELS)                       # 9 216 000
+# Algorithmic figures per sample, fwd+bwd, fp32 (SURVEY.md 8d / DESIGN.md):
+HBM_BYTES_PER_SAMPLE = 10 * 4 * SUM_NC                                   # 368 640 000
+FLOPS_FWD = sum(6 * h * w * c * c + (h * w) ** 2 * c for c, h, w in DSEC_LEVELS)
+FLOPS_BWD = sum(12 * h * w * c * c + 2.5 * (h * w) ** 2 * c for c, h, w in DSEC_LEVELS)
+METRIC = "fusion-block fwd+bwd samples/s at DSEC 640x480"
+
+
+def attn_flops(c, n, bwd):
+    """Algorithmic FLOPs of one streaming-attention launch per sample-block: fwd 4 N^2 d, bwd 10 N^2 d."""
+    d = c // 8
+    return (10.0 if bwd else 4.0) * n * n * d
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "tf_burst": p["bf16_tflops"], "tf_sustained": p["bf16_tflops_sustained"],
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_port_step(levels, batch, threads):
+    """One fwd+bwd of the 4-level stack for `batch` samples with the reference's ATen sequence on CPU."""
+    from oracle import fusion_torch as ot
+    torch.set_num_threads(threads)
+    t0 = time.perf_counter()
+    for k, (c, h, w) in enumerate(levels):
+        g = torch.Generator().manual_seed(1000 + k)
+        prm = ot.init_params(c, seed=0)
+        for b in range(batch):     # B=1 at a time: the reference materialises N x N (1.47 GB at level 1)
+            a = torch.randn(1, c, h, w, generator=g).relu()
+            e = torch.randn(1, c, h, w, generator=g).relu()
+            dout = torch.randn(1, 2 * c, h, w, generator=g)
+            ot.refusion_fwd_bwd(a, e, prm, dout)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path, all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    budget, t_start = 240.0, time.perf_counter()      # keep the whole arm within a few minutes
+    warm = 0
+    for _ in range(args.warmup):
+        if warm >= 1 and time.perf_counter() - t_start > budget / 4:
+            break
+        cpu_port_step(DSEC_LEVELS, 1, threads)
+        warm += 1
+    t = []
+    for _ in range(args.steps):
+        if t and time.perf_counter() - t_start > budget:
+            break
+        t.append(cpu_port_step(DSEC_LEVELS, 1, threads))
+    args.steps_ref, args.warmup_ref = len(t), warm
+    sec = sum(t) / len(t)
+    value = 1.0 / sec
+    sample = (f"{args.steps_ref} timed steps (+{args.warmup_ref} warm-up), each 1 sample of the 4-level DSEC stack "
+              "fwd+bwd, fp32, oracle/fusion_torch.py (same ATen call sequence as retinanet/fusion.py)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+        "steps": args.steps_ref, "warmup": args.warmup_ref, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "full fusion stack, 4 FPN levels, DSEC 480x640, fp32 (configs[1]); CPU arm runs "
+                               "batch 1 per step (the reference's N x N matrices need ~7 GB per sample)"},
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_ours(args):
+    import torch.distributed as dist
+
+    import frn_b200
+    from frn_b200 import _lib
+    from frn_b200.dist import GradBucket
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    B = args.batch                      # per-GPU batch (weak scaling)
+    levels = DSEC_LEVELS
+
+    # modules + synthetic DSEC-shaped inputs (seeds per SURVEY.md 8d)
+    torch.manual_seed(0)
+    mods = [frn_b200.REFusion(c, c).to(dev) for c, _, _ in levels]
+    params = [p for m in mods for p in m.parameters()]
+    for p in params:
+        p.grad = torch.zeros_like(p)
+    bucket = GradBucket(params)
+    host_a, host_e, dev_a, dev_e, douts = [], [], [], [], []
+    for k, (c, h, w) in enumerate(levels):
+        g = torch.Generator().manual_seed(1000 + k + 17 * rank)
+        a = torch.randn(B, c, h, w, generator=g).relu()
+        e = torch.randn(B, c, h, w, generator=g).relu()
+        host_a.append(a.pin_memory()); host_e.append(e.pin_memory())
+        dev_a.append(a.to(dev).requires_grad_(True)); dev_e.append(e.to(dev).requires_grad_(True))
+        douts.append(torch.randn(B, 2 * c, h, w, generator=g).to(dev))
+    h2d_bytes = sum(t.numel() * 4 for t in host_a + host_e)
+    norm_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def step_resident():
+        bucket.zero()
+        for m, a, e, go in zip(mods, dev_a, dev_e, douts):
+            a.grad = None; e.grad = None
+            m(a, e).backward(go)
+        bucket.allreduce(average=True)
+
+    stage_a = [torch.empty_like(t, device=dev) for t in host_a]
+    stage_e = [torch.empty_like(t, device=dev) for t in host_e]
+
+    def step_e2e():
+        bucket.zero()
+        for m, ha, he, sa, se, go in zip(mods, host_a, host_e, stage_a, stage_e, douts):
+            sa.copy_(ha, non_blocking=True); se.copy_(he, non_blocking=True)     # H2D from pinned memory
+            a = sa.detach().requires_grad_(True); e = se.detach().requires_grad_(True)
+            m(a, e).backward(go)
+        bucket.allreduce(average=True)
+        norm_host.copy_(torch.linalg.vector_norm(bucket.flat).reshape(1), non_blocking=True)   # D2H result
+        torch.cuda.current_stream().synchronize()
+        return float(norm_host[0])
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        sync_all()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        sync_all()
+        ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms[0])
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    sync_all()
+
+    # ---- timed region 1: device-resident inputs -------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.frn_timing_enable(1)
+    for cls in range(4):
+        lib.frn_timing_read(cls, C.byref(C.c_double()), C.byref(C.c_long()))
+    launches0 = lib.frn_launch_count()
+    ms_total = timed(step_resident, args.steps)
+    launches = lib.frn_launch_count() - launches0
+    classes = {}
+    for name, cls in (("attn_fwd", 0), ("attn_bwd", 1), ("gemm", 2), ("rows", 3)):
+        ms, n = C.c_double(), C.c_long()
+        lib.frn_timing_read(cls, C.byref(ms), C.byref(n))
+        classes[name] = {"ms": ms.value, "launches": n.value}
+    lib.frn_timing_enable(0)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- timed region 2: end to end through the public modules, host inputs ------------
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = measured_peaks()
+    samples = world * B * args.steps
+    value = samples / (ms_total / 1e3)
+    e2e_value = samples / (ms_e2e / 1e3)
+    # dominant kernel: streaming attention backward.  Levels 1-2 use it (two blocks each), per step:
+    # flops = B * 2 blocks * sum_l 10 N^2 d
+    fl_bwd = B * 2 * sum(attn_flops(c, h * w, True) for c, h, w in levels if c // 8 <= 64)
+    fl_fwd = B * 2 * sum(attn_flops(c, h * w, False) for c, h, w in levels if c // 8 <= 64)
+    t_bwd = classes["attn_bwd"]["ms"] / 1e3 / args.steps
+    t_fwd = classes["attn_fwd"]["ms"] / 1e3 / args.steps
+    ach = fl_bwd / t_bwd / 1e12 if t_bwd > 0 else 0.0
+    roofline = {"bound": "tensor", "kernel": "attn_bwd_kernel (streaming-softmax attention backward, levels 1-2)",
+                "achieved": ach, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                "frac": ach / peaks["tf_sustained"], "traffic": None,
+                "peak_source": peaks["source"] + ", bf16 sustained; kernel runs fp32 FFMA for 1e-5 parity",
+                "share_of_step": classes["attn_bwd"]["ms"] / ms_total,
+                "attn_fwd_tflops": fl_fwd / t_fwd / 1e12 if t_fwd > 0 else 0.0,
+                "class_ms_per_step": {k: v["ms"] / args.steps for k, v in classes.items()},
+                "block_hbm_frac": HBM_BYTES_PER_SAMPLE * value / world / 1e9 / peaks["hbm_gbs"],
+                "block_tensor_frac": (FLOPS_FWD + FLOPS_BWD) * value / world / 1e12 / peaks["tf_sustained"]}
+    cores = os.cpu_count() or 1
+    cpu_s = cpu_port_step(levels, 1, cores) if not args.no_cpu else None
+    if cpu_s is not None:
+        cpu_s = min(cpu_s, cpu_port_step(levels, 1, cores))       # second pass: oneDNN warm
+    line = {
+        "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"full fusion stack, 4 FPN levels, batch={B} per GPU, DSEC 480x640 synthetic "
+                               "features, fp32 (BASELINE.json configs[1])",
+                   "levels": [[B, c, h, w] for c, h, w in levels], "global_batch": world * B,
+                   "parallelism": f"dp{world} (batch shard + NCCL allreduce of {bucket.flat.numel()} fusion grads)",
+                   "l2": f"inputs+saved state per step >> 126 MB L2 ({h2d_bytes / 1e6:.0f} MB of inputs alone); no flush"},
+        "clocks": clocks, "gpu_launches": int(launches),
+        "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
+        "roofline": roofline,
+        "cpu_baseline": None if cpu_s is None else {
+            "value": 1.0 / cpu_s, "unit": "samples/s", "cores": cores, "kind": "port",
+            "sample": "best of 2 passes of 1 sample through the 4-level DSEC stack fwd+bwd, fp32, "
+                      "oracle/fusion_torch.py (ATen call sequence of retinanet/fusion.py)"},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="samples per GPU per step")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.steps_ref, args.warmup_ref = args.steps, args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

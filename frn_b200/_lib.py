@@ -56,6 +56,8 @@ _SIGNATURES = {
     "frn_refusion_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.POINTER(RefusionParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.POINTER(RefusionParams), C.c_void_p, C.c_size_t]),
+    "frn_timing_enable": (None, [C.c_int]),
+    "frn_timing_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]),
 }
 
 EXPORTS = tuple(_SIGNATURES)

@@ -267,6 +267,7 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // Dispatch on row length (warp- or CTA-per-row) and vector width.
 #define LAUNCH_ROWS(KERNEL, rows, N, vec, ...)                                            \
   do {                                                                                    \
+    ScopedTimer tm__(st, FRN_TIME_ROWS);                                                  \
     if ((N) >= 1024) {                                                                    \
       if (vec) KERNEL<256, 4><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);             \
       else KERNEL<256, 1><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);                 \

@@ -206,6 +206,7 @@ int launch_fwd(cudaStream_t st, int B, int N, int d, const float* Qc, const floa
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   dim3 grid(cdiv(N, BM), B);
+  ScopedTimer tm(st, FRN_TIME_ATTN_FWD);
   kern<<<grid, kThreads, smem, st>>>(N, d, Qc, Kc, Vp, Y, lse);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
@@ -406,6 +407,7 @@ int launch_bwd(cudaStream_t st, int B, int N, int d, const float* Qc, const floa
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   dim3 grid(cdiv(N, BN), B);
+  ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
   kern<<<grid, kThreads, smem, st>>>(N, d, Qc, Qp, Kc, Kp, Vc, dYc, dYp, lse, delta, dQp, dKp, dVp);
   FRN_LAUNCH_CHECK();
   return FRN_OK;

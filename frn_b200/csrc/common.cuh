@@ -22,6 +22,13 @@ extern std::atomic<unsigned long long> g_launches;
     if (rc__ != FRN_OK) return rc__; \
   } while (0)
 
+// Optional per-class kernel timing (include/frn_b200.h "measurement hooks").
+struct ScopedTimer {
+  cudaStream_t st; int cls; cudaEvent_t e0; bool on;
+  ScopedTimer(cudaStream_t s, int c);
+  ~ScopedTimer();
+};
+
 static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 

@@ -276,6 +276,7 @@ int gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
   if (d.M <= 0 || d.N <= 0 || d.K <= 0 || d.batch <= 0) return FRN_ERR_BAD_SHAPE;
   if ((d.sAm != 1 && d.sAk != 1) || (d.sBn != 1 && d.sBk != 1)) return FRN_ERR_UNSUPPORTED;
   Plan pl = make_plan(d);
+  ScopedTimer tm(st, FRN_TIME_GEMM);
   if (d.reduce_batch && pl.nsplit > 1) {
     size_t need = (size_t)pl.nsplit * d.M * d.N * sizeof(float);
     if (!ws || ws_bytes < need) return FRN_ERR_WORKSPACE;
@@ -296,6 +297,7 @@ int gemm_rowsumsq_parts(int N) { return cdiv(N, 128); }
 int gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
   if (d.M <= 0 || d.N <= 0 || d.K <= 0 || d.batch <= 0 || d.reduce_batch) return FRN_ERR_BAD_SHAPE;
   Plan pl = make_plan(d);
+  ScopedTimer tm(st, FRN_TIME_GEMM);
   return launch<GEMM_EPI_ROWSUMSQ>(st, d, pl, out_partial);
 }
 

@@ -1,6 +1,9 @@
 // Small glue kernels: per-(sample, channel) coefficient math, bias-gradient
 // row sums, transposes, and the row softmax used by the materialised
 // attention path for d > 64 (retinanet/Attention.py:30).
+#include <mutex>
+#include <utility>
+#include <vector>
 #include "common.cuh"
 
 namespace frn {
@@ -175,6 +178,27 @@ inline int grid_for(long total, int block = 256) {
 
 std::atomic<unsigned long long> g_launches{0};
 
+namespace {
+std::atomic<int> g_timing_on{0};
+std::mutex g_timing_mu;
+std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events[FRN_TIME_CLASSES];
+}  // namespace
+
+ScopedTimer::ScopedTimer(cudaStream_t s, int c) : st(s), cls(c), e0(nullptr), on(false) {
+  if (!g_timing_on.load(std::memory_order_relaxed)) return;
+  if (cudaEventCreate(&e0) != cudaSuccess) return;
+  cudaEventRecord(e0, st);
+  on = true;
+}
+ScopedTimer::~ScopedTimer() {
+  if (!on) return;
+  cudaEvent_t e1;
+  if (cudaEventCreate(&e1) != cudaSuccess) { cudaEventDestroy(e0); return; }
+  cudaEventRecord(e1, st);
+  std::lock_guard<std::mutex> lk(g_timing_mu);
+  g_events[cls].emplace_back(e0, e1);
+}
+
 int style_coeffs(cudaStream_t st, long rows, int N, const float* g1, const float* g2, const float* sd_t,
                  float* alpha, float* beta) {
   style_coeffs_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(rows, N, g1, g2, sd_t, alpha, beta);
@@ -259,3 +283,28 @@ int ds_from_p(cudaStream_t st, long rows, int N, const float* P, float* dP, cons
 }
 
 }  // namespace frn
+
+#pragma GCC visibility push(default)
+extern "C" {
+void frn_timing_enable(int on) { frn::g_timing_on.store(on ? 1 : 0); }
+int frn_timing_read(int cls, double* ms, long* launches) {
+  if (cls < 0 || cls >= FRN_TIME_CLASSES || !ms || !launches) return FRN_ERR_BAD_SHAPE;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
+  {
+    std::lock_guard<std::mutex> lk(frn::g_timing_mu);
+    ev.swap(frn::g_events[cls]);
+  }
+  double total = 0.0;
+  for (auto& p : ev) {
+    float t = 0.f;
+    cudaEventSynchronize(p.second);
+    if (cudaEventElapsedTime(&t, p.first, p.second) == cudaSuccess) total += t;
+    cudaEventDestroy(p.first);
+    cudaEventDestroy(p.second);
+  }
+  *ms = total;
+  *launches = (long)ev.size();
+  return FRN_OK;
+}
+}
+#pragma GCC visibility pop

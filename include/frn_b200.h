@@ -145,6 +145,19 @@ int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, con
  * (monotonic counter; bench.py reports the delta over the timed region). */
 unsigned long long frn_launch_count(void);
 
+/* ---- measurement hooks (bench.py / profiling only) --------------------------
+ * When enabled, the library brackets its hot kernels with cudaEvents on the
+ * launching stream.  Classes: 0 = streaming attention forward, 1 = streaming
+ * attention backward, 2 = fp32 GEMM (all 1x1 projections and their gradients),
+ * 3 = row kernels (statistics / AdaIN / gate).  frn_timing_read synchronises
+ * the recorded events, returns their summed duration in milliseconds and the
+ * number of launches, and clears the class.  Off by default; the only global
+ * mutable state in the library besides the launch counter. */
+enum { FRN_TIME_ATTN_FWD = 0, FRN_TIME_ATTN_BWD = 1, FRN_TIME_GEMM = 2, FRN_TIME_ROWS = 3,
+       FRN_TIME_CLASSES = 4 };
+void frn_timing_enable(int on);
+int frn_timing_read(int cls, double* ms, long* launches);
+
 #ifdef __cplusplus
 }
 #endif
