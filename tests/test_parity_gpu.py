@@ -59,6 +59,14 @@ def _check_ill_conditioned(name, d, params, got):
         o.update({k: rel_l2(np.asarray(g[k]), ref[3][k]) for k in ref[3] if not k.endswith("theta.bias")})
         return o
     ours, theirs = errs(got), errs(t32)
+    # theta/phi gradients are ~1e-5 here against ~50 for the other parameters (softmax rows are
+    # uniform to 6 digits): both fp32 implementations return rounding noise for them, so they are
+    # bounded absolutely, at 1e-5 of the block's largest gradient entry.
+    gscale = max(float(np.abs(v).max()) for v in ref[3].values())
+    tiny = {k for k, v in ref[3].items() if float(np.abs(v).max()) < 1e-5 * gscale}
+    for k in tiny - {k for k in tiny if k.endswith("theta.bias")}:
+        assert float(np.abs(np.asarray(got[3][k]) - ref[3][k]).max()) <= 1e-5 * gscale, k
+        ours.pop(k); theirs.pop(k)
     bad = {k: (ours[k], theirs[k]) for k in ours if ours[k] > max(2e-4, 3 * theirs[k])}
     assert not bad, f"{name}: worse than 3x the fp32 ATen restatement: {bad}"
     assert np.isfinite(got[0]).all()
