@@ -26,6 +26,13 @@ class RefusionParams(C.Structure):
                 ("rgb_ca", CabParams), ("event_ca", CabParams)]
 
 
+class GemmDesc(C.Structure):
+    _fields_ = ([("A", C.c_void_p), ("B", C.c_void_p), ("C", C.c_void_p)] +
+                [(n, C.c_int) for n in ("M", "N", "K", "batch")] +
+                [(n, C.c_long) for n in ("sAm", "sAk", "sAb", "sBk", "sBn", "sBb", "sCm", "sCn", "sCb")] +
+                [("bias_m", C.c_void_p), ("bias_n", C.c_void_p), ("accumulate", C.c_int), ("reduce_batch", C.c_int)])
+
+
 # name -> (restype, argtypes); mirrors include/frn_b200.h one to one
 _SIGNATURES = {
     "frn_abi_version": (C.c_int, []),
@@ -56,6 +63,10 @@ _SIGNATURES = {
     "frn_refusion_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.POINTER(RefusionParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.POINTER(RefusionParams), C.c_void_p, C.c_size_t]),
+    "frn_gemm_workspace_bytes": (C.c_size_t, [C.POINTER(GemmDesc)]),
+    "frn_gemm_f32": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(GemmDesc), C.c_void_p, C.c_size_t]),
+    "frn_set_gemm_engine": (None, [C.c_int]),
+    "frn_get_gemm_engine": (C.c_int, []),
     "frn_timing_enable": (None, [C.c_int]),
     "frn_timing_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]),
 }

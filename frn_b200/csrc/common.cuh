@@ -92,13 +92,26 @@ struct GemmDesc {
   long sBk, sBn, sBb;
   long sCm, sCn, sCb;
   const float* bias_m;   // length M (+ b*bias_bs) or nullptr
-  long bias_bs;          // batch stride of bias_m (0: shared)
+  const float* bias_n;   // length N (+ b*bias_bs) or nullptr
+  long bias_bs;          // batch stride of bias_m / bias_n (0: shared)
   float alpha;
   int accumulate;        // C += result
   int reduce_batch;
 };
 enum { GEMM_EPI_STORE = 0, GEMM_EPI_ROWSUMSQ = 1 };
 
+// Engine: 0 = FFMA (gemm.cu), 1 = tcgen05 3xTF32 (tc_gemm.cu).  Default from FRN_GEMM_ENGINE
+// ("ffma" / "tc"), see gemm_engine().
+__global__ void splitk_reduce_kernel(const float* __restrict__ part, int nsplit, int M, int N,
+                                     float* __restrict__ C, long sCm, long sCn, int accumulate);
+int gemm_engine();
+void set_gemm_engine(int e);
+size_t tc_gemm_workspace_bytes(const GemmDesc& d);
+int tc_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);
+int tc_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
+size_t ffma_gemm_workspace_bytes(const GemmDesc& d);
+int ffma_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);
+int ffma_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
 size_t gemm_workspace_bytes(const GemmDesc& d);
 // ws: split-K partials (only used when reduce_batch); may be null if bytes == 0.
 int gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);

@@ -412,13 +412,33 @@ const char* frn_error_string(int code) {
 }
 
 const char* frn_kernel_inventory(void) {
-  return "sgemm_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
+  return "sgemm_kernel,tc_gemm_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
          "gate_stats_kernel,adain_apply_kernel,adain_bwd_reduce_kernel,adain_bwd_content_kernel,"
          "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
          "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
          "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel";
 }
+
+// ---- GEMM ----------------------------------------------------------------------
+static GemmDesc from_public(const frn_gemm_desc* g) {
+  GemmDesc d{};
+  d.A = g->A; d.B = g->B; d.C = g->C; d.M = g->M; d.N = g->N; d.K = g->K; d.batch = g->batch;
+  d.sAm = g->sAm; d.sAk = g->sAk; d.sAb = g->sAb; d.sBk = g->sBk; d.sBn = g->sBn; d.sBb = g->sBb;
+  d.sCm = g->sCm; d.sCn = g->sCn; d.sCb = g->sCb;
+  d.bias_m = g->bias_m; d.bias_n = g->bias_n; d.alpha = 1.f;
+  d.accumulate = g->accumulate; d.reduce_batch = g->reduce_batch;
+  return d;
+}
+size_t frn_gemm_workspace_bytes(const frn_gemm_desc* g) { return g ? gemm_workspace_bytes(from_public(g)) : 0; }
+int frn_gemm_f32(void* stream, int engine, const frn_gemm_desc* g, void* ws, size_t ws_bytes) {
+  if (!g || !g->A || !g->B || !g->C) return FRN_ERR_NULL_POINTER;
+  GemmDesc d = from_public(g);
+  if (engine < 0) engine = gemm_engine();
+  return engine ? tc_gemm((cudaStream_t)stream, d, ws, ws_bytes) : ffma_gemm((cudaStream_t)stream, d, ws, ws_bytes);
+}
+void frn_set_gemm_engine(int engine) { set_gemm_engine(engine); }
+int frn_get_gemm_engine(void) { return gemm_engine(); }
 
 // ---- AdaIN -------------------------------------------------------------------
 int frn_mean_std(void* stream, int B, int C, int N, const float* feat, float eps, float* mean,

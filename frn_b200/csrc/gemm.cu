@@ -7,6 +7,7 @@
 //
 // Tiling: BMxBN output tile per CTA, BK-deep smem stages (double buffered via
 // registers), TMxTN register tile per thread read with 128-bit LDS.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace frn {
@@ -152,7 +153,11 @@ sgemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_spli
     int gm = m0 + (i / 4) * SM_STRIDE + ty * 4 + (i % 4);
     float bias = (!partial && p.bias_m && gm < p.M) ? __ldg(p.bias_m + (p.reduce_batch ? 0 : (long)z * p.bias_bs) + gm) : 0.f;
 #pragma unroll
-    for (int j = 0; j < TN; j++) acc[i][j] = fmaf(p.alpha, acc[i][j], bias);
+    for (int j = 0; j < TN; j++) {
+      int gn = n0 + (j / 4) * SN_STRIDE + tx * 4 + (j % 4);
+      float bn = (!partial && p.bias_n && gn < p.N) ? __ldg(p.bias_n + (p.reduce_batch ? 0 : (long)z * p.bias_bs) + gn) : 0.f;
+      acc[i][j] = fmaf(p.alpha, acc[i][j], bias + bn);
+    }
   }
   if (vec_n) {
 #pragma unroll
@@ -210,6 +215,7 @@ sgemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_spli
   }
 }
 
+}  // namespace
 // C[m][n] (+)= sum_z part[z][m][n]
 __global__ void splitk_reduce_kernel(const float* __restrict__ part, int nsplit, int M, int N,
                                      float* __restrict__ C, long sCm, long sCn, int accumulate) {
@@ -224,6 +230,7 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, int nsplit,
   }
 }
 
+namespace {
 struct Plan { int bm, bn, ktiles, nsplit, tiles_per_split; };
 constexpr int kBK = 16;
 
@@ -266,13 +273,13 @@ int launch(cudaStream_t st, const GemmDesc& d, const Plan& pl, float* aux) {
 
 }  // namespace
 
-size_t gemm_workspace_bytes(const GemmDesc& d) {
+size_t ffma_gemm_workspace_bytes(const GemmDesc& d) {
   if (!d.reduce_batch) return 0;
   Plan pl = make_plan(d);
   return pl.nsplit > 1 ? align_up((size_t)pl.nsplit * d.M * d.N * sizeof(float)) : 0;
 }
 
-int gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
+int ffma_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
   if (d.M <= 0 || d.N <= 0 || d.K <= 0 || d.batch <= 0) return FRN_ERR_BAD_SHAPE;
   if ((d.sAm != 1 && d.sAk != 1) || (d.sBn != 1 && d.sBk != 1)) return FRN_ERR_UNSUPPORTED;
   Plan pl = make_plan(d);
@@ -294,11 +301,38 @@ int gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
 
 int gemm_rowsumsq_parts(int N) { return cdiv(N, 128); }
 
-int gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
+int ffma_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
   if (d.M <= 0 || d.N <= 0 || d.K <= 0 || d.batch <= 0 || d.reduce_batch) return FRN_ERR_BAD_SHAPE;
   Plan pl = make_plan(d);
   ScopedTimer tm(st, FRN_TIME_GEMM);
   return launch<GEMM_EPI_ROWSUMSQ>(st, d, pl, out_partial);
+}
+
+// ---- engine dispatch ---------------------------------------------------------------
+namespace {
+std::atomic<int> g_engine{-1};
+}
+int gemm_engine() {
+  int e = g_engine.load(std::memory_order_relaxed);
+  if (e < 0) {
+    const char* s = getenv("FRN_GEMM_ENGINE");
+    e = (s && (s[0] == 't' || s[0] == 'T' || s[0] == '1')) ? 1 : 0;   // default: FFMA
+    g_engine.store(e);
+  }
+  return e;
+}
+void set_gemm_engine(int e) { g_engine.store(e ? 1 : 0); }
+
+size_t gemm_workspace_bytes(const GemmDesc& d) {
+  // the larger of the two so that a workspace sized once serves either engine
+  size_t a = ffma_gemm_workspace_bytes(d), b = tc_gemm_workspace_bytes(d);
+  return a > b ? a : b;
+}
+int gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
+  return gemm_engine() ? tc_gemm(st, d, ws, ws_bytes) : ffma_gemm(st, d, ws, ws_bytes);
+}
+int gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
+  return gemm_engine() ? tc_gemm_rowsumsq(st, d, out_partial) : ffma_gemm_rowsumsq(st, d, out_partial);
 }
 
 }  // namespace frn

@@ -145,6 +145,25 @@ int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, con
  * (monotonic counter; bench.py reports the delta over the timed region). */
 unsigned long long frn_launch_count(void);
 
+/* ---- strided batched fp32 GEMM (stage-level entry point for unit parity) -------
+ * C[b][m][n] (+)= sum_k A[b][m][k] * B[b][k][n] + bias_m[m] + bias_n[n] with element strides
+ * (one of sAm/sAk and one of sBk/sBn must be 1).  reduce_batch != 0 sums the product over the
+ * batch into a single C (weight gradients).  engine: 0 = FFMA kernel, 1 = tcgen05 3xTF32
+ * kernel, -1 = the library default (frn_set_gemm_engine / env FRN_GEMM_ENGINE=ffma|tc).
+ * Every 1x1 conv of the block and its gradients go through this routine
+ * (retinanet/fusion.py:23-24, retinanet/Attention.py:24-27,34). */
+typedef struct frn_gemm_desc {
+  const float* A; const float* B; float* C;
+  int M, N, K, batch;
+  long sAm, sAk, sAb, sBk, sBn, sBb, sCm, sCn, sCb;
+  const float* bias_m; const float* bias_n;
+  int accumulate, reduce_batch;
+} frn_gemm_desc;
+size_t frn_gemm_workspace_bytes(const frn_gemm_desc* d);
+int frn_gemm_f32(void* stream, int engine, const frn_gemm_desc* d, void* ws, size_t ws_bytes);
+void frn_set_gemm_engine(int engine);
+int frn_get_gemm_engine(void);
+
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
  * launching stream.  Classes: 0 = streaming attention forward, 1 = streaming
