@@ -284,6 +284,8 @@ def run_ours(args):
                                "features, fp32 (BASELINE.json configs[1])",
                    "levels": [[B, c, h, w] for c, h, w in levels], "global_batch": world * B,
                    "parallelism": f"dp{world} (batch shard + NCCL allreduce of {bucket.flat.numel()} fusion grads)",
+                   "engines": {"attention": ["ffma", "tcgen05"][lib.frn_get_attn_engine()],
+                               "gemm": ["ffma", "tcgen05"][lib.frn_get_gemm_engine()]},
                    "l2": f"inputs+saved state per step >> 126 MB L2 ({h2d_bytes / 1e6:.0f} MB of inputs alone); no flush"},
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,

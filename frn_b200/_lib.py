@@ -67,6 +67,8 @@ _SIGNATURES = {
     "frn_gemm_f32": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(GemmDesc), C.c_void_p, C.c_size_t]),
     "frn_set_gemm_engine": (None, [C.c_int]),
     "frn_get_gemm_engine": (C.c_int, []),
+    "frn_set_attn_engine": (None, [C.c_int]),
+    "frn_get_attn_engine": (C.c_int, []),
     "frn_timing_enable": (None, [C.c_int]),
     "frn_timing_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]),
 }

@@ -124,6 +124,12 @@ int gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
 // Y: (B, N, d) row-major; lse: (B, N).
 int attn_forward(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc,
                  const float* Vp, float* Y, float* lse);
+// tcgen05 engine (attention_tc.cu): all operands channel-major (B, d, N).
+int attn_forward_tc(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc,
+                    const float* Vc, float* Y, float* lse);
+// 0 = FFMA kernels (attention.cu), 1 = tcgen05 kernels; default from FRN_ATTN_ENGINE ("ffma" / "tc").
+int attn_engine();
+void set_attn_engine(int e);
 // Backward needs both orientations: *c = (B, d, N), *p = (B, N, d).
 // dQp must be zero-initialised by the caller (accumulated with atomics).
 int attn_backward(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Qp,

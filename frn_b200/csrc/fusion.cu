@@ -121,7 +121,11 @@ int chunk_for_scores(int B, int N, int mats) {
 // softmax(Q K) V for all samples.  d <= 64: fused streaming kernel; else GEMM + row softmax.
 int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
   if (d <= 64) {
-    float* Vp = c.ws.take<float>((size_t)B * N * d);
+    float* Vp = c.ws.take<float>((size_t)B * N * d);   // (taken on both engines: sizes stay engine-independent)
+    if (attn_engine() == 1) {
+      RUN(c, attn_forward_tc(c.st, B, N, d, s.Qc, s.Kc, s.Vc, s.Y, s.lse));
+      return FRN_OK;
+    }
     RUN(c, transpose_batched(c.st, B, d, N, s.Vc, Vp));
     RUN(c, attn_forward(c.st, B, N, d, s.Qc, s.Kc, Vp, s.Y, s.lse));
     return FRN_OK;
@@ -412,7 +416,7 @@ const char* frn_error_string(int code) {
 }
 
 const char* frn_kernel_inventory(void) {
-  return "sgemm_kernel,tc_gemm_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
+  return "sgemm_kernel,tc_gemm_kernel,attn_fwd_tc_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
          "gate_stats_kernel,adain_apply_kernel,adain_bwd_reduce_kernel,adain_bwd_content_kernel,"
          "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
@@ -438,6 +442,8 @@ int frn_gemm_f32(void* stream, int engine, const frn_gemm_desc* g, void* ws, siz
   return engine ? tc_gemm((cudaStream_t)stream, d, ws, ws_bytes) : ffma_gemm((cudaStream_t)stream, d, ws, ws_bytes);
 }
 void frn_set_gemm_engine(int engine) { set_gemm_engine(engine); }
+void frn_set_attn_engine(int engine) { set_attn_engine(engine); }
+int frn_get_attn_engine(void) { return attn_engine(); }
 int frn_get_gemm_engine(void) { return gemm_engine(); }
 
 // ---- AdaIN -------------------------------------------------------------------

@@ -323,6 +323,20 @@ int gemm_engine() {
 }
 void set_gemm_engine(int e) { g_engine.store(e ? 1 : 0); }
 
+namespace {
+std::atomic<int> g_attn_engine{-1};
+}
+int attn_engine() {
+  int e = g_attn_engine.load(std::memory_order_relaxed);
+  if (e < 0) {
+    const char* s = getenv("FRN_ATTN_ENGINE");
+    e = (s && (s[0] == 't' || s[0] == 'T' || s[0] == '1')) ? 1 : 0;   // default: FFMA
+    g_attn_engine.store(e);
+  }
+  return e;
+}
+void set_attn_engine(int e) { g_attn_engine.store(e ? 1 : 0); }
+
 size_t gemm_workspace_bytes(const GemmDesc& d) {
   // the larger of the two so that a workspace sized once serves either engine
   size_t a = ffma_gemm_workspace_bytes(d), b = tc_gemm_workspace_bytes(d);

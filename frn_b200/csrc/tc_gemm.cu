@@ -28,7 +28,7 @@ template <int BN> struct TcCfg {
   static constexpr int kBBytes = BN * TBK * 4;
   static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-  static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+  static constexpr int kTmemCols = 2 * BN;               // [0, BN): hi*hi ; [BN, 2BN): lo*hi + hi*lo
 };
 
 // Stage a [ROWS x 32] K-major tile: element (r, k) = g[r*rs + k*ks], zero outside (rows, kvalid).
@@ -131,10 +131,12 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       uint64_t b_lo = umma_desc_sw128(base + 2 * Cfg::kABytes + Cfg::kBBytes);
 #pragma unroll
       for (int k = 0; k < TBK / 8; k++) {   // +32 bytes per K = 8 slice: start-address field += 2
-        umma_tf32_ss(tmem_acc, a_lo + 2 * k, b_hi + 2 * k, idesc, acc);
+        // The tensor core truncates when it aligns addends to the accumulator, so the two
+        // correction terms (2^-11 of the main term) get their own accumulator (columns [BN, 2BN)).
+        umma_tf32_ss(tmem_acc + BN, a_lo + 2 * k, b_hi + 2 * k, idesc, acc);
+        umma_tf32_ss(tmem_acc + BN, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
+        umma_tf32_ss(tmem_acc, a_hi + 2 * k, b_hi + 2 * k, idesc, acc);
         acc = true;
-        umma_tf32_ss(tmem_acc, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
-        umma_tf32_ss(tmem_acc, a_hi + 2 * k, b_hi + 2 * k, idesc, true);
       }
       umma_commit(&empty[stage]);            // frees the stage once these MMAs have read it
       if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -156,11 +158,11 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       float s = 0.f;
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 16) {
-        float v[16];
-        if (any) { tmem_ld16(taddr + c0, v); tmem_wait_ld(); }
+        float v[16], w[16];
+        if (any) { tmem_ld16(taddr + c0, v); tmem_ld16(taddr + BN + c0, w); tmem_wait_ld(); }
 #pragma unroll
         for (int j = 0; j < 16; j++) {
-          float x = any ? p.alpha * v[j] : 0.f;
+          float x = any ? p.alpha * (v[j] + w[j]) : 0.f;
           s += (n0 + c0 + j < p.N) ? x * x : 0.f;
         }
       }
@@ -175,9 +177,12 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 16) {
-        float v[16];
-        if (any) { tmem_ld16(taddr + c0, v); tmem_wait_ld(); }
-        else {
+        float v[16], w[16];
+        if (any) {
+          tmem_ld16(taddr + c0, v); tmem_ld16(taddr + BN + c0, w); tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 16; j++) v[j] += w[j];
+        } else {
 #pragma unroll
           for (int j = 0; j < 16; j++) v[j] = 0.f;
         }

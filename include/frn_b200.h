@@ -163,6 +163,9 @@ size_t frn_gemm_workspace_bytes(const frn_gemm_desc* d);
 int frn_gemm_f32(void* stream, int engine, const frn_gemm_desc* d, void* ws, size_t ws_bytes);
 void frn_set_gemm_engine(int engine);
 int frn_get_gemm_engine(void);
+/* Attention core engine: 0 = FFMA streaming kernels, 1 = tcgen05/TMEM kernels (env FRN_ATTN_ENGINE). */
+void frn_set_attn_engine(int engine);
+int frn_get_attn_engine(void);
 
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
