@@ -65,6 +65,9 @@ _SIGNATURES = {
                                         C.c_void_p, C.POINTER(RefusionParams), C.c_void_p, C.c_size_t]),
     "frn_gemm_workspace_bytes": (C.c_size_t, [C.POINTER(GemmDesc)]),
     "frn_gemm_f32": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(GemmDesc), C.c_void_p, C.c_size_t]),
+    "frn_attn_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_attn_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_size_t]),
+    "frn_attn_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 10 + [C.c_size_t]),
     "frn_set_gemm_engine": (None, [C.c_int]),
     "frn_get_gemm_engine": (C.c_int, []),
     "frn_set_attn_engine": (None, [C.c_int]),

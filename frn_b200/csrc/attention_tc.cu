@@ -1,18 +1,26 @@
 // tcgen05 / TMEM streaming-softmax attention for CrossAttentionBlock
-// (retinanet/Attention.py:29-32), split-precision (3xTF32) so that fp32 parity holds.
+// (retinanet/Attention.py:29-32) and its backward, split-precision (3xTF32) so that fp32 parity
+// holds: every fp32 operand x is carried as a tf32 pair (hi, lo), and each product is accumulated
+// as hi*hi' (main accumulator) and lo*hi' + hi*lo' (a second, 2^-11-sized accumulator) in fp32
+// TMEM columns.
 //
-// Forward, one CTA per 128 query rows, 64-key tiles, 9 warps:
-//   warps 0-3  softmax: thread = query row.  Read S from TMEM, online softmax in registers,
-//              write P (tf32 hi / lo) back to TMEM, promote the previous tile's P.V product
-//              from TMEM into fp32 register accumulators (rescaled there, so Y in TMEM never
-//              needs a correction pass and no accumulation chain exceeds 8 tensor-core steps:
-//              tcgen05 truncates when it aligns addends, ~0.4 ulp bias per step, which over
-//              N/8 = 2400 steps would cost 6e-5).
-//   warp  4    one thread issues tcgen05.mma: S = Q.K (A, B from shared memory) and
-//              Y_tile = P.V (A = P from TMEM, B = V from shared memory).
-//   warps 5-8  operand staging: global (channel-major d x N, as the projection GEMM wrote it)
-//              -> tf32 hi/lo split -> SWIZZLE_128B K-major shared memory tiles.
-// The 2^-11-sized correction products (lo.hi + hi.lo) accumulate in their own TMEM columns.
+// Operands reach shared memory by bulk async copies (cp.async.bulk, one elected thread, mbarrier
+// transaction counts) from PACKED SPLIT IMAGES: a small pre-pass (pack_split_kernel) writes each
+// (B, d, N) operand as tf32 hi / lo planes that already have the SWIZZLE_128B K-major tile layout
+// the UMMA descriptors expect, zero padded to 128 positions, so a tile is one contiguous chunk:
+//   pos image   rows = positions, 128-byte rows of 32 channels   (Q.K^T style products)
+//   chan image  rows = channels, 128-byte rows of 32 positions   (P.V style products)
+//
+// tcgen05 truncates (does not round) when it aligns addends to the accumulator, a relative bias
+// of ~3e-9 per K = 8 step (tools/tc_error_vs_k.py).  No accumulation chain here is longer than 8
+// steps: every tile product is promoted from TMEM into fp32 register accumulators.
+//
+// Kernels (d <= 64; larger d goes through the GEMM engine, see fusion.cu):
+//   attn_fwd_tc_kernel   CTA = 128 queries, 64-key tiles, double-buffered S, online softmax
+//   attn_dq_tc_kernel    CTA = NQ x 128 queries (ping-pong), 32-key tiles: S, dP -> dS -> dQ
+//   attn_dkv_tc_kernel   CTA = NKT x 128 keys (ping-pong), 32-query tiles: S^T, dP^T -> P^T, dS^T
+//                        -> dV, dK   (d = 64: one 32-channel half of dV / dK per CTA)
+// No atomics anywhere: the backward is deterministic.
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -22,59 +30,145 @@ namespace {
 using namespace tc;
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int ABM = 128;   // query rows per CTA (UMMA M)
-constexpr int ABN = 64;    // keys per tile
-constexpr int kSoftmaxThreads = 128, kLoaderThreads = 128, kAttnThreads = 288;
 
-// Stage a [ROWS x 32] K-major SWIZZLE_128B tile pair (hi, lo); element (r, k) = g[r*rs + k*ks].
-template <int ROWS>
-__device__ __forceinline__ void stage_split(float* __restrict__ hi, float* __restrict__ lo,
-                                            const float* __restrict__ g, long rs, long ks, int rows, int kvalid,
-                                            int tid) {
-  constexpr int CHUNKS = ROWS * 8;
-  const bool kfast = (ks == 1);
-  const bool vec = kfast && ((rs & 3) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
-#pragma unroll 2
-  for (int idx = tid; idx < CHUNKS; idx += kLoaderThreads) {
-    int r, c;
-    if (kfast) { c = idx & 7; r = idx >> 3; } else { r = idx % ROWS; c = idx / ROWS; }
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    if (r < rows) {
-      const float* p = g + (long)r * rs + (long)(c * 4) * ks;
-      if (vec && c * 4 + 3 < kvalid) {
-        float4 t = __ldg(reinterpret_cast<const float4*>(p));
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-      } else {
-#pragma unroll
-        for (int q = 0; q < 4; q++)
-          if (c * 4 + q < kvalid) v[q] = __ldg(p + (long)q * ks);
-      }
+// ------------------------------------------------------------------------------------------------
+// packed split images
+// ------------------------------------------------------------------------------------------------
+// X element (c, n) of sample b at X[b*bs + c*cs + n*ns]; sub (optional): per-(b, c) value subtracted
+// first (the key operand is centred over positions, see attn_tc_pack).  grid (NP/32, B), 256 threads.
+template <int DPAD>
+__global__ void __launch_bounds__(256)
+pack_split_kernel(const float* __restrict__ X, const float* __restrict__ sub, long bs, long cs, long ns, int d,
+                  int N, int NP, float* __restrict__ pos_hi, float* __restrict__ pos_lo, float* __restrict__ chan_hi,
+                  float* __restrict__ chan_lo) {
+  constexpr int kSub = DPAD / 32;
+  __shared__ float tile[DPAD][33];
+  const int b = blockIdx.y, n0 = blockIdx.x * 32, tid = threadIdx.x;
+  const float* Xb = X + (long)b * bs;
+  for (int idx = tid; idx < DPAD * 32; idx += 256) {
+    int c, nl;
+    if (ns == 1) { c = idx >> 5; nl = idx & 31; } else { c = idx % DPAD; nl = idx / DPAD; }
+    float v = 0.f;
+    if (c < d && n0 + nl < N) {
+      v = __ldg(Xb + (long)c * cs + (long)(n0 + nl) * ns);
+      if (sub) v -= __ldg(sub + (long)b * d + c);
     }
-    float h[4], l[4];
+    tile[c][nl] = v;
+  }
+  __syncthreads();
+  if (pos_hi) {
+    for (int idx = tid; idx < kSub * 32 * 8; idx += 256) {
+      const int chunk = idx & 7, nl = (idx >> 3) & 31, s = idx >> 8;
+      const int n = n0 + nl;
+      float h[4], l[4];
 #pragma unroll
-    for (int q = 0; q < 4; q++) split_tf32(v[q], h[q], l[q]);
-    int o = sw128_chunk_offset(r, c);
-    *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+      for (int q = 0; q < 4; q++) split_tf32(tile[s * 32 + chunk * 4 + q][nl], h[q], l[q]);
+      const long o = (((long)b * kSub + s) * NP + n) * 32 + ((chunk ^ (n & 7)) << 2);
+      *reinterpret_cast<float4*>(pos_hi + o) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(pos_lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+  }
+  if (chan_hi) {
+    for (int idx = tid; idx < DPAD * 8; idx += 256) {
+      const int chunk = idx & 7, c = idx >> 3;
+      float h[4], l[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) split_tf32(tile[c][chunk * 4 + q], h[q], l[q]);
+      const long o = (((long)b * (NP / 32) + blockIdx.x) * DPAD + c) * 32 + ((chunk ^ (c & 7)) << 2);
+      *reinterpret_cast<float4*>(chan_hi + o) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(chan_lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+    }
   }
 }
+
+// delta[b][n] = sum_k dY[b][n][k] * Y[b][n][k] and a copy of lse, both padded to NP positions
+// (lse = +inf, delta = 0 beyond N, so padded queries get P = exp(S - inf) = 0).
+__global__ void attn_bwd_prep_kernel(int N, int NP, int d, const float* __restrict__ dYp,
+                                     const float* __restrict__ Y, const float* __restrict__ lse,
+                                     float* __restrict__ lse_pad, float* __restrict__ delta_pad) {
+  const int b = blockIdx.y;
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= NP) return;
+  float l = INFINITY, dl = 0.f;
+  if (n < N) {
+    const float* a = dYp + ((long)b * N + n) * d;
+    const float* y = Y + ((long)b * N + n) * d;
+    l = lse[(long)b * N + n];
+    if ((d & 3) == 0) {
+      for (int k = 0; k < d; k += 4) {
+        float4 u = __ldg(reinterpret_cast<const float4*>(a + k));
+        float4 v = __ldg(reinterpret_cast<const float4*>(y + k));
+        dl = fmaf(u.x, v.x, dl); dl = fmaf(u.y, v.y, dl); dl = fmaf(u.z, v.z, dl); dl = fmaf(u.w, v.w, dl);
+      }
+    } else {
+      for (int k = 0; k < d; k++) dl = fmaf(__ldg(a + k), __ldg(y + k), dl);
+    }
+  }
+  lse_pad[(long)b * NP + n] = l;
+  delta_pad[(long)b * NP + n] = dl;
+}
+
+// 3xTF32 products of one 32-deep K sub-tile (4 K = 8 slices of 32 bytes each) into ONE fp32
+// accumulator.  The 2^-11-sized correction terms a_lo.b_hi + a_hi.b_lo of ALL sub-tiles are issued
+// first and the main terms a_hi.b_hi after them: the tensor core truncates the smaller addend when
+// it aligns it to the accumulator, so corrections added to an already large accumulator would lose
+// their low bits at every step, whereas in this order they are truncated once (when the first main
+// term arrives) -- the same accuracy as a separate accumulator at half the TMEM read traffic
+// (tcgen05.ld bandwidth is what bounds these kernels).
+__device__ __forceinline__ void mma_corr_ss(uint32_t dst, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi,
+                                            uint32_t b_lo, uint32_t idesc, bool first) {
+  const uint64_t ah = umma_desc_sw128(a_hi), al = umma_desc_sw128(a_lo);
+  const uint64_t bh = umma_desc_sw128(b_hi), bl = umma_desc_sw128(b_lo);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    umma_tf32_ss(dst, al + 2 * k, bh + 2 * k, idesc, !(first && k == 0));
+    umma_tf32_ss(dst, ah + 2 * k, bl + 2 * k, idesc, true);
+  }
+}
+__device__ __forceinline__ void mma_main_ss(uint32_t dst, uint32_t a_hi, uint32_t b_hi, uint32_t idesc) {
+  const uint64_t ah = umma_desc_sw128(a_hi), bh = umma_desc_sw128(b_hi);
+#pragma unroll
+  for (int k = 0; k < 4; k++) umma_tf32_ss(dst, ah + 2 * k, bh + 2 * k, idesc, true);
+}
+// Same with A = 32 TMEM columns (hi at a_hi, lo at a_lo; lane = row), B one 32-deep sub-tile.
+__device__ __forceinline__ void mma_corr_ts(uint32_t dst, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi,
+                                            uint32_t b_lo, uint32_t idesc, bool first) {
+  const uint64_t bh = umma_desc_sw128(b_hi), bl = umma_desc_sw128(b_lo);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    umma_tf32_ts(dst, a_lo + 8 * k, bh + 2 * k, idesc, !(first && k == 0));
+    umma_tf32_ts(dst, a_hi + 8 * k, bl + 2 * k, idesc, true);
+  }
+}
+__device__ __forceinline__ void mma_main_ts(uint32_t dst, uint32_t a_hi, uint32_t b_hi, uint32_t idesc) {
+  const uint64_t bh = umma_desc_sw128(b_hi);
+#pragma unroll
+  for (int k = 0; k < 4; k++) umma_tf32_ts(dst, a_hi + 8 * k, bh + 2 * k, idesc, true);
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------------
+constexpr int ABM = 128;   // query rows per CTA (UMMA M)
+constexpr int ABN = 64;    // keys per tile
+constexpr int kFwdThreads = 192;   // warps 0-3 softmax, 4 MMA issue, 5 bulk-copy producer
 
 template <int DPAD> struct FwdCfg {
   static constexpr int kSub = DPAD / 32;                    // 32-channel sub-tiles
   static constexpr int kQBytes = 2 * kSub * ABM * 128;      // hi + lo
   static constexpr int kKBytes = 2 * kSub * ABN * 128;
-  static constexpr int kVBytes = 2 * 2 * DPAD * 128;        // two 32-key sub-tiles, hi + lo
+  static constexpr int kVBytes = 2 * 2 * DPAD * 128;        // two 32-key blocks, hi + lo
   static constexpr int kStageBytes = kKBytes + kVBytes;
-  static constexpr int kStages = DPAD == 32 ? 3 : 2;
+  static constexpr int kStages = DPAD == 32 ? 4 : 2;
   static constexpr int kSmem = kQBytes + kStages * kStageBytes + 1024 + 256;
   // TMEM columns
-  static constexpr int kSMain = 0, kSSmall = 128, kYMain = 256, kYSmall = 256 + 2 * DPAD;
+  static constexpr int kSMain = 0 /* S, then P hi */, kSSmall = 128 /* P lo */, kYMain = 256;
 };
 
 template <int DPAD>
-__global__ void __launch_bounds__(kAttnThreads, 1)
-attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __restrict__ Kc,
-                   const float* __restrict__ Vc, float* __restrict__ Y, float* __restrict__ lse) {
+__global__ void __launch_bounds__(kFwdThreads, 1)
+attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, float* __restrict__ Y,
+                   float* __restrict__ lse) {
   using Cfg = FwdCfg<DPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -93,14 +187,13 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.y, i0 = blockIdx.x * ABM;
   const int T = (N + ABN - 1) / ABN;
-  const long bo = (long)b * d * N;
 
   if (tid == 0) {
-    mbar_init(q_full, kLoaderThreads);
-    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&kv_full[s], kLoaderThreads); mbar_init(&kv_empty[s], 1); }
+    mbar_init(q_full, 1);
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
     for (int s = 0; s < 2; s++) {
-      mbar_init(&s_full[s], 1); mbar_init(&p_full[s], kSoftmaxThreads);
-      mbar_init(&y_full[s], 1); mbar_init(&y_free[s], kSoftmaxThreads);
+      mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 128);
+      mbar_init(&y_full[s], 1); mbar_init(&y_free[s], 128);
     }
     mbar_init_fence();
   }
@@ -110,41 +203,37 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp >= 5) {
-    // ======================= operand staging =======================
-    const int lt = tid - 5 * 32;
+  if (warp == 5) {
+    // ======================= bulk-copy producer =======================
+    if (lane == 0) {
+      mbar_expect_tx(q_full, Cfg::kQBytes);
 #pragma unroll
-    for (int s = 0; s < Cfg::kSub; s++) {     // Q[i][c] = Qc[c*N + i]
-      float* hi = reinterpret_cast<float*>(sQ + s * ABM * 128);
-      float* lo = reinterpret_cast<float*>(sQ + (Cfg::kSub + s) * ABM * 128);
-      stage_split<ABM>(hi, lo, Qc + bo + (long)(s * 32) * N + i0, 1, N, N - i0, d - s * 32, lt);
-    }
-    fence_proxy_async_smem();
-    mbar_arrive(q_full);
-    int stage = 0; uint32_t phase = 0;
-    for (int j = 0; j < T; j++) {
-      const int j0 = j * ABN;
-      mbar_wait(&kv_empty[stage], phase ^ 1);
-      uint8_t* st = sKV + stage * Cfg::kStageBytes;
-#pragma unroll
-      for (int s = 0; s < Cfg::kSub; s++) {   // K[j][c] = Kc[c*N + j]
-        float* hi = reinterpret_cast<float*>(st + s * ABN * 128);
-        float* lo = reinterpret_cast<float*>(st + (Cfg::kSub + s) * ABN * 128);
-        stage_split<ABN>(hi, lo, Kc + bo + (long)(s * 32) * N + j0, 1, N, N - j0, d - s * 32, lt);
+      for (int s = 0; s < Cfg::kSub; s++) {
+        const long o = (((long)b * Cfg::kSub + s) * NP + i0) * 32;
+        bulk_g2s(sQ + s * ABM * 128, Qi.pos_hi + o, ABM * 128, q_full);
+        bulk_g2s(sQ + (Cfg::kSub + s) * ABM * 128, Qi.pos_lo + o, ABM * 128, q_full);
       }
+      int stage = 0; uint32_t phase = 0;
+      for (int j = 0; j < T; j++) {
+        const int j0 = j * ABN;
+        mbar_wait(&kv_empty[stage], phase ^ 1);
+        uint8_t* st = sKV + stage * Cfg::kStageBytes;
+        mbar_expect_tx(&kv_full[stage], Cfg::kStageBytes);
 #pragma unroll
-      for (int s = 0; s < 2; s++) {           // V^T[c][j] = Vc[c*N + j], 32 keys per sub-tile
-        float* hi = reinterpret_cast<float*>(st + Cfg::kKBytes + s * DPAD * 128);
-        float* lo = reinterpret_cast<float*>(st + Cfg::kKBytes + (2 + s) * DPAD * 128);
-        stage_split<DPAD>(hi, lo, Vc + bo + j0 + s * 32, N, 1, d, N - j0 - s * 32, lt);
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + j0) * 32;
+          bulk_g2s(st + s * ABN * 128, Ki.pos_hi + o, ABN * 128, &kv_full[stage]);
+          bulk_g2s(st + (Cfg::kSub + s) * ABN * 128, Ki.pos_lo + o, ABN * 128, &kv_full[stage]);
+        }
+        const long ov = (((long)b * (NP / 32) + (j0 >> 5)) * DPAD) * 32;
+        bulk_g2s(st + Cfg::kKBytes, Vi.chan_hi + ov, 2 * DPAD * 128, &kv_full[stage]);
+        bulk_g2s(st + Cfg::kKBytes + 2 * DPAD * 128, Vi.chan_lo + ov, 2 * DPAD * 128, &kv_full[stage]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
-      fence_proxy_async_smem();
-      mbar_arrive(&kv_full[stage]);
-      if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 4) {
-    // ======================= MMA issue =======================
-    if (lane == 0) {
+    // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
+    {
       constexpr uint32_t idesc_s = umma_idesc_tf32(ABM, ABN);
       constexpr uint32_t idesc_y = umma_idesc_tf32(ABM, DPAD);
       const uint32_t q_base = smem_u32(sQ);
@@ -153,47 +242,39 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
         mbar_wait(&p_full[buf], (j >> 1) & 1);
         if (j >= 2) mbar_wait(&y_free[buf], ((j - 2) >> 1) & 1);
         tc_fence_after();
+        if (elect_one()) {
         const uint32_t v_base = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKBytes);
         const uint32_t p_hi = tmem + Cfg::kSMain + buf * ABN, p_lo = tmem + Cfg::kSSmall + buf * ABN;
-        const uint32_t y_main = tmem + Cfg::kYMain + buf * DPAD, y_small = tmem + Cfg::kYSmall + buf * DPAD;
+        const uint32_t y_acc = tmem + Cfg::kYMain + buf * DPAD;
 #pragma unroll
-        for (int s = 0; s < 2; s++) {
-          uint64_t v_hi = umma_desc_sw128(v_base + s * DPAD * 128);
-          uint64_t v_lo = umma_desc_sw128(v_base + (2 + s) * DPAD * 128);
+        for (int s = 0; s < 2; s++)
+          mma_corr_ts(y_acc, p_hi + s * 32, p_lo + s * 32, v_base + s * DPAD * 128,
+                      v_base + (2 + s) * DPAD * 128, idesc_y, s == 0);
 #pragma unroll
-          for (int k = 0; k < 4; k++) {
-            const bool acc = (s | k) != 0;
-            const uint32_t col = s * 32 + k * 8;
-            umma_tf32_ts(y_small, p_lo + col, v_hi + 2 * k, idesc_y, acc);
-            umma_tf32_ts(y_small, p_hi + col, v_lo + 2 * k, idesc_y, true);
-            umma_tf32_ts(y_main, p_hi + col, v_hi + 2 * k, idesc_y, acc);
-          }
-        }
+        for (int s = 0; s < 2; s++) mma_main_ts(y_acc, p_hi + s * 32, v_base + s * DPAD * 128, idesc_y);
         umma_commit(&y_full[buf]);
         umma_commit(&kv_empty[stage]);
+        }
+        __syncwarp();
       };
       mbar_wait(q_full, 0);
       for (int j = 0; j < T; j++) {
         const int buf = j & 1, stage = j % Cfg::kStages;
         mbar_wait(&kv_full[stage], (j / Cfg::kStages) & 1);
         tc_fence_after();
+        if (elect_one()) {
         const uint32_t k_base = smem_u32(sKV + stage * Cfg::kStageBytes);
-        const uint32_t s_main = tmem + Cfg::kSMain + buf * ABN, s_small = tmem + Cfg::kSSmall + buf * ABN;
+        const uint32_t s_acc = tmem + Cfg::kSMain + buf * ABN;
 #pragma unroll
-        for (int s = 0; s < Cfg::kSub; s++) {
-          uint64_t q_hi = umma_desc_sw128(q_base + s * ABM * 128);
-          uint64_t q_lo = umma_desc_sw128(q_base + (Cfg::kSub + s) * ABM * 128);
-          uint64_t k_hi = umma_desc_sw128(k_base + s * ABN * 128);
-          uint64_t k_lo = umma_desc_sw128(k_base + (Cfg::kSub + s) * ABN * 128);
+        for (int s = 0; s < Cfg::kSub; s++)
+          mma_corr_ss(s_acc, q_base + s * ABM * 128, q_base + (Cfg::kSub + s) * ABM * 128,
+                      k_base + s * ABN * 128, k_base + (Cfg::kSub + s) * ABN * 128, idesc_s, s == 0);
 #pragma unroll
-          for (int k = 0; k < 4; k++) {
-            const bool acc = (s | k) != 0;
-            umma_tf32_ss(s_small, q_lo + 2 * k, k_hi + 2 * k, idesc_s, acc);
-            umma_tf32_ss(s_small, q_hi + 2 * k, k_lo + 2 * k, idesc_s, true);
-            umma_tf32_ss(s_main, q_hi + 2 * k, k_hi + 2 * k, idesc_s, acc);
-          }
-        }
+        for (int s = 0; s < Cfg::kSub; s++)
+          mma_main_ss(s_acc, q_base + s * ABM * 128, k_base + s * ABN * 128, idesc_s);
         umma_commit(&s_full[buf]);
+        }
+        __syncwarp();
         if (j >= 1) issue_pv(j - 1);
       }
       issue_pv(T - 1);
@@ -213,12 +294,11 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
       tc_fence_after();
 #pragma unroll
       for (int c0 = 0; c0 < DPAD; c0 += 16) {
-        float a[16], s[16];
+        float a[16];
         tmem_ld16(tmem + lane_base + Cfg::kYMain + buf * DPAD + c0, a);
-        tmem_ld16(tmem + lane_base + Cfg::kYSmall + buf * DPAD + c0, s);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 16; q++) y[c0 + q] = fmaf(y[c0 + q], corr, a[q] + s[q]);
+        for (int q = 0; q < 16; q++) y[c0 + q] = fmaf(y[c0 + q], corr, a[q]);
       }
       tc_fence_before();
       mbar_arrive(&y_free[buf]);
@@ -231,13 +311,12 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
       float s[ABN];
 #pragma unroll
       for (int c0 = 0; c0 < ABN; c0 += 16) {
-        float a[16], w[16];
+        float a[16];
         tmem_ld16(tmem + lane_base + Cfg::kSMain + buf * ABN + c0, a);
-        tmem_ld16(tmem + lane_base + Cfg::kSSmall + buf * ABN + c0, w);
-        tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 16; q++) s[c0 + q] = a[q] + w[q];
+        for (int q = 0; q < 16; q++) s[c0 + q] = a[q];
       }
+      tmem_wait_ld();
       float mx = -INFINITY;
       if (j0 + ABN > N) {
 #pragma unroll
@@ -275,7 +354,7 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
       const float inv = 1.f / l;
       lse[(long)b * N + gi] = m + logf(l);
       float* dst = Y + ((long)b * N + gi) * d;
-      if ((d & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+      if ((d & 3) == 0) {
 #pragma unroll
         for (int c = 0; c < DPAD; c += 4)
           if (c < d) *reinterpret_cast<float4*>(dst + c) = make_float4(y[c] * inv, y[c + 1] * inv, y[c + 2] * inv, y[c + 3] * inv);
@@ -291,26 +370,570 @@ attn_fwd_tc_kernel(int N, int d, const float* __restrict__ Qc, const float* __re
   if (warp == 4) tmem_dealloc<512>(tmem);
 }
 
+// ------------------------------------------------------------------------------------------------
+// backward, part 1: dQ.   CTA = NQ tiles of 128 queries (one compute warpgroup each, ping-pong on
+// the tensor pipe), streaming 32-key tiles:  S = Q.K^T, dP = dY.V^T  (shared-memory operands)
+//   -> dS = exp(S - lse) * (dP - delta)  (thread = query row; written back to TMEM as tf32 hi/lo)
+//   -> dQ_tile = dS.K  (A from TMEM), promoted into fp32 registers every tile.
+// ------------------------------------------------------------------------------------------------
+constexpr int BT = 32;     // keys (dQ kernel) / queries (dK,dV kernel) per streamed tile
+
+template <int DPAD, int NQ> struct DqCfg {
+  static constexpr int kSub = DPAD / 32;
+  static constexpr int kOperBytes = kSub * 128 * 128;          // one 128-row pos tile, hi or lo
+  static constexpr int kResBytes = 4 * kOperBytes;             // Q hi, Q lo, dY hi, dY lo
+  static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile, hi or lo
+  static constexpr int kChanBytes = DPAD * 128;                // streamed chan block, hi or lo
+  static constexpr int kStageBytes = 4 * kPosBytes + 2 * kChanBytes;   // K pos hi/lo, V pos hi/lo, K chan hi/lo
+  static constexpr int kStages = DPAD == 32 ? 3 : 2;
+  static constexpr int kSmem = NQ * kResBytes + kStages * kStageBytes + 1024 + 256;
+  static constexpr int kTmemCols = 256 * NQ;
+  static constexpr int kThreads = (4 * NQ + 2) * 32;
+  // TMEM columns of one query tile
+  static constexpr int kS = 0 /* S, then dS hi */, kSs = 32 /* dS lo */, kP = 64 /* dP */, kAcc = 128;
+};
+
+template <int DPAD, int NQ>
+__global__ void __launch_bounds__(DqCfg<DPAD, NQ>::kThreads, 1)
+attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, SplitImage dYi,
+                  const float* __restrict__ lse_pad, const float* __restrict__ delta_pad,
+                  float* __restrict__ dQp) {
+  using Cfg = DqCfg<DPAD, NQ>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sRes = smem;
+  uint8_t* sStage = smem + NQ * Cfg::kResBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sStage + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* res_full = bars;                       // NQ
+  uint64_t* kv_full = res_full + NQ;               // kStages
+  uint64_t* kv_empty = kv_full + Cfg::kStages;     // kStages
+  uint64_t* sdp_full = kv_empty + Cfg::kStages;    // NQ   S, dP of the tile are in TMEM (and the previous dQ tile)
+  uint64_t* ds_full = sdp_full + NQ;               // NQ   dS written, previous dQ tile promoted
+  uint64_t* acc_done = ds_full + NQ;               // NQ   last dQ tile complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_done + NQ);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y;
+  const int nqt = NP / 128;                          // query tiles per sample
+  const int TK = (N + BT - 1) / BT;                  // key tiles
+  const int qt0 = blockIdx.x * NQ;
+
+  if (tid == 0) {
+    for (int h = 0; h < NQ; h++) {
+      mbar_init(&res_full[h], 1); mbar_init(&sdp_full[h], 1); mbar_init(&ds_full[h], 128); mbar_init(&acc_done[h], 1);
+    }
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    mbar_init_fence();
+  }
+  if (warp == 4 * NQ) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4 * NQ + 1) {
+    // ======================= bulk-copy producer =======================
+    if (lane == 0) {
+      for (int h = 0; h < NQ; h++) {
+        if (qt0 + h >= nqt) break;
+        uint8_t* r = sRes + h * Cfg::kResBytes;
+        mbar_expect_tx(&res_full[h], Cfg::kResBytes);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)(qt0 + h) * 128) * 32;
+          bulk_g2s(r + s * 16384, Qi.pos_hi + o, 16384, &res_full[h]);
+          bulk_g2s(r + Cfg::kOperBytes + s * 16384, Qi.pos_lo + o, 16384, &res_full[h]);
+          bulk_g2s(r + 2 * Cfg::kOperBytes + s * 16384, dYi.pos_hi + o, 16384, &res_full[h]);
+          bulk_g2s(r + 3 * Cfg::kOperBytes + s * 16384, dYi.pos_lo + o, 16384, &res_full[h]);
+        }
+      }
+      int stage = 0; uint32_t phase = 0;
+      for (int j = 0; j < TK; j++) {
+        mbar_wait(&kv_empty[stage], phase ^ 1);
+        uint8_t* st = sStage + stage * Cfg::kStageBytes;
+        mbar_expect_tx(&kv_full[stage], Cfg::kStageBytes);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * BT) * 32;
+          bulk_g2s(st + s * BT * 128, Ki.pos_hi + o, BT * 128, &kv_full[stage]);
+          bulk_g2s(st + Cfg::kPosBytes + s * BT * 128, Ki.pos_lo + o, BT * 128, &kv_full[stage]);
+          bulk_g2s(st + 2 * Cfg::kPosBytes + s * BT * 128, Vi.pos_hi + o, BT * 128, &kv_full[stage]);
+          bulk_g2s(st + 3 * Cfg::kPosBytes + s * BT * 128, Vi.pos_lo + o, BT * 128, &kv_full[stage]);
+        }
+        const long oc = (((long)b * (NP / 32) + j) * DPAD) * 32;
+        bulk_g2s(st + 4 * Cfg::kPosBytes, Ki.chan_hi + oc, Cfg::kChanBytes, &kv_full[stage]);
+        bulk_g2s(st + 4 * Cfg::kPosBytes + Cfg::kChanBytes, Ki.chan_lo + oc, Cfg::kChanBytes, &kv_full[stage]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 4 * NQ) {
+    // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
+    {
+      constexpr uint32_t idesc_s = umma_idesc_tf32(128, BT);
+      constexpr uint32_t idesc_q = umma_idesc_tf32(128, DPAD);
+      int nact = 0;
+      for (int h = 0; h < NQ; h++)
+        if (qt0 + h < nqt) { mbar_wait(&res_full[h], 0); nact = h + 1; }
+      tc_fence_after();
+      for (int j = 0; j <= TK; j++) {
+        if (j < TK) {
+          mbar_wait(&kv_full[j % Cfg::kStages], (j / Cfg::kStages) & 1);
+          tc_fence_after();
+        }
+        for (int h = 0; h < nact; h++) {
+          const uint32_t tb = tmem + h * 256;
+          const uint32_t r = smem_u32(sRes + h * Cfg::kResBytes);
+          if (j > 0) {                                   // dQ_h(j-1) = dS.K
+            mbar_wait(&ds_full[h], (j - 1) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t kc =
+                  smem_u32(sStage + ((j - 1) % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
+              mma_corr_ts(tb + Cfg::kAcc, tb + Cfg::kS, tb + Cfg::kSs, kc, kc + Cfg::kChanBytes, idesc_q, true);
+              mma_main_ts(tb + Cfg::kAcc, tb + Cfg::kS, kc, idesc_q);
+              if (h == nact - 1) umma_commit(&kv_empty[(j - 1) % Cfg::kStages]);
+            }
+            __syncwarp();
+          }
+          if (elect_one()) {
+          if (j < TK) {                                  // S_h(j) = Q.K^T ; dP_h(j) = dY.V^T
+            const uint32_t st = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_corr_ss(tb + Cfg::kS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
+                          st + Cfg::kPosBytes + s * BT * 128, idesc_s, s == 0);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_main_ss(tb + Cfg::kS, r + s * 16384, st + s * BT * 128, idesc_s);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_corr_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, r + 3 * Cfg::kOperBytes + s * 16384,
+                          st + 2 * Cfg::kPosBytes + s * BT * 128, st + 3 * Cfg::kPosBytes + s * BT * 128, idesc_s,
+                          s == 0);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_main_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128,
+                          idesc_s);
+            umma_commit(&sdp_full[h]);
+          } else {
+            umma_commit(&acc_done[h]);
+          }
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ======================= dS + promotion (thread = query row) =======================
+    const int h = warp >> 2;
+    if (qt0 + h < nqt) {
+      const int row = (warp & 3) * 32 + lane;
+      const int gi = (qt0 + h) * 128 + row;
+      const uint32_t tb = tmem + h * 256 + (((uint32_t)((warp & 3) * 32)) << 16);
+      const float lse_i = __ldg(lse_pad + (long)b * NP + gi);
+      const float delta_i = __ldg(delta_pad + (long)b * NP + gi);
+      float dq[DPAD];
+#pragma unroll
+      for (int c = 0; c < DPAD; c++) dq[c] = 0.f;
+      auto promote = [&]() {
+#pragma unroll
+        for (int c0 = 0; c0 < DPAD; c0 += 16) {
+          float a[16];
+          tmem_ld16(tb + Cfg::kAcc + c0, a);
+          tmem_wait_ld();
+#pragma unroll
+          for (int q = 0; q < 16; q++) dq[c0 + q] += a[q];
+        }
+      };
+      for (int j = 0; j < TK; j++) {
+        mbar_wait(&sdp_full[h], j & 1);
+        tc_fence_after();
+        if (j > 0) promote();
+        const int j0 = j * BT;
+#pragma unroll
+        for (int c0 = 0; c0 < BT; c0 += 16) {
+          float p[16], hi[16], lo[16];
+          {
+            float a[16], g[16];
+            tmem_ld16(tb + Cfg::kS + c0, a);
+            tmem_ld16(tb + Cfg::kP + c0, g);
+            tmem_wait_ld();
+#pragma unroll
+            for (int q = 0; q < 16; q++) {
+              p[q] = exp2f((a[q] - lse_i) * kLog2e);
+              if (j0 + c0 + q >= N) p[q] = 0.f;
+              split_tf32(p[q] * (g[q] - delta_i), hi[q], lo[q]);
+            }
+          }
+          tmem_st16(tb + Cfg::kS + c0, hi);
+          tmem_st16(tb + Cfg::kSs + c0, lo);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(&ds_full[h]);
+      }
+      mbar_wait(&acc_done[h], 0);
+      tc_fence_after();
+      promote();
+      if (gi < N) {
+        float* dst = dQp + ((long)b * N + gi) * d;
+        if ((d & 3) == 0) {
+#pragma unroll
+          for (int c = 0; c < DPAD; c += 4)
+            if (c < d) *reinterpret_cast<float4*>(dst + c) = make_float4(dq[c], dq[c + 1], dq[c + 2], dq[c + 3]);
+        } else {
+#pragma unroll
+          for (int c = 0; c < DPAD; c++)
+            if (c < d) dst[c] = dq[c];
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4 * NQ) tmem_dealloc<Cfg::kTmemCols>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward, part 2: dK, dV.   CTA = NKT tiles of 128 keys (lanes = keys), streaming 32-query tiles:
+//   S^T = K.Q^T, dP^T = V.dY^T  ->  P^T = exp(S^T - lse[q]), dS^T = P^T * (dP^T - delta[q])
+//   -> dV_tile = P^T.dY, dK_tile = dS^T.Q  (A from TMEM), promoted into registers every tile.
+// Each CTA accumulates one 32-channel group of dV / dK (blockIdx.z), so d = 64 runs two CTAs per
+// key tile (S^T and dP^T are recomputed; the accumulators stay at 64 registers per thread).
+// ------------------------------------------------------------------------------------------------
+template <int DPAD, int NKT> struct DkvCfg {
+  static constexpr int kSub = DPAD / 32;
+  static constexpr int kOperBytes = kSub * 128 * 128;          // one 128-row pos tile, hi or lo
+  static constexpr int kResBytes = 4 * kOperBytes;             // K hi, K lo, V hi, V lo
+  static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile, hi or lo
+  static constexpr int kChanBytes = 32 * 128;                  // one 32-channel group of a chan block
+  static constexpr int kStageBytes = 4 * kPosBytes + 4 * kChanBytes;  // Q pos, dY pos, dY chan, Q chan (hi/lo each)
+  static constexpr int kStages = 2;
+  static constexpr int kRowBytes = kStages * 2 * BT * 4;       // lse, delta of the tile's queries
+  static constexpr int kSmem = NKT * kResBytes + kStages * kStageBytes + kRowBytes + 1024 + 256;
+  static constexpr int kTmemCols = 256 * NKT;
+  static constexpr int kThreads = (4 * NKT + 2) * 32;
+  static constexpr int kS = 0 /* S^T, then P^T hi */, kSs = 32 /* P^T lo */, kP = 64 /* dP^T, then dS^T hi */,
+                       kPs = 96 /* dS^T lo */, kV = 128, kK = 160;
+};
+
+template <int DPAD, int NKT>
+__global__ void __launch_bounds__(DkvCfg<DPAD, NKT>::kThreads, 1)
+attn_dkv_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, SplitImage dYi,
+                   const float* __restrict__ lse_pad, const float* __restrict__ delta_pad,
+                   float* __restrict__ dKp, float* __restrict__ dVp) {
+  using Cfg = DkvCfg<DPAD, NKT>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sRes = smem;
+  uint8_t* sStage = smem + NKT * Cfg::kResBytes;
+  float* sRows = reinterpret_cast<float*>(sStage + Cfg::kStages * Cfg::kStageBytes);   // [stage][lse BT | delta BT]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sRows) + Cfg::kRowBytes);
+  uint64_t* res_full = bars;                       // NKT
+  uint64_t* q_full = res_full + NKT;               // kStages
+  uint64_t* q_empty = q_full + Cfg::kStages;       // kStages
+  uint64_t* sdp_full = q_empty + Cfg::kStages;     // NKT
+  uint64_t* ds_full = sdp_full + NKT;              // NKT
+  uint64_t* acc_done = ds_full + NKT;              // NKT
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_done + NKT);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, cg = blockIdx.z;          // cg: 32-channel group of dV / dK
+  const int nkt = NP / 128;                          // key tiles per sample
+  const int TQ = (N + BT - 1) / BT;                  // query tiles
+  const int kt0 = blockIdx.x * NKT;
+
+  if (tid == 0) {
+    for (int h = 0; h < NKT; h++) {
+      mbar_init(&res_full[h], 1); mbar_init(&sdp_full[h], 1); mbar_init(&ds_full[h], 128); mbar_init(&acc_done[h], 1);
+    }
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+    mbar_init_fence();
+  }
+  if (warp == 4 * NKT) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4 * NKT + 1) {
+    // ======================= bulk-copy producer =======================
+    if (lane == 0) {
+      for (int h = 0; h < NKT; h++) {
+        if (kt0 + h >= nkt) break;
+        uint8_t* r = sRes + h * Cfg::kResBytes;
+        mbar_expect_tx(&res_full[h], Cfg::kResBytes);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)(kt0 + h) * 128) * 32;
+          bulk_g2s(r + s * 16384, Ki.pos_hi + o, 16384, &res_full[h]);
+          bulk_g2s(r + Cfg::kOperBytes + s * 16384, Ki.pos_lo + o, 16384, &res_full[h]);
+          bulk_g2s(r + 2 * Cfg::kOperBytes + s * 16384, Vi.pos_hi + o, 16384, &res_full[h]);
+          bulk_g2s(r + 3 * Cfg::kOperBytes + s * 16384, Vi.pos_lo + o, 16384, &res_full[h]);
+        }
+      }
+      int stage = 0; uint32_t phase = 0;
+      for (int j = 0; j < TQ; j++) {
+        mbar_wait(&q_empty[stage], phase ^ 1);
+        uint8_t* st = sStage + stage * Cfg::kStageBytes;
+        mbar_expect_tx(&q_full[stage], Cfg::kStageBytes + 2 * BT * 4);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * BT) * 32;
+          bulk_g2s(st + s * BT * 128, Qi.pos_hi + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + Cfg::kPosBytes + s * BT * 128, Qi.pos_lo + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + 2 * Cfg::kPosBytes + s * BT * 128, dYi.pos_hi + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + 3 * Cfg::kPosBytes + s * BT * 128, dYi.pos_lo + o, BT * 128, &q_full[stage]);
+        }
+        const long oc = (((long)b * (NP / 32) + j) * DPAD + cg * 32) * 32;
+        uint8_t* sc = st + 4 * Cfg::kPosBytes;
+        bulk_g2s(sc, dYi.chan_hi + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + Cfg::kChanBytes, dYi.chan_lo + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + 2 * Cfg::kChanBytes, Qi.chan_hi + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + 3 * Cfg::kChanBytes, Qi.chan_lo + oc, Cfg::kChanBytes, &q_full[stage]);
+        float* rw = sRows + stage * 2 * BT;
+        bulk_g2s(rw, lse_pad + (long)b * NP + (long)j * BT, BT * 4, &q_full[stage]);
+        bulk_g2s(rw + BT, delta_pad + (long)b * NP + (long)j * BT, BT * 4, &q_full[stage]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 4 * NKT) {
+    // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
+    {
+      constexpr uint32_t idesc = umma_idesc_tf32(128, BT);     // every product here is 128 x 32
+      int nact = 0;
+      for (int h = 0; h < NKT; h++)
+        if (kt0 + h < nkt) { mbar_wait(&res_full[h], 0); nact = h + 1; }
+      tc_fence_after();
+      for (int j = 0; j <= TQ; j++) {
+        if (j < TQ) {
+          mbar_wait(&q_full[j % Cfg::kStages], (j / Cfg::kStages) & 1);
+          tc_fence_after();
+        }
+        for (int h = 0; h < nact; h++) {
+          const uint32_t tb = tmem + h * 256;
+          const uint32_t r = smem_u32(sRes + h * Cfg::kResBytes);
+          if (j > 0) {                                   // dV_h(j-1) = P^T.dY ; dK_h(j-1) = dS^T.Q
+            mbar_wait(&ds_full[h], (j - 1) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t sc =
+                  smem_u32(sStage + ((j - 1) % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
+              mma_corr_ts(tb + Cfg::kV, tb + Cfg::kS, tb + Cfg::kSs, sc, sc + Cfg::kChanBytes, idesc, true);
+              mma_main_ts(tb + Cfg::kV, tb + Cfg::kS, sc, idesc);
+              mma_corr_ts(tb + Cfg::kK, tb + Cfg::kP, tb + Cfg::kPs, sc + 2 * Cfg::kChanBytes,
+                          sc + 3 * Cfg::kChanBytes, idesc, true);
+              mma_main_ts(tb + Cfg::kK, tb + Cfg::kP, sc + 2 * Cfg::kChanBytes, idesc);
+              if (h == nact - 1) umma_commit(&q_empty[(j - 1) % Cfg::kStages]);
+            }
+            __syncwarp();
+          }
+          if (elect_one()) {
+          if (j < TQ) {                                  // S^T_h(j) = K.Q^T ; dP^T_h(j) = V.dY^T
+            const uint32_t st = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_corr_ss(tb + Cfg::kS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
+                          st + Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_main_ss(tb + Cfg::kS, r + s * 16384, st + s * BT * 128, idesc);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_corr_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, r + 3 * Cfg::kOperBytes + s * 16384,
+                          st + 2 * Cfg::kPosBytes + s * BT * 128, st + 3 * Cfg::kPosBytes + s * BT * 128, idesc,
+                          s == 0);
+#pragma unroll
+            for (int s = 0; s < Cfg::kSub; s++)
+              mma_main_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128,
+                          idesc);
+            umma_commit(&sdp_full[h]);
+          } else {
+            umma_commit(&acc_done[h]);
+          }
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ======================= P^T, dS^T + promotion (thread = key row) =======================
+    const int h = warp >> 2;
+    if (kt0 + h < nkt) {
+      const int row = (warp & 3) * 32 + lane;
+      const int gj = (kt0 + h) * 128 + row;
+      const uint32_t tb = tmem + h * 256 + (((uint32_t)((warp & 3) * 32)) << 16);
+      float dv[32], dk[32];
+#pragma unroll
+      for (int c = 0; c < 32; c++) { dv[c] = 0.f; dk[c] = 0.f; }
+      auto promote = [&]() {
+#pragma unroll
+        for (int c0 = 0; c0 < 32; c0 += 16) {
+          float a[16], s[16];
+          tmem_ld16(tb + Cfg::kV + c0, a);
+          tmem_ld16(tb + Cfg::kK + c0, s);
+          tmem_wait_ld();
+#pragma unroll
+          for (int q = 0; q < 16; q++) { dv[c0 + q] += a[q]; dk[c0 + q] += s[q]; }
+        }
+      };
+      for (int j = 0; j < TQ; j++) {
+        mbar_wait(&sdp_full[h], j & 1);
+        tc_fence_after();
+        if (j > 0) promote();
+        mbar_wait(&q_full[j % Cfg::kStages], (j / Cfg::kStages) & 1);   // lse / delta of the tile have landed
+        const float* rw = sRows + (j % Cfg::kStages) * 2 * BT;
+#pragma unroll
+        for (int c0 = 0; c0 < BT; c0 += 16) {
+          float p[16], hi[16], lo[16], g[16];
+          {
+            float a[16];
+            tmem_ld16(tb + Cfg::kS + c0, a);
+            tmem_ld16(tb + Cfg::kP + c0, g);
+            tmem_wait_ld();
+#pragma unroll
+            for (int q = 0; q < 16; q++) {
+              p[q] = exp2f((a[q] - rw[c0 + q]) * kLog2e);
+              split_tf32(p[q], hi[q], lo[q]);
+            }
+          }
+          tmem_st16(tb + Cfg::kS + c0, hi);
+          tmem_st16(tb + Cfg::kSs + c0, lo);
+#pragma unroll
+          for (int q = 0; q < 16; q++) split_tf32(p[q] * (g[q] - rw[BT + c0 + q]), hi[q], lo[q]);
+          tmem_st16(tb + Cfg::kP + c0, hi);
+          tmem_st16(tb + Cfg::kPs + c0, lo);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(&ds_full[h]);
+      }
+      mbar_wait(&acc_done[h], 0);
+      tc_fence_after();
+      promote();
+      if (gj < N) {
+        const int cw = min(32, d - cg * 32);             // channels of this group that exist
+        float* dv_dst = dVp + ((long)b * N + gj) * d + cg * 32;
+        float* dk_dst = dKp + ((long)b * N + gj) * d + cg * 32;
+        if ((d & 3) == 0) {
+#pragma unroll
+          for (int c = 0; c < 32; c += 4)
+            if (c < cw) {
+              *reinterpret_cast<float4*>(dv_dst + c) = make_float4(dv[c], dv[c + 1], dv[c + 2], dv[c + 3]);
+              *reinterpret_cast<float4*>(dk_dst + c) = make_float4(dk[c], dk[c + 1], dk[c + 2], dk[c + 3]);
+            }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; c++)
+            if (c < cw) { dv_dst[c] = dv[c]; dk_dst[c] = dk[c]; }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4 * NKT) tmem_dealloc<Cfg::kTmemCols>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+template <typename K>
+int set_smem(K kern, int bytes) {
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  return e == cudaSuccess ? FRN_OK : (int)e;
+}
+
 template <int DPAD>
-int launch_fwd_tc(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc, const float* Vc,
-                  float* Y, float* lse) {
+int launch_pack(cudaStream_t st, int B, int d, int N, const float* X, const float* sub, long bs, long cs, long ns,
+                const SplitImage& img) {
+  const int NP = attn_tc_np(N);
+  dim3 grid(NP / 32, B);
+  pack_split_kernel<DPAD><<<grid, 256, 0, st>>>(X, sub, bs, cs, ns, d, N, NP, img.pos_hi, img.pos_lo, img.chan_hi,
+                                                img.chan_lo);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+template <int DPAD>
+int launch_fwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
+                  const SplitImage& V, float* Y, float* lse) {
   using Cfg = FwdCfg<DPAD>;
   auto kern = attn_fwd_tc_kernel<DPAD>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem);
-  if (e != cudaSuccess) return (int)e;
+  FRN_TRY(set_smem(kern, Cfg::kSmem));
   dim3 grid(cdiv(N, ABM), B);
   ScopedTimer tm(st, FRN_TIME_ATTN_FWD);
-  kern<<<grid, kAttnThreads, Cfg::kSmem, st>>>(N, d, Qc, Kc, Vc, Y, lse);
+  kern<<<grid, kFwdThreads, Cfg::kSmem, st>>>(N, attn_tc_np(N), d, Q, K, V, Y, lse);
   FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+template <int DPAD, int NT>
+int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
+                  const SplitImage& V, const SplitImage& dY, const float* lse_pad, const float* delta_pad,
+                  float* dQp, float* dKp, float* dVp) {
+  const int NP = attn_tc_np(N);
+  ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
+  {
+    using Cfg = DkvCfg<DPAD, NT>;
+    auto kern = attn_dkv_tc_kernel<DPAD, NT>;
+    FRN_TRY(set_smem(kern, Cfg::kSmem));
+    dim3 grid(cdiv(NP / 128, NT), B, cdiv(d, 32));
+    kern<<<grid, Cfg::kThreads, Cfg::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+    FRN_LAUNCH_CHECK();
+  }
+  {
+    using Cfg = DqCfg<DPAD, NT>;
+    auto kern = attn_dq_tc_kernel<DPAD, NT>;
+    FRN_TRY(set_smem(kern, Cfg::kSmem));
+    dim3 grid(cdiv(NP / 128, NT), B);
+    kern<<<grid, Cfg::kThreads, Cfg::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+    FRN_LAUNCH_CHECK();
+  }
   return FRN_OK;
 }
 
 }  // namespace
 
-int attn_forward_tc(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc, const float* Vc,
-                    float* Y, float* lse) {
-  if (d <= 32) return launch_fwd_tc<32>(st, B, N, d, Qc, Kc, Vc, Y, lse);
-  if (d <= 64) return launch_fwd_tc<64>(st, B, N, d, Qc, Kc, Vc, Y, lse);
+int attn_tc_np(int N) { return (N + 127) / 128 * 128; }
+
+size_t attn_tc_plane_floats(int B, int N, int d) {
+  const int dpad = d <= 32 ? 32 : 64;
+  return (size_t)B * dpad * attn_tc_np(N);
+}
+
+int attn_tc_pack(cudaStream_t st, int B, int d, int N, const float* X, const float* sub, long bs, long cs,
+                 long ns, const SplitImage& img) {
+  if (d > 64) return FRN_ERR_UNSUPPORTED;
+  if ((img.pos_hi == nullptr) != (img.pos_lo == nullptr) || (img.chan_hi == nullptr) != (img.chan_lo == nullptr))
+    return FRN_ERR_NULL_POINTER;
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  return d <= 32 ? launch_pack<32>(st, B, d, N, X, sub, bs, cs, ns, img)
+                 : launch_pack<64>(st, B, d, N, X, sub, bs, cs, ns, img);
+}
+
+int attn_forward_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
+                    const SplitImage& V, float* Y, float* lse) {
+  if (d <= 32) return launch_fwd_tc<32>(st, B, N, d, Q, K, V, Y, lse);
+  if (d <= 64) return launch_fwd_tc<64>(st, B, N, d, Q, K, V, Y, lse);
+  return FRN_ERR_UNSUPPORTED;
+}
+
+int attn_bwd_prep_tc(cudaStream_t st, int B, int N, int d, const float* dYp, const float* Y, const float* lse,
+                     float* lse_pad, float* delta_pad) {
+  const int NP = attn_tc_np(N);
+  dim3 grid(cdiv(NP, 128), B);
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  attn_bwd_prep_kernel<<<grid, 128, 0, st>>>(N, NP, d, dYp, Y, lse, lse_pad, delta_pad);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int attn_backward_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
+                     const SplitImage& V, const SplitImage& dY, const float* lse_pad, const float* delta_pad,
+                     float* dQp, float* dKp, float* dVp) {
+  if (d <= 32) return launch_bwd_tc<32, 2>(st, B, N, d, Q, K, V, dY, lse_pad, delta_pad, dQp, dKp, dVp);
+  if (d <= 64) return launch_bwd_tc<64, 1>(st, B, N, d, Q, K, V, dY, lse_pad, delta_pad, dQp, dKp, dVp);
   return FRN_ERR_UNSUPPORTED;
 }
 

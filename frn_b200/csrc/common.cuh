@@ -124,9 +124,28 @@ int gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
 // Y: (B, N, d) row-major; lse: (B, N).
 int attn_forward(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc,
                  const float* Vp, float* Y, float* lse);
-// tcgen05 engine (attention_tc.cu): all operands channel-major (B, d, N).
-int attn_forward_tc(cudaStream_t st, int B, int N, int d, const float* Qc, const float* Kc,
-                    const float* Vc, float* Y, float* lse);
+// tcgen05 engine (attention_tc.cu).  Operands are "packed split images": tf32 hi / lo planes in the
+// SWIZZLE_128B tile layout, zero padded to attn_tc_np(N) positions and 32 / 64 channels; each plane
+// holds attn_tc_plane_floats(B, N, d) floats.  A null pair of planes is not written by the packer.
+struct SplitImage { float *pos_hi, *pos_lo, *chan_hi, *chan_lo; };
+int attn_tc_np(int N);
+size_t attn_tc_plane_floats(int B, int N, int d);
+// X element (c, n) of sample b at X[b*bs + c*cs + n*ns]; sub (optional, (B, d)) is subtracted first.
+// The tcgen05 engine packs the KEY operand centred over positions (sub = its per-channel mean):
+// softmax_j(q_i.k_j) and dQ_i = sum_j dS_ij k_j are invariant under k_j -> k_j - kbar (rows of dS sum
+// to zero), and without the common component the cancellation in dQ no longer amplifies rounding.
+int attn_tc_pack(cudaStream_t st, int B, int d, int N, const float* X, const float* sub, long bs, long cs,
+                 long ns, const SplitImage& img);
+// needs Q.pos, K.pos, V.chan
+int attn_forward_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
+                    const SplitImage& V, float* Y, float* lse);
+// lse_pad, delta_pad: (B, attn_tc_np(N)); delta = rowsum(dY * Y)
+int attn_bwd_prep_tc(cudaStream_t st, int B, int N, int d, const float* dYp, const float* Y, const float* lse,
+                     float* lse_pad, float* delta_pad);
+// needs Q.pos/chan, K.pos/chan, V.pos, dY.pos/chan; writes dQp, dKp, dVp (B, N, d), no atomics
+int attn_backward_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
+                     const SplitImage& V, const SplitImage& dY, const float* lse_pad, const float* delta_pad,
+                     float* dQp, float* dKp, float* dVp);
 // 0 = FFMA kernels (attention.cu), 1 = tcgen05 kernels; default from FRN_ATTN_ENGINE ("ffma" / "tc").
 int attn_engine();
 void set_attn_engine(int e);

@@ -24,8 +24,10 @@ struct Ctx {
   size_t splitk_need;   // dry: max split-K partial bytes over all reduce GEMMs
   void* splitk;
   size_t splitk_cap;
+  int attn_eng;         // 0 = FFMA streaming kernels, 1 = tcgen05 kernels
   Ctx(cudaStream_t s, void* p, size_t bytes, bool dry_)
-      : st(s), dry(dry_), ws(p, bytes, dry_), splitk_need(0), splitk(nullptr), splitk_cap(0) {}
+      : st(s), dry(dry_), ws(p, bytes, dry_), splitk_need(0), splitk(nullptr), splitk_cap(0),
+        attn_eng(attn_engine()) {}
 };
 
 #define RUN(c, expr)              \
@@ -118,14 +120,34 @@ int chunk_for_scores(int B, int N, int mats) {
   return (int)ch;
 }
 
+// workspace planes of one packed split image (attention_tc.cu)
+SplitImage take_image(Ctx& c, int B, int N, int d, bool pos, bool chan) {
+  const size_t n = attn_tc_plane_floats(B, N, d);
+  SplitImage im{nullptr, nullptr, nullptr, nullptr};
+  if (pos) { im.pos_hi = c.ws.take<float>(n); im.pos_lo = c.ws.take<float>(n); }
+  if (chan) { im.chan_hi = c.ws.take<float>(n); im.chan_lo = c.ws.take<float>(n); }
+  return im;
+}
+
 // softmax(Q K) V for all samples.  d <= 64: fused streaming kernel; else GEMM + row softmax.
 int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
   if (d <= 64) {
-    float* Vp = c.ws.take<float>((size_t)B * N * d);   // (taken on both engines: sizes stay engine-independent)
-    if (attn_engine() == 1) {
-      RUN(c, attn_forward_tc(c.st, B, N, d, s.Qc, s.Kc, s.Vc, s.Y, s.lse));
-      return FRN_OK;
+    if (c.attn_eng == 1 || c.dry) {     // dry: count both engines' scratch, the arena keeps the peak
+      const size_t m0 = c.ws.off;
+      const long dn = (long)d * N;
+      SplitImage Q = take_image(c, B, N, d, true, false), K = take_image(c, B, N, d, true, false);
+      SplitImage V = take_image(c, B, N, d, false, true);
+      float* kbar = c.ws.take<float>((size_t)B * d);
+      float* ksd = c.ws.take<float>((size_t)B * d);
+      RUN(c, row_mean_std(c.st, (long)B * d, N, s.Kc, kEps, kbar, ksd));
+      RUN(c, attn_tc_pack(c.st, B, d, N, s.Qc, nullptr, dn, N, 1, Q));
+      RUN(c, attn_tc_pack(c.st, B, d, N, s.Kc, kbar, dn, N, 1, K));
+      RUN(c, attn_tc_pack(c.st, B, d, N, s.Vc, nullptr, dn, N, 1, V));
+      RUN(c, attn_forward_tc(c.st, B, N, d, Q, K, V, s.Y, s.lse));
+      if (!c.dry) return FRN_OK;
+      c.ws.release_to(m0);
     }
+    float* Vp = c.ws.take<float>((size_t)B * N * d);
     RUN(c, transpose_batched(c.st, B, d, N, s.Vc, Vp));
     RUN(c, attn_forward(c.st, B, N, d, s.Qc, s.Kc, Vp, s.Y, s.lse));
     return FRN_OK;
@@ -193,6 +215,26 @@ int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, c
 // Gradients of softmax(Q K) V wrt Q, K, V given dY; outputs position-major (B, N, d).
 int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* dYp, float* dQp,
                   float* dKp, float* dVp) {
+  if (d <= 64 && (c.attn_eng == 1 || c.dry)) {
+    const size_t m0 = c.ws.off;
+    const long dn = (long)d * N;
+    const size_t np = (size_t)B * attn_tc_np(N);
+    float* lse_pad = c.ws.take<float>(np);
+    float* delta_pad = c.ws.take<float>(np);
+    SplitImage Q = take_image(c, B, N, d, true, true), K = take_image(c, B, N, d, true, true);
+    SplitImage V = take_image(c, B, N, d, true, false), dY = take_image(c, B, N, d, true, true);
+    RUN(c, attn_bwd_prep_tc(c.st, B, N, d, dYp, s.Y, s.lse, lse_pad, delta_pad));
+    float* kbar = c.ws.take<float>((size_t)B * d);
+    float* ksd = c.ws.take<float>((size_t)B * d);
+    RUN(c, row_mean_std(c.st, (long)B * d, N, s.Kc, kEps, kbar, ksd));   // same centring as the forward pass
+    RUN(c, attn_tc_pack(c.st, B, d, N, s.Qc, nullptr, dn, N, 1, Q));
+    RUN(c, attn_tc_pack(c.st, B, d, N, s.Kc, kbar, dn, N, 1, K));
+    RUN(c, attn_tc_pack(c.st, B, d, N, s.Vc, nullptr, dn, N, 1, V));
+    RUN(c, attn_tc_pack(c.st, B, d, N, dYp, nullptr, dn, 1, d, dY));     // dY is position-major (B, N, d)
+    RUN(c, attn_backward_tc(c.st, B, N, d, Q, K, V, dY, lse_pad, delta_pad, dQp, dKp, dVp));
+    if (!c.dry) return FRN_OK;
+    c.ws.release_to(m0);
+  }
   float* delta = c.ws.take<float>((size_t)B * N);
   RUN(c, row_dot(c.st, (long)B * N, d, dYp, s.Y, delta));           // rowsum(dY * Y)
   if (d <= 64) {
@@ -367,12 +409,13 @@ bool shape_ok(int B, int C, int N) { return B > 0 && C > 0 && N >= 2 && C % 8 ==
 
 // Finish a Ctx for a real call: carve the split-K buffer whose size a dry pass determined.
 template <typename F>
-int with_ctx(void* stream, void* ws, size_t ws_bytes, F body) {
+int with_ctx(void* stream, void* ws, size_t ws_bytes, F body, int attn_eng = -1) {
   Ctx dry(nullptr, nullptr, 0, true);
   FRN_TRY(body(dry));
   size_t need = dry.ws.peak + align_up(dry.splitk_need);
   if (need > 0 && (!ws || ws_bytes < need)) return FRN_ERR_WORKSPACE;
   Ctx c((cudaStream_t)stream, ws, ws_bytes, false);
+  if (attn_eng >= 0) c.attn_eng = attn_eng;
   if (dry.splitk_need) {
     c.splitk = c.ws.take<char>(dry.splitk_need);
     c.splitk_cap = dry.splitk_need;
@@ -416,7 +459,7 @@ const char* frn_error_string(int code) {
 }
 
 const char* frn_kernel_inventory(void) {
-  return "sgemm_kernel,tc_gemm_kernel,attn_fwd_tc_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
+  return "sgemm_kernel,tc_gemm_kernel,attn_fwd_tc_kernel,attn_dq_tc_kernel,attn_dkv_tc_kernel,pack_split_kernel,attn_bwd_prep_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
          "gate_stats_kernel,adain_apply_kernel,adain_bwd_reduce_kernel,adain_bwd_content_kernel,"
          "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
@@ -445,6 +488,36 @@ void frn_set_gemm_engine(int engine) { set_gemm_engine(engine); }
 void frn_set_attn_engine(int engine) { set_attn_engine(engine); }
 int frn_get_attn_engine(void) { return attn_engine(); }
 int frn_get_gemm_engine(void) { return gemm_engine(); }
+
+// ---- attention core (Attention.py:29-32) -------------------------------------------
+static CabSaved attn_only(const float* Qc, const float* Kc, const float* Vc, float* Y, float* lse) {
+  CabSaved s{};
+  s.Qc = const_cast<float*>(Qc); s.Kc = const_cast<float*>(Kc); s.Vc = const_cast<float*>(Vc);
+  s.Y = Y; s.lse = lse;
+  return s;
+}
+size_t frn_attn_workspace_bytes(int B, int N, int d) {
+  if (B <= 0 || N < 2 || d <= 0) return 0;
+  CabSaved s{};
+  size_t fwd = dry_bytes([&](Ctx& c) { return attention_fwd(c, B, N, d, s); });
+  size_t bwd = dry_bytes([&](Ctx& c) { return attention_bwd(c, B, N, d, s, nullptr, nullptr, nullptr, nullptr); });
+  return std::max(fwd, bwd);
+}
+int frn_attn_forward(void* stream, int engine, int B, int N, int d, const float* Qc, const float* Kc,
+                     const float* Vc, float* Y, float* lse, void* ws, size_t ws_bytes) {
+  if (B <= 0 || N < 2 || d <= 0) return FRN_ERR_BAD_SHAPE;
+  if (!Qc || !Kc || !Vc || !Y || !lse) return FRN_ERR_NULL_POINTER;
+  CabSaved s = attn_only(Qc, Kc, Vc, Y, lse);
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) { return attention_fwd(c, B, N, d, s); }, engine);
+}
+int frn_attn_backward(void* stream, int engine, int B, int N, int d, const float* Qc, const float* Kc,
+                      const float* Vc, const float* Y, const float* lse, const float* dY, float* dQ,
+                      float* dK, float* dV, void* ws, size_t ws_bytes) {
+  if (B <= 0 || N < 2 || d <= 0) return FRN_ERR_BAD_SHAPE;
+  if (!Qc || !Kc || !Vc || !Y || !lse || !dY || !dQ || !dK || !dV) return FRN_ERR_NULL_POINTER;
+  CabSaved s = attn_only(Qc, Kc, Vc, const_cast<float*>(Y), const_cast<float*>(lse));
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) { return attention_bwd(c, B, N, d, s, dY, dQ, dK, dV); }, engine);
+}
 
 // ---- AdaIN -------------------------------------------------------------------
 int frn_mean_std(void* stream, int B, int C, int N, const float* feat, float eps, float* mean,

@@ -167,6 +167,22 @@ int frn_get_gemm_engine(void);
 void frn_set_attn_engine(int engine);
 int frn_get_attn_engine(void);
 
+/* ---- attention core (stage-level entry point for unit parity) -------------------------------
+ * Y = softmax(Q^T K, dim = keys) V^T of retinanet/Attention.py:29-32 (no 1/sqrt(d) scale), never
+ * materialising the N x N matrix for d <= 64.  Qc = phi(x1), Kc = theta(x1), Vc = g(x0), each
+ * (B, d, N) channel-major as the 1x1 convs write them; Y, dY, dQ, dK, dV are (B, N, d) row-major
+ * (so the reference's y.view(B, d, H, W) is a reinterpretation of Y); lse is (B, N), the row
+ * log-sum-exp of the logits as the engine formed them (the tcgen05 engine subtracts the per-channel
+ * mean over positions from Kc first, which leaves the softmax and all gradients unchanged); pass the
+ * forward's lse to the backward of the SAME engine.
+ * engine: 0 = FFMA kernels, 1 = tcgen05 kernels, -1 = library default. */
+size_t frn_attn_workspace_bytes(int B, int N, int d);
+int frn_attn_forward(void* stream, int engine, int B, int N, int d, const float* Qc, const float* Kc,
+                     const float* Vc, float* Y, float* lse, void* ws, size_t ws_bytes);
+int frn_attn_backward(void* stream, int engine, int B, int N, int d, const float* Qc, const float* Kc,
+                      const float* Vc, const float* Y, const float* lse, const float* dY, float* dQ,
+                      float* dK, float* dV, void* ws, size_t ws_bytes);
+
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
  * launching stream.  Classes: 0 = streaming attention forward, 1 = streaming
