@@ -146,6 +146,52 @@ __device__ __forceinline__ void mma_main_ts(uint32_t dst, uint32_t a_hi, uint32_
   for (int k = 0; k < 4; k++) umma_tf32_ts(dst, a_hi + 8 * k, bh + 2 * k, idesc, true);
 }
 
+// Two independent products issued interleaved (different accumulators), so that consecutive
+// tcgen05.mma never form a read-after-write chain on one accumulator.
+__device__ __forceinline__ void mma2_corr_ss(uint32_t d0, uint32_t a0_hi, uint32_t a0_lo, uint32_t b0_hi, uint32_t b0_lo,
+                                             uint32_t d1, uint32_t a1_hi, uint32_t a1_lo, uint32_t b1_hi, uint32_t b1_lo,
+                                             uint32_t idesc, bool first) {
+  const uint64_t ah0 = umma_desc_sw128(a0_hi), al0 = umma_desc_sw128(a0_lo), bh0 = umma_desc_sw128(b0_hi),
+                 bl0 = umma_desc_sw128(b0_lo);
+  const uint64_t ah1 = umma_desc_sw128(a1_hi), al1 = umma_desc_sw128(a1_lo), bh1 = umma_desc_sw128(b1_hi),
+                 bl1 = umma_desc_sw128(b1_lo);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    umma_tf32_ss(d0, al0 + 2 * k, bh0 + 2 * k, idesc, !(first && k == 0));
+    umma_tf32_ss(d1, al1 + 2 * k, bh1 + 2 * k, idesc, !(first && k == 0));
+    umma_tf32_ss(d0, ah0 + 2 * k, bl0 + 2 * k, idesc, true);
+    umma_tf32_ss(d1, ah1 + 2 * k, bl1 + 2 * k, idesc, true);
+  }
+}
+__device__ __forceinline__ void mma2_main_ss(uint32_t d0, uint32_t a0_hi, uint32_t b0_hi, uint32_t d1, uint32_t a1_hi,
+                                             uint32_t b1_hi, uint32_t idesc) {
+  const uint64_t ah0 = umma_desc_sw128(a0_hi), bh0 = umma_desc_sw128(b0_hi);
+  const uint64_t ah1 = umma_desc_sw128(a1_hi), bh1 = umma_desc_sw128(b1_hi);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    umma_tf32_ss(d0, ah0 + 2 * k, bh0 + 2 * k, idesc, true);
+    umma_tf32_ss(d1, ah1 + 2 * k, bh1 + 2 * k, idesc, true);
+  }
+}
+__device__ __forceinline__ void mma2_ts(uint32_t d0, uint32_t a0_hi, uint32_t a0_lo, uint32_t b0_hi, uint32_t b0_lo,
+                                        uint32_t d1, uint32_t a1_hi, uint32_t a1_lo, uint32_t b1_hi, uint32_t b1_lo,
+                                        uint32_t idesc) {
+  const uint64_t bh0 = umma_desc_sw128(b0_hi), bl0 = umma_desc_sw128(b0_lo);
+  const uint64_t bh1 = umma_desc_sw128(b1_hi), bl1 = umma_desc_sw128(b1_lo);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    umma_tf32_ts(d0, a0_lo + 8 * k, bh0 + 2 * k, idesc, k != 0);
+    umma_tf32_ts(d1, a1_lo + 8 * k, bh1 + 2 * k, idesc, k != 0);
+    umma_tf32_ts(d0, a0_hi + 8 * k, bl0 + 2 * k, idesc, true);
+    umma_tf32_ts(d1, a1_hi + 8 * k, bl1 + 2 * k, idesc, true);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    umma_tf32_ts(d0, a0_hi + 8 * k, bh0 + 2 * k, idesc, true);
+    umma_tf32_ts(d1, a1_hi + 8 * k, bh1 + 2 * k, idesc, true);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------
@@ -719,11 +765,9 @@ attn_dkv_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
             if (elect_one()) {
               const uint32_t sc =
                   smem_u32(sStage + ((j - 1) % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
-              mma_corr_ts(tb + Cfg::kV, tb + Cfg::kS, tb + Cfg::kSs, sc, sc + Cfg::kChanBytes, idesc, true);
-              mma_main_ts(tb + Cfg::kV, tb + Cfg::kS, sc, idesc);
-              mma_corr_ts(tb + Cfg::kK, tb + Cfg::kP, tb + Cfg::kPs, sc + 2 * Cfg::kChanBytes,
-                          sc + 3 * Cfg::kChanBytes, idesc, true);
-              mma_main_ts(tb + Cfg::kK, tb + Cfg::kP, sc + 2 * Cfg::kChanBytes, idesc);
+              mma2_ts(tb + Cfg::kV, tb + Cfg::kS, tb + Cfg::kSs, sc, sc + Cfg::kChanBytes,
+                      tb + Cfg::kK, tb + Cfg::kP, tb + Cfg::kPs, sc + 2 * Cfg::kChanBytes, sc + 3 * Cfg::kChanBytes,
+                      idesc);
               if (h == nact - 1) umma_commit(&q_empty[(j - 1) % Cfg::kStages]);
             }
             __syncwarp();
@@ -733,20 +777,16 @@ attn_dkv_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
             const uint32_t st = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes);
 #pragma unroll
             for (int s = 0; s < Cfg::kSub; s++)
-              mma_corr_ss(tb + Cfg::kS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
-                          st + Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+              mma2_corr_ss(tb + Cfg::kS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
+                           st + Cfg::kPosBytes + s * BT * 128,
+                           tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, r + 3 * Cfg::kOperBytes + s * 16384,
+                           st + 2 * Cfg::kPosBytes + s * BT * 128, st + 3 * Cfg::kPosBytes + s * BT * 128, idesc,
+                           s == 0);
 #pragma unroll
             for (int s = 0; s < Cfg::kSub; s++)
-              mma_main_ss(tb + Cfg::kS, r + s * 16384, st + s * BT * 128, idesc);
-#pragma unroll
-            for (int s = 0; s < Cfg::kSub; s++)
-              mma_corr_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, r + 3 * Cfg::kOperBytes + s * 16384,
-                          st + 2 * Cfg::kPosBytes + s * BT * 128, st + 3 * Cfg::kPosBytes + s * BT * 128, idesc,
-                          s == 0);
-#pragma unroll
-            for (int s = 0; s < Cfg::kSub; s++)
-              mma_main_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128,
-                          idesc);
+              mma2_main_ss(tb + Cfg::kS, r + s * 16384, st + s * BT * 128,
+                           tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128,
+                           idesc);
             umma_commit(&sdp_full[h]);
           } else {
             umma_commit(&acc_done[h]);

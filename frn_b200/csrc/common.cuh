@@ -207,6 +207,9 @@ int softmax_rows(cudaStream_t st, long rows, int N, float* S, float* lse);      
 int exp_sub_lse(cudaStream_t st, long rows, int N, float* S, const float* lse);   // in place
 int ds_from_p(cudaStream_t st, long rows, int N, const float* P, float* dP, const float* delta);
 int fill_zero(cudaStream_t st, float* p, size_t count);
+// x (B, N, d) -= its mean over the N positions, per (b, channel); part: B * center_cols_parts(N) * d floats.
+int center_cols_parts(int N);
+int center_cols(cudaStream_t st, int B, int N, int d, float* x, float* part);
 int scale_sum_batch(cudaStream_t st, int B, int C, const float* alpha, float scale, float* out);
 
 }  // namespace frn

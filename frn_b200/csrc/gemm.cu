@@ -316,7 +316,7 @@ int gemm_engine() {
   int e = g_engine.load(std::memory_order_relaxed);
   if (e < 0) {
     const char* s = getenv("FRN_GEMM_ENGINE");
-    e = (s && (s[0] == 't' || s[0] == 'T' || s[0] == '1')) ? 1 : 0;   // default: FFMA
+    e = (s && (s[0] == 'f' || s[0] == 'F' || s[0] == '0')) ? 0 : 1;   // default: tcgen05
     g_engine.store(e);
   }
   return e;

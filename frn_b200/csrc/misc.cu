@@ -110,6 +110,42 @@ __global__ void outer_accumulate_kernel(int B, int C, int K, const float* __rest
   }
 }
 
+// Column sums of x (B, N, d) over a chunk of positions: part[(b*G + g)*d + k].  grid (G, B), 256 threads.
+__global__ void __launch_bounds__(256)
+col_partial_sum_kernel(int N, int d, int rows_per_block, const float* __restrict__ x, float* __restrict__ part) {
+  __shared__ float red[256];
+  const int b = blockIdx.y, g = blockIdx.x, G = gridDim.x;
+  const int n0 = g * rows_per_block, n1 = min(N, n0 + rows_per_block);
+  const int lanes = 256 / d * d;                 // threads used: a whole number of rows per pass
+  const int tid = threadIdx.x, k = tid % d, r = tid / d, rstep = 256 / d;
+  float s = 0.f;
+  if (tid < lanes)
+    for (int n = n0 + r; n < n1; n += rstep) s += __ldg(x + ((long)b * N + n) * d + k);
+  red[tid] = tid < lanes ? s : 0.f;
+  __syncthreads();
+  if (tid < d) {
+    float t = 0.f;
+    for (int q = 0; q < rstep; q++) t += red[q * d + tid];
+    part[((long)b * G + g) * d + tid] = t;
+  }
+}
+// x[b][n][k] -= (sum_g part[b][g][k]) / N
+__global__ void __launch_bounds__(256)
+col_center_kernel(int N, int d, int G, int rows_per_block, float* __restrict__ x, const float* __restrict__ part) {
+  __shared__ float mean[256];
+  const int b = blockIdx.y, n0 = blockIdx.x * rows_per_block, n1 = min(N, n0 + rows_per_block);
+  const int tid = threadIdx.x;
+  if (tid < d) {
+    float t = 0.f;
+    for (int g = 0; g < G; g++) t += part[((long)b * G + g) * d + tid];
+    mean[tid] = t / (float)N;
+  }
+  __syncthreads();
+  float* xb = x + ((long)b * N + n0) * d;
+  const int total = (n1 - n0) * d;
+  for (int i = tid; i < total; i += 256) xb[i] -= mean[i % d];
+}
+
 __global__ void fill_zero_kernel(float* __restrict__ p, size_t count) {
   size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += stride) p[i] = 0.f;
@@ -249,6 +285,19 @@ int scale_rows(cudaStream_t st, int B, int C, int K, const float* w, const float
 int outer_accumulate(cudaStream_t st, int B, int C, int K, const float* alpha, const float* ybar, float scale,
                      float* dW) {
   outer_accumulate_kernel<<<grid_for((long)C * K), 256, 0, st>>>(B, C, K, alpha, ybar, scale, dW);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int center_cols_parts(int N) { return cdiv(N, 256) < 64 ? cdiv(N, 256) : 64; }
+
+int center_cols(cudaStream_t st, int B, int N, int d, float* x, float* part) {
+  if (d > 256) return FRN_ERR_UNSUPPORTED;
+  const int G = center_cols_parts(N), rpb = cdiv(N, G);
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  col_partial_sum_kernel<<<dim3(G, B), 256, 0, st>>>(N, d, rpb, x, part);
+  FRN_LAUNCH_CHECK();
+  col_center_kernel<<<dim3(G, B), 256, 0, st>>>(N, d, G, rpb, x, part);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }

@@ -1,14 +1,22 @@
 // tcgen05 (5th-gen tensor core) version of the strided batched GEMM in gemm.cu, with
 // split-precision operands: every fp32 operand x is staged in shared memory as a tf32 pair
-// (hi, lo) and the product is accumulated as lo*hi' + hi*lo' + hi*hi' in an fp32 TMEM
-// accumulator (3xTF32), which keeps the fp32 parity gate (<= 1e-5 vs fp64) that single-pass
-// TF32 (~1e-3) cannot meet.
+// (hi, lo) and the product is accumulated as hi*hi' (main accumulator) and lo*hi' + hi*lo' + lo*lo'
+// (second accumulator) in fp32 TMEM columns (split TF32), which keeps the fp32 parity gate
+// (<= 1e-5 vs fp64) that single-pass TF32 (~1e-3) cannot meet.
 //
-// CTA = 128 x BN output tile.  Warps 0-3 stage operand tiles (global -> registers -> hi/lo split
-// -> SWIZZLE_128B K-major shared memory; arbitrary element strides, so every transposed use is
-// free), warp 4 lane 0 issues tcgen05.mma (M=128, N=BN, K=8 per instruction, 12 per 32-deep
-// stage) and commits stage release / accumulator-ready to mbarriers, then warps 0-3 read the
-// accumulator back with tcgen05.ld (thread = output row) for the epilogue.
+// CTA = 128 x BN output tile, 17 warps:
+//   warps 0-3 / 4-7  two operand-staging groups that alternate 32-deep K stages (global ->
+//                    registers, all loads of a stage in flight before the first use -> hi/lo split
+//                    -> SWIZZLE_128B K-major shared memory; arbitrary element strides, so every
+//                    transposed use is free),
+//   warp 8           tcgen05.mma issue (whole warp waits, one elected lane issues: M=128, N=BN,
+//                    K=8 per instruction, 16 per stage) and commits to mbarriers,
+//   warps 9-16       accumulator drain + epilogue (thread = output row, half of the columns).
+// The tensor core TRUNCATES when it aligns addends to the accumulator: a relative bias of
+// ~3e-9 per K = 8 step that grows linearly with K (tools/tc_error_vs_k.py: 6e-6 at K = 2048).
+// So no accumulation chain is longer than kChunk = 4 stages (K = 128): the accumulators are
+// double buffered in TMEM and each finished chunk is added into fp32 registers by the drain
+// warps while the next chunk is being multiplied.
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -19,46 +27,58 @@ using namespace tc;
 
 constexpr int TBM = 128;      // UMMA M
 constexpr int TBK = 32;       // 32 tf32 = one 128-byte swizzle row
-constexpr int kLoaders = 128;
-constexpr int kTcThreads = 160;
+constexpr int kGroup = 128;   // threads of one staging group
+constexpr int kMmaWarp = 8;
+constexpr int kEpiWarp0 = 9;
+constexpr int kEpiThreads = 256;
+constexpr int kTcThreads = (kEpiWarp0 + 8) * 32;   // 544
+constexpr int kChunk = 4;     // stages per accumulation chain (K = 128)
 
 template <int BN> struct TcCfg {
   static constexpr int kStages = BN <= 64 ? 4 : 3;
   static constexpr int kABytes = TBM * TBK * 4;            // one of hi / lo
   static constexpr int kBBytes = BN * TBK * 4;
   static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
-  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-  static constexpr int kTmemCols = 2 * BN;               // [0, BN): hi*hi ; [BN, 2BN): lo*hi + hi*lo
+  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 1024 /*barriers, reduction scratch*/;
+  static constexpr int kTmemCols = 4 * BN;               // 2 buffers x (hi*hi | lo*hi + hi*lo)
 };
 
 // Stage a [ROWS x 32] K-major tile: element (r, k) = g[r*rs + k*ks], zero outside (rows, kvalid).
 template <int ROWS>
 __device__ __forceinline__ void stage_tile(float* __restrict__ hi, float* __restrict__ lo,
                                            const float* __restrict__ g, long rs, long ks, int rows, int kvalid,
-                                           int tid) {
-  constexpr int CHUNKS = ROWS * 8;
+                                           int lt) {
+  constexpr int CH = ROWS * 8 / kGroup;        // 16-byte chunks per thread
   const bool kfast = (ks == 1);
   const bool vec = kfast && ((rs & 3) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
-#pragma unroll 4
-  for (int idx = tid; idx < CHUNKS; idx += kLoaders) {
+  float v[CH][4];
+#pragma unroll
+  for (int i = 0; i < CH; i++) {
+    const int idx = lt + i * kGroup;
     int r, c;
     if (kfast) { c = idx & 7; r = idx >> 3; } else { r = idx % ROWS; c = idx / ROWS; }
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    v[i][0] = v[i][1] = v[i][2] = v[i][3] = 0.f;
     if (r < rows) {
       const float* p = g + (long)r * rs + (long)(c * 4) * ks;
       if (vec && c * 4 + 3 < kvalid) {
         float4 t = __ldg(reinterpret_cast<const float4*>(p));
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+        v[i][0] = t.x; v[i][1] = t.y; v[i][2] = t.z; v[i][3] = t.w;
       } else {
 #pragma unroll
         for (int q = 0; q < 4; q++)
-          if (c * 4 + q < kvalid) v[q] = __ldg(p + (long)q * ks);
+          if (c * 4 + q < kvalid) v[i][q] = __ldg(p + (long)q * ks);
       }
     }
+  }
+#pragma unroll
+  for (int i = 0; i < CH; i++) {
+    const int idx = lt + i * kGroup;
+    int r, c;
+    if (kfast) { c = idx & 7; r = idx >> 3; } else { r = idx % ROWS; c = idx / ROWS; }
     float h[4], l[4];
 #pragma unroll
-    for (int q = 0; q < 4; q++) split_tf32(v[q], h[q], l[q]);
-    int o = sw128_chunk_offset(r, c);
+    for (int q = 0; q < 4; q++) split_tf32(v[i][q], h[q], l[q]);
+    const int o = sw128_chunk_offset(r, c);
     *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
     *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
   }
@@ -68,12 +88,15 @@ template <int BN, int EPI>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_split, int nsplit) {
   using Cfg = TcCfg<BN>;
+  constexpr int HC = BN / 2;          // columns per drain thread
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
   uint64_t* empty = full + Cfg::kStages;
-  uint64_t* acc_ready = empty + Cfg::kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+  uint64_t* acc_full = empty + Cfg::kStages;     // 2
+  uint64_t* acc_free = acc_full + 2;             // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_free + 2);
+  float* red = reinterpret_cast<float*>(tmem_slot + 4);   // 128 floats (row-sum-of-squares epilogue)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * BN;
@@ -86,128 +109,141 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
   } else {
     t_begin = 0; t_end = ktiles; b_fixed = z;
   }
+  const int ntiles = max(t_end - t_begin, 0);
 
   if (tid == 0) {
-    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&full[s], kLoaders); mbar_init(&empty[s], 1); }
-    mbar_init(acc_ready, 1);
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&full[s], kGroup); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_free[s], kEpiThreads); }
     mbar_init_fence();
   }
-  if (warp == 4) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == kMmaWarp) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
 
-  if (warp < 4) {
-    // ===== operand staging =====
-    int stage = 0; uint32_t phase = 0;
-    for (int t = t_begin; t < t_end; t++) {
-      int b = b_fixed >= 0 ? b_fixed : t / ktiles;
-      int k0 = (b_fixed >= 0 ? t : t % ktiles) * TBK;
+  if (warp < kMmaWarp) {
+    // ===== operand staging: group g takes local tiles g, g+2, ... =====
+    const int grp = warp >> 2, lt = tid & (kGroup - 1);
+    for (int i = grp; i < ntiles; i += 2) {
+      const int t = t_begin + i;
+      const int stage = i % Cfg::kStages;
+      const uint32_t phase = (i / Cfg::kStages) & 1;
+      const int b = b_fixed >= 0 ? b_fixed : t / ktiles;
+      const int k0 = (b_fixed >= 0 ? t : t % ktiles) * TBK;
       mbar_wait(&empty[stage], phase ^ 1);
       float* sA = reinterpret_cast<float*>(smem + stage * Cfg::kStageBytes);
       float* sAl = sA + TBM * TBK;
       float* sB = sAl + TBM * TBK;
       float* sBl = sB + BN * TBK;
       stage_tile<TBM>(sA, sAl, p.A + (long)b * p.sAb + (long)m0 * p.sAm + (long)k0 * p.sAk, p.sAm, p.sAk,
-                      p.M - m0, p.K - k0, tid);
+                      p.M - m0, p.K - k0, lt);
       stage_tile<BN>(sB, sBl, p.B + (long)b * p.sBb + (long)n0 * p.sBn + (long)k0 * p.sBk, p.sBn, p.sBk,
-                     p.N - n0, p.K - k0, tid);
+                     p.N - n0, p.K - k0, lt);
       fence_proxy_async_smem();
       mbar_arrive(&full[stage]);
-      if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
     }
-  } else if (lane == 0) {
-    // ===== MMA issue (one thread) =====
+  } else if (warp == kMmaWarp) {
+    // ===== MMA issue =====
     constexpr uint32_t idesc = umma_idesc_tf32(TBM, BN);
-    int stage = 0; uint32_t phase = 0;
-    bool acc = false;
-    for (int t = t_begin; t < t_end; t++) {
+    for (int i = 0; i < ntiles; i++) {
+      const int stage = i % Cfg::kStages;
+      const uint32_t phase = (i / Cfg::kStages) & 1;
+      const int chunk = i / kChunk, buf = chunk & 1;
+      const bool first = (i % kChunk) == 0;
+      if (first && chunk >= 2) mbar_wait(&acc_free[buf], ((chunk >> 1) - 1) & 1);
       mbar_wait(&full[stage], phase);
       tc_fence_after();
-      uint32_t base = smem_u32(smem + stage * Cfg::kStageBytes);
-      uint64_t a_hi = umma_desc_sw128(base), a_lo = umma_desc_sw128(base + Cfg::kABytes);
-      uint64_t b_hi = umma_desc_sw128(base + 2 * Cfg::kABytes);
-      uint64_t b_lo = umma_desc_sw128(base + 2 * Cfg::kABytes + Cfg::kBBytes);
+      if (elect_one()) {
+        const uint32_t base = smem_u32(smem + stage * Cfg::kStageBytes);
+        const uint64_t a_hi = umma_desc_sw128(base), a_lo = umma_desc_sw128(base + Cfg::kABytes);
+        const uint64_t b_hi = umma_desc_sw128(base + 2 * Cfg::kABytes);
+        const uint64_t b_lo = umma_desc_sw128(base + 2 * Cfg::kABytes + Cfg::kBBytes);
+        const uint32_t d_main = tmem_acc + buf * 2 * BN, d_small = d_main + BN;
 #pragma unroll
-      for (int k = 0; k < TBK / 8; k++) {   // +32 bytes per K = 8 slice: start-address field += 2
-        // The tensor core truncates when it aligns addends to the accumulator, so the two
-        // correction terms (2^-11 of the main term) get their own accumulator (columns [BN, 2BN)).
-        umma_tf32_ss(tmem_acc + BN, a_lo + 2 * k, b_hi + 2 * k, idesc, acc);
-        umma_tf32_ss(tmem_acc + BN, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
-        umma_tf32_ss(tmem_acc, a_hi + 2 * k, b_hi + 2 * k, idesc, acc);
-        acc = true;
+        for (int k = 0; k < TBK / 8; k++) {   // +32 bytes per K = 8 slice: start-address field += 2
+          const bool acc = !(first && k == 0);
+          // lo*lo (2^-22 of the product) is kept as well: when one operand is near-constant (|mean| >> sigma,
+          // the blanked-RGB case of model.py:279-280) all of its variation lives in `lo`, and a product with a
+          // zero-sum partner would otherwise be 2^-11 off.
+          umma_tf32_ss(d_small, a_lo + 2 * k, b_lo + 2 * k, idesc, acc);
+          umma_tf32_ss(d_small, a_lo + 2 * k, b_hi + 2 * k, idesc, true);
+          umma_tf32_ss(d_small, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
+          umma_tf32_ss(d_main, a_hi + 2 * k, b_hi + 2 * k, idesc, acc);
+        }
+        umma_commit(&empty[stage]);            // frees the stage once these MMAs have read it
+        if ((i % kChunk) == kChunk - 1 || i == ntiles - 1) umma_commit(&acc_full[buf]);
       }
-      umma_commit(&empty[stage]);            // frees the stage once these MMAs have read it
-      if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      __syncwarp();
     }
-    umma_commit(acc_ready);
-  }
-
-  // ===== epilogue: warps 0-3, thread = output row =====
-  if (warp < 4) {
-    const bool any = t_begin < t_end;
-    if (any) {
-      mbar_wait(acc_ready, 0);
+  } else {
+    // ===== accumulator drain + epilogue: thread = output row, HC of the BN columns =====
+    const int e = warp - kEpiWarp0;
+    const int quad = warp & 3, half = e >> 2;
+    const int row = quad * 32 + lane, gm = m0 + row;
+    const uint32_t tlane = ((uint32_t)(quad * 32)) << 16;
+    float acc[HC];
+#pragma unroll
+    for (int j = 0; j < HC; j++) acc[j] = 0.f;
+    const int nchunks = (ntiles + kChunk - 1) / kChunk;
+    for (int chunk = 0; chunk < nchunks; chunk++) {
+      const int buf = chunk & 1;
+      mbar_wait(&acc_full[buf], (chunk >> 1) & 1);
       tc_fence_after();
+      const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
+#pragma unroll
+      for (int c0 = 0; c0 < HC; c0 += 16) {
+        float v[16], w[16];
+        tmem_ld16(taddr + c0, v);
+        tmem_ld16(taddr + BN + c0, w);
+        tmem_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_free[buf]);
     }
-    const int row = warp * 32 + lane, gm = m0 + row;
-    const uint32_t taddr = tmem_acc + ((uint32_t)(warp * 32) << 16);
     const bool partial = p.reduce_batch && nsplit > 1;
+    const int nb = n0 + half * HC;          // first global column of this thread
     if (EPI == GEMM_EPI_ROWSUMSQ) {
       float s = 0.f;
 #pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += 16) {
-        float v[16], w[16];
-        if (any) { tmem_ld16(taddr + c0, v); tmem_ld16(taddr + BN + c0, w); tmem_wait_ld(); }
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-          float x = any ? p.alpha * (v[j] + w[j]) : 0.f;
-          s += (n0 + c0 + j < p.N) ? x * x : 0.f;
-        }
+      for (int j = 0; j < HC; j++) {
+        const float x = p.alpha * acc[j];
+        s += (nb + j < p.N) ? x * x : 0.f;
       }
-      if (gm < p.M) aux[((long)z * p.M + gm) * gridDim.x + blockIdx.x] = s;
-    } else {
+      if (half == 1) red[row] = s;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0 && gm < p.M) aux[((long)z * p.M + gm) * gridDim.x + blockIdx.x] = s + red[row];
+    } else if (gm < p.M) {
       float* Cb; long sCm, sCn;
       if (partial) { Cb = aux + (long)z * p.M * p.N; sCm = p.N; sCn = 1; }
       else { Cb = p.C + (p.reduce_batch ? 0 : (long)z * p.sCb); sCm = p.sCm; sCn = p.sCn; }
       const bool acc_out = !partial && p.accumulate;
       const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
-      const float bm = (!partial && p.bias_m && gm < p.M) ? __ldg(p.bias_m + boff + gm) : 0.f;
+      const float bm = (!partial && p.bias_m) ? __ldg(p.bias_m + boff + gm) : 0.f;
       const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
 #pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += 16) {
-        float v[16], w[16];
-        if (any) {
-          tmem_ld16(taddr + c0, v); tmem_ld16(taddr + BN + c0, w); tmem_wait_ld();
+      for (int c0 = 0; c0 < HC; c0 += 4) {
+        float o[4];
 #pragma unroll
-          for (int j = 0; j < 16; j++) v[j] += w[j];
+        for (int j = 0; j < 4; j++) {
+          const int gn = nb + c0 + j;
+          const float bn = (!partial && p.bias_n && gn < p.N) ? __ldg(p.bias_n + boff + gn) : 0.f;
+          o[j] = fmaf(p.alpha, acc[c0 + j], bm + bn);
+        }
+        float* dst = Cb + (long)gm * sCm + (long)(nb + c0) * sCn;
+        if (vec && nb + c0 + 3 < p.N) {
+          float4 q = make_float4(o[0], o[1], o[2], o[3]);
+          float4* d4 = reinterpret_cast<float4*>(dst);
+          if (acc_out) { float4 c = *d4; q.x += c.x; q.y += c.y; q.z += c.z; q.w += c.w; }
+          *d4 = q;
         } else {
 #pragma unroll
-          for (int j = 0; j < 16; j++) v[j] = 0.f;
-        }
-        if (gm >= p.M) continue;
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-          int gn = n0 + c0 + j;
-          float bn = (!partial && p.bias_n && gn < p.N) ? __ldg(p.bias_n + boff + gn) : 0.f;
-          v[j] = fmaf(p.alpha, v[j], bm + bn);
-        }
-        float* dst = Cb + (long)gm * sCm + (long)(n0 + c0) * sCn;
-        if (vec && n0 + c0 + 15 < p.N) {
-#pragma unroll
-          for (int q = 0; q < 4; q++) {
-            float4 o = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-            float4* d4 = reinterpret_cast<float4*>(dst) + q;
-            if (acc_out) { float4 c = *d4; o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w; }
-            *d4 = o;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; j++)
-            if (n0 + c0 + j < p.N) {
+          for (int j = 0; j < 4; j++)
+            if (nb + c0 + j < p.N) {
               float* d1 = dst + (long)j * sCn;
-              *d1 = v[j] + (acc_out ? *d1 : 0.f);
+              *d1 = o[j] + (acc_out ? *d1 : 0.f);
             }
         }
       }
@@ -215,7 +251,7 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc<Cfg::kTmemCols>(tmem_acc);
+  if (warp == kMmaWarp) tmem_dealloc<Cfg::kTmemCols>(tmem_acc);
 }
 
 
@@ -245,7 +281,7 @@ TcPlan tc_plan(const GemmDesc& in, bool allow_swap) {
     long T = (long)d.batch * pl.ktiles;
     long ctas = (long)cdiv(d.M, TBM) * cdiv(d.N, pl.bn);
     long want = cdiv(2 * 148, ctas);
-    long min_split = cdiv(T, 128);              // <= 4096 k per partial
+    long min_split = cdiv(T, 1024);             // <= 32768 k per partial (chunk sums are added in fp32 registers)
     long max_split = T / 4 > 0 ? T / 4 : 1;     // >= 128 k per split
     long ns = want < min_split ? min_split : want;
     if (ns > max_split) ns = max_split;

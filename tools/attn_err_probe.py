@@ -43,12 +43,12 @@ def block_tensors(c, h, w, kind, blk):
     z = (x0 - mu_x) / sd_x * sd_t + mu_t
     half = dout[:, :c] if blk == "rgb_cross_attention" else dout[:, c:]
     z.backward(half)
-    return Q, K, V, Y, Y.grad
+    return Q, K, V, Y, Y.grad, x0.detach(), x1.detach()
 
 
 for (c, h, w, kind) in [(512, 60, 80, "randn"), (256, 120, 160, "relu"), (512, 33, 44, "relu")]:
     for blk in ("rgb_cross_attention", "event_cross_attention"):
-        Q, K, V, Y, dY = block_tensors(c, h, w, kind, blk)
+        Q, K, V, Y, dY, x0, x1 = block_tensors(c, h, w, kind, blk)
         q32, k32, v32, dy32 = (t.detach().float().contiguous() for t in (Q, K, V, dY))
         # reference gradients for the fp32-rounded operands, in fp64
         q, k, v = (t.double().requires_grad_(True) for t in (q32, k32, v32))
@@ -61,3 +61,13 @@ for (c, h, w, kind) in [(512, 60, 80, "randn"), (256, 120, 160, "relu"), (512, 3
             print(f"C={c} {h}x{w} {kind} {blk[:3]} {['ffma', 'tc  '][eng]}: Y {stats(y, Yr.detach())} | "
                   f"dQ {stats(g[0], ref[0])} | dK {stats(g[1], ref[1])} | dV {stats(g[2], ref[2])}"
                   f" | sum_n dQ {stats(g[0].double().sum(1), ref[0].sum(1))}")
+            # weight gradients formed in fp64 from the engine's fp32 dK / dQ (isolates the attention error)
+            X1 = x1.view(1, c, -1).double()                      # (1, C, N)
+            for nm, gi, ri in (("theta.w", g[1], ref[1]), ("phi.w", g[0], ref[0])):
+                w_ref = ri.transpose(1, 2) @ X1.transpose(1, 2)     # (1, d, C)
+                gd = gi.double()
+                w_eng = gd.transpose(1, 2) @ X1.transpose(1, 2)
+                gz = gd - gd.mean(1, keepdim=True) if nm == "theta.w" else gd
+                w_prj = gz.transpose(1, 2) @ X1.transpose(1, 2)
+                print(f"      {nm}: wgrad-from-engine-grad {stats(w_eng, w_ref)} | after zero-mean projection {stats(w_prj, w_ref)}"
+                      f" | |sum_n g| / sum_n |g| = {float(gd.sum(1).abs().sum() / gd.abs().sum()):.2e}")
