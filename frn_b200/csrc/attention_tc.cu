@@ -919,6 +919,7 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
     auto kern = attn_dkv_tc_kernel<DPAD, NT>;
     FRN_TRY(set_smem(kern, Cfg::kSmem));
     dim3 grid(cdiv(NP / 128, NT), B, cdiv(d, 32));
+    ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
     kern<<<grid, Cfg::kThreads, Cfg::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
     FRN_LAUNCH_CHECK();
   }

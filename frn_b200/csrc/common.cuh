@@ -109,6 +109,7 @@ void set_gemm_engine(int e);
 size_t tc_gemm_workspace_bytes(const GemmDesc& d);
 int tc_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);
 int tc_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
+int tc_gemm_trace_read(unsigned long long* out16);   // role cycle counters, only with -DFRN_GEMM_TRACE
 size_t ffma_gemm_workspace_bytes(const GemmDesc& d);
 int ffma_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);
 int ffma_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
@@ -187,8 +188,10 @@ int center_rows(cudaStream_t st, long rows, int N, const float* y, const float* 
 // out[r] = sum_n x[r][n]*y[r][n]   (rows of length N)
 int row_dot(cudaStream_t st, long rows, int N, const float* x, const float* y, float* out);
 // out[m] = sum_b sum_n x[b*sb + m*sm + n*sn]
+// scratch (optional, batch_row_sum_scratch floats) enables the coalesced path for position-major x
 int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb, long sm, long sn,
-                  float* out);
+                  float* out, float* scratch = nullptr);
+size_t batch_row_sum_scratch(int B, int M, int N);
 // gate backward: dr0 = dr1*(1+e0) + de1*e0 ; de0 = de1*(1+r0) + dr1*r0 (in place allowed)
 int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
                   const float* de1, float* dr0, float* de0);

@@ -89,7 +89,12 @@ int conv1x1_wgrad(Ctx& c, const float* dy, long sm, long sn, long sb, const floa
   d.sCm = K; d.sCn = 1;
   d.reduce_batch = 1;
   FRN_TRY(run_gemm(c, d));
-  if (db) RUN(c, batch_row_sum(c.st, batch, M, N, dy, sb, sm, sn, db));
+  if (db) {
+    size_t mark = c.ws.off;
+    float* scratch = c.ws.take<float>(batch_row_sum_scratch(batch, M, N));
+    RUN(c, batch_row_sum(c.st, batch, M, N, dy, sb, sm, sn, db, scratch));
+    c.ws.release_to(mark);
+  }
   return FRN_OK;
 }
 
@@ -501,6 +506,7 @@ int frn_gemm_f32(void* stream, int engine, const frn_gemm_desc* g, void* ws, siz
   if (engine < 0) engine = gemm_engine();
   return engine ? tc_gemm((cudaStream_t)stream, d, ws, ws_bytes) : ffma_gemm((cudaStream_t)stream, d, ws, ws_bytes);
 }
+int frn_debug_gemm_trace(unsigned long long* out16) { return frn::tc_gemm_trace_read(out16); }
 void frn_set_gemm_engine(int engine) { set_gemm_engine(engine); }
 void frn_set_attn_engine(int engine) { set_attn_engine(engine); }
 int frn_get_attn_engine(void) { return attn_engine(); }

@@ -248,7 +248,22 @@ int finish_style_std(cudaStream_t st, long rows, int nparts, int N, const float*
   return FRN_OK;
 }
 
-int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb, long sm, long sn, float* out) {
+int center_cols_parts(int N) { return cdiv(N, 256) < 64 ? cdiv(N, 256) : 64; }
+
+size_t batch_row_sum_scratch(int B, int M, int N) { return (size_t)B * center_cols_parts(N) * M; }
+
+int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb, long sm, long sn, float* out,
+                  float* scratch) {
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  if (scratch && sm == 1 && sn == M && sb == (long)N * M && M <= 256) {
+    // position-major (B, N, M): coalesced column sums over chunks of positions, then one small reduction
+    const int G = center_cols_parts(N), rpb = cdiv(N, G);
+    col_partial_sum_kernel<<<dim3(G, B), 256, 0, st>>>(N, M, rpb, x, scratch);
+    FRN_LAUNCH_CHECK();
+    batch_row_sum_kernel<<<M, 256, 0, st>>>(1, M, B * G, scratch, 0, 1, M, out);
+    FRN_LAUNCH_CHECK();
+    return FRN_OK;
+  }
   batch_row_sum_kernel<<<M, 256, 0, st>>>(B, M, N, x, sb, sm, sn, out);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
@@ -288,8 +303,6 @@ int outer_accumulate(cudaStream_t st, int B, int C, int K, const float* alpha, c
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }
-
-int center_cols_parts(int N) { return cdiv(N, 256) < 64 ? cdiv(N, 256) : 64; }
 
 int center_cols(cudaStream_t st, int B, int N, int d, float* x, float* part) {
   if (d > 256) return FRN_ERR_UNSUPPORTED;

@@ -27,66 +27,158 @@ using namespace tc;
 
 constexpr int TBM = 128;      // UMMA M
 constexpr int TBK = 32;       // 32 tf32 = one 128-byte swizzle row
-constexpr int kGroup = 128;   // threads of one staging group
+constexpr int kLoaders = 256;  // staging threads (warps 0-7)
 constexpr int kMmaWarp = 8;
 constexpr int kEpiWarp0 = 9;
 constexpr int kEpiThreads = 256;
 constexpr int kTcThreads = (kEpiWarp0 + 8) * 32;   // 544
+constexpr int kSmCount = 148;  // B200
 constexpr int kChunk = 4;     // stages per accumulation chain (K = 128)
 
+// Optional cycle accounting of the role loops (CTA 0, one thread per role): compile with -DFRN_GEMM_TRACE.
+#ifdef FRN_GEMM_TRACE
+__device__ unsigned long long g_trace[16];
+#define TRACE_T0() const long long tr0__ = clock64()
+#define TRACE_ADD(slot) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) atomicAdd(&g_trace[slot], (unsigned long long)(clock64() - tr0__)); } while (0)
+#else
+#define TRACE_T0() do {} while (0)
+#define TRACE_ADD(slot) do {} while (0)
+#endif
+
 template <int BN> struct TcCfg {
-  static constexpr int kStages = BN <= 64 ? 4 : 3;
+  static constexpr int kStages = BN == 128 ? 2 : 3;        // split (hi / lo) operand stages feeding the MMAs
+  static constexpr int kRaw = 3;                           // raw fp32 stages in flight (cp.async)
   static constexpr int kABytes = TBM * TBK * 4;            // one of hi / lo
   static constexpr int kBBytes = BN * TBK * 4;
   static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
-  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 1024 /*barriers, reduction scratch*/;
-  static constexpr int kTmemCols = 4 * BN;               // 2 buffers x (hi*hi | lo*hi + hi*lo)
+  static constexpr int kRawBytes = kABytes + kBBytes;
+  static constexpr int kSmem = kStages * kStageBytes + kRaw * kRawBytes + 1024 /*align*/ + 1024 /*barriers, scratch*/;
+  static constexpr int kTmemCols = 4 * BN;               // 2 buffers x (hi*hi | lo*hi + hi*lo + lo*lo)
 };
 
-// Stage a [ROWS x 32] K-major tile: element (r, k) = g[r*rs + k*ks], zero outside (rows, kvalid).
-template <int ROWS>
-__device__ __forceinline__ void stage_tile(float* __restrict__ hi, float* __restrict__ lo,
-                                           const float* __restrict__ g, long rs, long ks, int rows, int kvalid,
-                                           int lt) {
-  constexpr int CH = ROWS * 8 / kGroup;        // 16-byte chunks per thread
-  const bool kfast = (ks == 1);
-  const bool vec = kfast && ((rs & 3) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
-  float v[CH][4];
+// ---- cp.async (LDGSTS) with zero fill: copies src_bytes (<= 16 or 4) and zero-fills the rest ----
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Per-thread plan of one operand's [ROWS x 32] tile, computed ONCE per kernel: the stage loop then runs
+// without index arithmetic (the generic-stride address math cost ~65 instructions per 16-byte chunk when it
+// lived inside the loop and made the staging warps, not the tensor pipe, the bottleneck).
+// Raw layout: k contiguous ([r][32]) when ks == 1 (KFAST), else r contiguous ([k][ROWS]).  Chunk = 4
+// consecutive elements along the unit-stride axis; thread t owns chunks t, t + 256, ...
+template <int ROWS> struct OperandPlan {
+  static constexpr int CH = ROWS * 8 / kLoaders;
+  long goff[CH];        // global element offset of the chunk from the tile origin
+  int outer[CH];        // index along the strided axis (row if KFAST else k)
+  int inner[CH];        // first index along the unit-stride axis (k if KFAST else row)
+  int dst[CH];          // float offset of the (row, 4 k) chunk in the swizzled hi / lo tiles
+  bool kfast;
+  __device__ __forceinline__ void init(long rs, long ks, int t) {
+    kfast = (ks == 1);
+    const long os = kfast ? rs : ks;
 #pragma unroll
-  for (int i = 0; i < CH; i++) {
-    const int idx = lt + i * kGroup;
-    int r, c;
-    if (kfast) { c = idx & 7; r = idx >> 3; } else { r = idx % ROWS; c = idx / ROWS; }
-    v[i][0] = v[i][1] = v[i][2] = v[i][3] = 0.f;
-    if (r < rows) {
-      const float* p = g + (long)r * rs + (long)(c * 4) * ks;
-      if (vec && c * 4 + 3 < kvalid) {
-        float4 t = __ldg(reinterpret_cast<const float4*>(p));
-        v[i][0] = t.x; v[i][1] = t.y; v[i][2] = t.z; v[i][3] = t.w;
-      } else {
-#pragma unroll
-        for (int q = 0; q < 4; q++)
-          if (c * 4 + q < kvalid) v[i][q] = __ldg(p + (long)q * ks);
+    for (int i = 0; i < CH; i++) {
+      const int idx = t + i * kLoaders;
+      if (kfast) { inner[i] = (idx & 7) * 4; outer[i] = idx >> 3; dst[i] = sw128_chunk_offset(outer[i], idx & 7); }
+      else {
+        inner[i] = (idx % (ROWS / 4)) * 4; outer[i] = idx / (ROWS / 4);
+        dst[i] = 0;   // conversion of this layout re-maps threads, see convert_tile
       }
+      goff[i] = (long)outer[i] * os + inner[i];
     }
+  }
+};
+
+template <int ROWS>
+__device__ __forceinline__ void issue_raw(float* __restrict__ raw, const float* __restrict__ g,
+                                          const OperandPlan<ROWS>& pl, long os, int rows, int kvalid, int t) {
+  constexpr int CH = OperandPlan<ROWS>::CH;
+  const bool vec = ((os & 3) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
+  const int n_in = pl.kfast ? kvalid : rows, n_out = pl.kfast ? rows : kvalid;
+  const bool interior = rows >= ROWS && kvalid >= TBK;
+  if (interior && vec) {
+#pragma unroll
+    for (int i = 0; i < CH; i++) cp_async16(raw + (t + i * kLoaders) * 4, g + pl.goff[i], 16);
+    return;
   }
 #pragma unroll
   for (int i = 0; i < CH; i++) {
-    const int idx = lt + i * kGroup;
-    int r, c;
-    if (kfast) { c = idx & 7; r = idx >> 3; } else { r = idx % ROWS; c = idx / ROWS; }
+    float* dst = raw + (t + i * kLoaders) * 4;
+    const float* src = g + pl.goff[i];
+    int valid = pl.outer[i] < n_out ? n_in - pl.inner[i] : 0;
+    valid = valid < 0 ? 0 : (valid > 4 ? 4 : valid);
+    if (vec) {
+      cp_async16(dst, valid ? src : g, valid * 4);
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; q++) cp_async4(dst + q, q < valid ? src + q : g, q < valid ? 4 : 0);
+    }
+  }
+}
+
+// raw tile -> tf32 hi / lo split -> SWIZZLE_128B K-major tiles
+template <int ROWS, bool KFAST>
+__device__ __forceinline__ void convert_tile(float* __restrict__ hi, float* __restrict__ lo,
+                                             const float* __restrict__ raw, const OperandPlan<ROWS>& pl, int t) {
+  constexpr int CH = OperandPlan<ROWS>::CH;
+#pragma unroll
+  for (int i = 0; i < CH; i++) {
+    float v[4];
+    int o;
+    if (KFAST) {
+      const float4 x = *reinterpret_cast<const float4*>(raw + (t + i * kLoaders) * 4);
+      v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+      o = pl.dst[i];
+    } else {
+      const int idx = t + i * kLoaders;
+      const int r = idx % ROWS, c = idx / ROWS;          // ROWS is a power of two: shifts and masks
+#pragma unroll
+      for (int q = 0; q < 4; q++) v[q] = raw[(c * 4 + q) * ROWS + r];
+      o = sw128_chunk_offset(r, c);
+    }
     float h[4], l[4];
 #pragma unroll
-    for (int q = 0; q < 4; q++) split_tf32(v[i][q], h[q], l[q]);
-    const int o = sw128_chunk_offset(r, c);
+    for (int q = 0; q < 4; q++) split_tf32(v[q], h[q], l[q]);
     *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
     *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
   }
 }
 
+// Work item of the persistent loop: output tile (m, n) of batch entry / K split z.
+struct TcTile { int m0, n0, z, t_begin, ntiles, b_fixed; };
+
+__device__ __forceinline__ TcTile tc_tile(const GemmDesc& p, int id, int gx, int gy, int ktiles,
+                                          int tiles_per_split, int BN) {
+  TcTile t;
+  const int my = id % gy;            // m fastest: CTAs that run together share the same B (activation) tile
+  const int nx = (id / gy) % gx;
+  t.z = id / (gx * gy);
+  t.m0 = my * TBM; t.n0 = nx * BN;
+  if (p.reduce_batch) {
+    t.t_begin = t.z * tiles_per_split;
+    const int t_end = min(t.t_begin + tiles_per_split, p.batch * ktiles);
+    t.ntiles = max(t_end - t.t_begin, 0);
+    t.b_fixed = -1;
+  } else {
+    t.t_begin = 0; t.ntiles = ktiles; t.b_fixed = t.z;
+  }
+  return t;
+}
+
+// Persistent: gridDim.x CTAs (one per SM) walk the gx*gy*gz output tiles; the shared-memory stage ring
+// and the two TMEM accumulator buffers keep running across tiles, so the staging of tile i+1 and its
+// first MMAs overlap the drain / global stores of tile i.
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kTcThreads, 1)
-tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_split, int nsplit) {
+tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_split, int nsplit, int gx, int gy,
+               int gz) {
   using Cfg = TcCfg<BN>;
   constexpr int HC = BN / 2;          // columns per drain thread
   extern __shared__ uint8_t smem_raw[];
@@ -99,20 +191,10 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
   float* red = reinterpret_cast<float*>(tmem_slot + 4);   // 128 floats (row-sum-of-squares epilogue)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * BN;
-  const int z = blockIdx.z;
-  int t_begin, t_end, b_fixed;
-  if (p.reduce_batch) {
-    t_begin = z * tiles_per_split;
-    t_end = min(t_begin + tiles_per_split, p.batch * ktiles);
-    b_fixed = -1;
-  } else {
-    t_begin = 0; t_end = ktiles; b_fixed = z;
-  }
-  const int ntiles = max(t_end - t_begin, 0);
+  const int total = gx * gy * gz;
 
   if (tid == 0) {
-    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&full[s], kGroup); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&full[s], kLoaders); mbar_init(&empty[s], 1); }
     for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_free[s], kEpiThreads); }
     mbar_init_fence();
   }
@@ -123,130 +205,208 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
   const uint32_t tmem_acc = *tmem_slot;
 
   if (warp < kMmaWarp) {
-    // ===== operand staging: group g takes local tiles g, g+2, ... =====
-    const int grp = warp >> 2, lt = tid & (kGroup - 1);
-    for (int i = grp; i < ntiles; i += 2) {
-      const int t = t_begin + i;
-      const int stage = i % Cfg::kStages;
-      const uint32_t phase = (i / Cfg::kStages) & 1;
-      const int b = b_fixed >= 0 ? b_fixed : t / ktiles;
-      const int k0 = (b_fixed >= 0 ? t : t % ktiles) * TBK;
+    // ===== operand staging: cp.async raw tiles kRaw - 1 stages ahead, then split into the MMA stage ring =====
+    uint8_t* raw_base = smem + Cfg::kStages * Cfg::kStageBytes + 1024;
+    OperandPlan<TBM> planA;
+    OperandPlan<BN> planB;
+    planA.init(p.sAm, p.sAk, tid);
+    planB.init(p.sBn, p.sBk, tid);
+    const long osA = planA.kfast ? p.sAm : p.sAk, osB = planB.kfast ? p.sBn : p.sBk;
+    struct Cursor { int id, i; TcTile tl; };
+    auto settle = [&](Cursor& c) {                 // move to the next tile that has stages left
+      while (c.id < total) {
+        c.tl = tc_tile(p, c.id, gx, gy, ktiles, tiles_per_split, BN);
+        if (c.i < c.tl.ntiles) return;
+        c.id += gridDim.x; c.i = 0;
+      }
+    };
+    auto issue = [&](const Cursor& c, long it) {
+      const TcTile& tl = c.tl;
+      const int t = tl.t_begin + c.i;
+      const int b = tl.b_fixed >= 0 ? tl.b_fixed : t / ktiles;
+      const int k0 = (tl.b_fixed >= 0 ? t : t % ktiles) * TBK;
+      float* rA = reinterpret_cast<float*>(raw_base + (it % Cfg::kRaw) * Cfg::kRawBytes);
+      float* rB = rA + TBM * TBK;
+      issue_raw<TBM>(rA, p.A + (long)b * p.sAb + (long)tl.m0 * p.sAm + (long)k0 * p.sAk, planA, osA,
+                     p.M - tl.m0, p.K - k0, tid);
+      issue_raw<BN>(rB, p.B + (long)b * p.sBb + (long)tl.n0 * p.sBn + (long)k0 * p.sBk, planB, osB,
+                    p.N - tl.n0, p.K - k0, tid);
+    };
+    Cursor ci{(int)blockIdx.x, 0, {}}, cc{(int)blockIdx.x, 0, {}};
+    settle(ci); settle(cc);
+    long it_issue = 0;
+    for (int r = 0; r < Cfg::kRaw - 1; r++) {      // prologue
+      if (ci.id < total) { issue(ci, it_issue); ci.i++; settle(ci); }
+      it_issue++;
+      cp_async_commit();
+    }
+    for (long it = 0; cc.id < total; it++) {
+      { TRACE_T0();
+      cp_async_wait<Cfg::kRaw - 2>();              // this thread's copies of stage `it` have landed
+      TRACE_ADD(0); }
+      { TRACE_T0();
+      asm volatile("bar.sync 2, 256;" ::: "memory");  // ... everyone's have, and everyone is done with stage it-1
+      TRACE_ADD(1); }
+      { TRACE_T0();
+      if (ci.id < total) { issue(ci, it_issue); ci.i++; settle(ci); }
+      it_issue++;
+      cp_async_commit();
+      TRACE_ADD(12); }
+      const int stage = (int)(it % Cfg::kStages);
+      const uint32_t phase = (uint32_t)((it / Cfg::kStages) & 1);
+      { TRACE_T0();
       mbar_wait(&empty[stage], phase ^ 1);
+      TRACE_ADD(2); }
+      TRACE_T0();
+      const float* rA = reinterpret_cast<const float*>(raw_base + (it % Cfg::kRaw) * Cfg::kRawBytes);
+      const float* rB = rA + TBM * TBK;
       float* sA = reinterpret_cast<float*>(smem + stage * Cfg::kStageBytes);
       float* sAl = sA + TBM * TBK;
       float* sB = sAl + TBM * TBK;
       float* sBl = sB + BN * TBK;
-      stage_tile<TBM>(sA, sAl, p.A + (long)b * p.sAb + (long)m0 * p.sAm + (long)k0 * p.sAk, p.sAm, p.sAk,
-                      p.M - m0, p.K - k0, lt);
-      stage_tile<BN>(sB, sBl, p.B + (long)b * p.sBb + (long)n0 * p.sBn + (long)k0 * p.sBk, p.sBn, p.sBk,
-                     p.N - n0, p.K - k0, lt);
+      { TRACE_T0();
+      if (planA.kfast) convert_tile<TBM, true>(sA, sAl, rA, planA, tid);
+      else convert_tile<TBM, false>(sA, sAl, rA, planA, tid);
+      TRACE_ADD(9); }
+      { TRACE_T0();
+      if (planB.kfast) convert_tile<BN, true>(sB, sBl, rB, planB, tid);
+      else convert_tile<BN, false>(sB, sBl, rB, planB, tid);
+      TRACE_ADD(10); }
+      { TRACE_T0();
       fence_proxy_async_smem();
       mbar_arrive(&full[stage]);
+      TRACE_ADD(11); }
+      TRACE_ADD(3);
+      cc.i++; settle(cc);
     }
+    cp_async_wait<0>();
   } else if (warp == kMmaWarp) {
     // ===== MMA issue =====
     constexpr uint32_t idesc = umma_idesc_tf32(TBM, BN);
-    for (int i = 0; i < ntiles; i++) {
-      const int stage = i % Cfg::kStages;
-      const uint32_t phase = (i / Cfg::kStages) & 1;
-      const int chunk = i / kChunk, buf = chunk & 1;
-      const bool first = (i % kChunk) == 0;
-      if (first && chunk >= 2) mbar_wait(&acc_free[buf], ((chunk >> 1) - 1) & 1);
-      mbar_wait(&full[stage], phase);
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t base = smem_u32(smem + stage * Cfg::kStageBytes);
-        const uint64_t a_hi = umma_desc_sw128(base), a_lo = umma_desc_sw128(base + Cfg::kABytes);
-        const uint64_t b_hi = umma_desc_sw128(base + 2 * Cfg::kABytes);
-        const uint64_t b_lo = umma_desc_sw128(base + 2 * Cfg::kABytes + Cfg::kBBytes);
-        const uint32_t d_main = tmem_acc + buf * 2 * BN, d_small = d_main + BN;
+    long it = 0;
+    int gc = 0;                                    // running chunk (accumulation chain) counter
+    for (int id = blockIdx.x; id < total; id += gridDim.x) {
+      const TcTile tl = tc_tile(p, id, gx, gy, ktiles, tiles_per_split, BN);
+      for (int i = 0; i < tl.ntiles; i++, it++) {
+        const int stage = (int)(it % Cfg::kStages);
+        const uint32_t phase = (uint32_t)((it / Cfg::kStages) & 1);
+        const bool first = (i % kChunk) == 0;
+        const bool last = (i % kChunk) == kChunk - 1 || i == tl.ntiles - 1;
+        const int buf = gc & 1;
+        { TRACE_T0();
+        if (first && gc >= 2) mbar_wait(&acc_free[buf], ((gc >> 1) - 1) & 1);
+        TRACE_ADD(4); }
+        { TRACE_T0();
+        mbar_wait(&full[stage], phase);
+        TRACE_ADD(5); }
+        tc_fence_after();
+        TRACE_T0();
+        if (elect_one()) {
+          const uint32_t base = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint64_t a_hi = umma_desc_sw128(base), a_lo = umma_desc_sw128(base + Cfg::kABytes);
+          const uint64_t b_hi = umma_desc_sw128(base + 2 * Cfg::kABytes);
+          const uint64_t b_lo = umma_desc_sw128(base + 2 * Cfg::kABytes + Cfg::kBBytes);
+          const uint32_t d_main = tmem_acc + buf * 2 * BN, d_small = d_main + BN;
 #pragma unroll
-        for (int k = 0; k < TBK / 8; k++) {   // +32 bytes per K = 8 slice: start-address field += 2
-          const bool acc = !(first && k == 0);
-          // lo*lo (2^-22 of the product) is kept as well: when one operand is near-constant (|mean| >> sigma,
-          // the blanked-RGB case of model.py:279-280) all of its variation lives in `lo`, and a product with a
-          // zero-sum partner would otherwise be 2^-11 off.
-          umma_tf32_ss(d_small, a_lo + 2 * k, b_lo + 2 * k, idesc, acc);
-          umma_tf32_ss(d_small, a_lo + 2 * k, b_hi + 2 * k, idesc, true);
-          umma_tf32_ss(d_small, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
-          umma_tf32_ss(d_main, a_hi + 2 * k, b_hi + 2 * k, idesc, acc);
+          for (int k = 0; k < TBK / 8; k++) {   // +32 bytes per K = 8 slice: start-address field += 2
+            const bool acc = !(first && k == 0);
+            // lo*lo (2^-22 of the product) is kept as well: when one operand is near-constant (|mean| >> sigma,
+            // the blanked-RGB case of model.py:279-280) all of its variation lives in `lo`, and a product with a
+            // zero-sum partner would otherwise be 2^-11 off.
+            umma_tf32_ss(d_small, a_lo + 2 * k, b_lo + 2 * k, idesc, acc);
+            umma_tf32_ss(d_small, a_lo + 2 * k, b_hi + 2 * k, idesc, true);
+            umma_tf32_ss(d_small, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
+            umma_tf32_ss(d_main, a_hi + 2 * k, b_hi + 2 * k, idesc, acc);
+          }
+          umma_commit(&empty[stage]);            // frees the stage once these MMAs have read it
+          if (last) umma_commit(&acc_full[buf]);
         }
-        umma_commit(&empty[stage]);            // frees the stage once these MMAs have read it
-        if ((i % kChunk) == kChunk - 1 || i == ntiles - 1) umma_commit(&acc_full[buf]);
+        __syncwarp();
+        TRACE_ADD(6);
+        if (last) gc++;
       }
-      __syncwarp();
     }
   } else {
     // ===== accumulator drain + epilogue: thread = output row, HC of the BN columns =====
     const int e = warp - kEpiWarp0;
     const int quad = warp & 3, half = e >> 2;
-    const int row = quad * 32 + lane, gm = m0 + row;
+    const int row = quad * 32 + lane;
     const uint32_t tlane = ((uint32_t)(quad * 32)) << 16;
-    float acc[HC];
+    int gc = 0;
+    for (int id = blockIdx.x; id < total; id += gridDim.x) {
+      const TcTile tl = tc_tile(p, id, gx, gy, ktiles, tiles_per_split, BN);
+      const int gm = tl.m0 + row, z = tl.z;
+      float acc[HC];
 #pragma unroll
-    for (int j = 0; j < HC; j++) acc[j] = 0.f;
-    const int nchunks = (ntiles + kChunk - 1) / kChunk;
-    for (int chunk = 0; chunk < nchunks; chunk++) {
-      const int buf = chunk & 1;
-      mbar_wait(&acc_full[buf], (chunk >> 1) & 1);
-      tc_fence_after();
-      const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
+      for (int j = 0; j < HC; j++) acc[j] = 0.f;
+      const int nchunks = (tl.ntiles + kChunk - 1) / kChunk;
+      for (int chunk = 0; chunk < nchunks; chunk++, gc++) {
+        const int buf = gc & 1;
+        { TRACE_T0();
+        mbar_wait(&acc_full[buf], (gc >> 1) & 1);
+        TRACE_ADD(7); }
+        tc_fence_after();
+        const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
 #pragma unroll
-      for (int c0 = 0; c0 < HC; c0 += 16) {
-        float v[16], w[16];
-        tmem_ld16(taddr + c0, v);
-        tmem_ld16(taddr + BN + c0, w);
-        tmem_wait_ld();
+        for (int c0 = 0; c0 < HC; c0 += 16) {
+          float v[16], w[16];
+          tmem_ld16(taddr + c0, v);
+          tmem_ld16(taddr + BN + c0, w);
+          tmem_wait_ld();
 #pragma unroll
-        for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
-      }
-      tc_fence_before();
-      mbar_arrive(&acc_free[buf]);
-    }
-    const bool partial = p.reduce_batch && nsplit > 1;
-    const int nb = n0 + half * HC;          // first global column of this thread
-    if (EPI == GEMM_EPI_ROWSUMSQ) {
-      float s = 0.f;
-#pragma unroll
-      for (int j = 0; j < HC; j++) {
-        const float x = p.alpha * acc[j];
-        s += (nb + j < p.N) ? x * x : 0.f;
-      }
-      if (half == 1) red[row] = s;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (half == 0 && gm < p.M) aux[((long)z * p.M + gm) * gridDim.x + blockIdx.x] = s + red[row];
-    } else if (gm < p.M) {
-      float* Cb; long sCm, sCn;
-      if (partial) { Cb = aux + (long)z * p.M * p.N; sCm = p.N; sCn = 1; }
-      else { Cb = p.C + (p.reduce_batch ? 0 : (long)z * p.sCb); sCm = p.sCm; sCn = p.sCn; }
-      const bool acc_out = !partial && p.accumulate;
-      const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
-      const float bm = (!partial && p.bias_m) ? __ldg(p.bias_m + boff + gm) : 0.f;
-      const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
-#pragma unroll
-      for (int c0 = 0; c0 < HC; c0 += 4) {
-        float o[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const int gn = nb + c0 + j;
-          const float bn = (!partial && p.bias_n && gn < p.N) ? __ldg(p.bias_n + boff + gn) : 0.f;
-          o[j] = fmaf(p.alpha, acc[c0 + j], bm + bn);
+          for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
         }
-        float* dst = Cb + (long)gm * sCm + (long)(nb + c0) * sCn;
-        if (vec && nb + c0 + 3 < p.N) {
-          float4 q = make_float4(o[0], o[1], o[2], o[3]);
-          float4* d4 = reinterpret_cast<float4*>(dst);
-          if (acc_out) { float4 c = *d4; q.x += c.x; q.y += c.y; q.z += c.z; q.w += c.w; }
-          *d4 = q;
-        } else {
+        tc_fence_before();
+        mbar_arrive(&acc_free[buf]);
+      }
+      const bool partial = p.reduce_batch && nsplit > 1;
+      const int nb = tl.n0 + half * HC;          // first global column of this thread
+      TRACE_T0();
+      if (EPI == GEMM_EPI_ROWSUMSQ) {
+        float s = 0.f;
 #pragma unroll
-          for (int j = 0; j < 4; j++)
-            if (nb + c0 + j < p.N) {
-              float* d1 = dst + (long)j * sCn;
-              *d1 = o[j] + (acc_out ? *d1 : 0.f);
-            }
+        for (int j = 0; j < HC; j++) {
+          const float x = p.alpha * acc[j];
+          s += (nb + j < p.N) ? x * x : 0.f;
+        }
+        if (half == 1) red[row] = s;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (half == 0 && gm < p.M) aux[((long)z * p.M + gm) * gx + (tl.n0 / BN)] = s + red[row];
+        asm volatile("bar.sync 1, 256;" ::: "memory");     // red[] is reused by the next tile
+      } else if (gm < p.M) {
+        float* Cb; long sCm, sCn;
+        if (partial) { Cb = aux + (long)z * p.M * p.N; sCm = p.N; sCn = 1; }
+        else { Cb = p.C + (p.reduce_batch ? 0 : (long)z * p.sCb); sCm = p.sCm; sCn = p.sCn; }
+        const bool acc_out = !partial && p.accumulate;
+        const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
+        const float bm = (!partial && p.bias_m) ? __ldg(p.bias_m + boff + gm) : 0.f;
+        const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+#pragma unroll
+        for (int c0 = 0; c0 < HC; c0 += 4) {
+          float o[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const int gn = nb + c0 + j;
+            const float bn = (!partial && p.bias_n && gn < p.N) ? __ldg(p.bias_n + boff + gn) : 0.f;
+            o[j] = fmaf(p.alpha, acc[c0 + j], bm + bn);
+          }
+          float* dst = Cb + (long)gm * sCm + (long)(nb + c0) * sCn;
+          if (vec && nb + c0 + 3 < p.N) {
+            float4 q = make_float4(o[0], o[1], o[2], o[3]);
+            float4* d4 = reinterpret_cast<float4*>(dst);
+            if (acc_out) { float4 c = *d4; q.x += c.x; q.y += c.y; q.z += c.z; q.w += c.w; }
+            *d4 = q;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+              if (nb + c0 + j < p.N) {
+                float* d1 = dst + (long)j * sCn;
+                *d1 = o[j] + (acc_out ? *d1 : 0.f);
+              }
+          }
         }
       }
+      TRACE_ADD(8);
     }
   }
   tc_fence_before();
@@ -300,8 +460,10 @@ int tc_launch_bn(cudaStream_t st, const TcPlan& pl, float* aux) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem);
   if (e != cudaSuccess) return (int)e;
   const GemmDesc& d = pl.d;
-  dim3 grid(cdiv(d.N, BN), cdiv(d.M, TBM), d.reduce_batch ? pl.nsplit : d.batch);
-  kern<<<grid, kTcThreads, Cfg::kSmem, st>>>(d, aux, pl.ktiles, pl.tiles_per_split, pl.nsplit);
+  const int gx = cdiv(d.N, BN), gy = cdiv(d.M, TBM), gz = d.reduce_batch ? pl.nsplit : d.batch;
+  const long total = (long)gx * gy * gz;
+  const int ctas = (int)(total < kSmCount ? total : kSmCount);      // persistent: one CTA per SM
+  kern<<<ctas, kTcThreads, Cfg::kSmem, st>>>(d, aux, pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }
@@ -314,6 +476,18 @@ int tc_launch(cudaStream_t st, const TcPlan& pl, float* aux) {
 }
 
 }  // namespace
+
+int tc_gemm_trace_read(unsigned long long* out16) {
+#ifdef FRN_GEMM_TRACE
+  unsigned long long z[16] = {0};
+  cudaMemcpyFromSymbol(out16, g_trace, sizeof(z));
+  cudaMemcpyToSymbol(g_trace, z, sizeof(z));
+  return 1;
+#else
+  (void)out16;
+  return 0;
+#endif
+}
 
 size_t tc_gemm_workspace_bytes(const GemmDesc& d) {
   if (!d.reduce_batch) return 0;

@@ -192,7 +192,8 @@ int frn_attn_backward(void* stream, int engine, int B, int N, int d, const float
  * number of launches, and clears the class.  Off by default; the only global
  * mutable state in the library besides the launch counter. */
 enum { FRN_TIME_ATTN_FWD = 0, FRN_TIME_ATTN_BWD = 1, FRN_TIME_GEMM = 2, FRN_TIME_ROWS = 3,
-       FRN_TIME_CLASSES = 4 };
+       FRN_TIME_ATTN_DKV = 4,   /* the dK/dV kernel alone (also counted inside class 1) */
+       FRN_TIME_CLASSES = 5 };
 void frn_timing_enable(int on);
 int frn_timing_read(int cls, double* ms, long* launches);
 

@@ -1,0 +1,55 @@
+"""Profiling driver: the tcgen05 GEMM on the block's dominant shapes (DSEC level 1, B = 8).
+  conv   C (8, 256, 19200) = W (256, 256) @ x (8, 256, 19200)          retinanet/fusion.py:23
+  wgrad  dW (256, 256) = sum_b dy_b (256, 19200) @ x_b^T (19200, 256)
+  proj   V (8, 32, 19200) = Wg (32, 256) @ x                            retinanet/Attention.py:24
+"""
+import os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch
+from test_gemm_gpu import run_gemm, DEV
+
+B, C_, N, d = 8, 256, 19200, 32
+C = C_
+g = torch.Generator().manual_seed(0)
+W = torch.randn(1, C, C, generator=g).to(DEV)
+Wg = torch.randn(1, d, C, generator=g).to(DEV)
+x = torch.randn(B, C, N, generator=g).to(DEV)
+dy = torch.randn(B, C, N, generator=g).to(DEV)
+out = torch.empty(B, C, N, device=DEV)
+outp = torch.empty(B, d, N, device=DEV)
+dW = torch.empty(C, C, device=DEV)
+
+
+def timeit(name, fn, flops, bytes_):
+    fn(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        fn()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    print(f"{name}: {ms:.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s  {bytes_ / ms / 1e6:.0f} GB/s (algorithmic)")
+
+
+eng = int(os.environ.get("ENGINE", "1"))
+timeit("conv ", lambda: run_gemm(eng, W, x, out, C, N, C, B, (C, 1, 0), (N, 1, C * N), (N, 1, C * N)),
+       2.0 * C * C * N * B, 2.0 * 4 * B * C * N)
+timeit("wgrad", lambda: run_gemm(eng, dy, x, dW, C, C, N, B, (N, 1, C * N), (1, N, C * N), (C, 1, 0), reduce_batch=1),
+       2.0 * C * C * N * B, 2.0 * 4 * B * C * N)
+timeit("proj ", lambda: run_gemm(eng, Wg, x, outp, d, N, C, B, (C, 1, 0), (N, 1, C * N), (N, 1, d * N)),
+       2.0 * d * C * N * B, 4.0 * B * (C + d) * N)
+
+import ctypes as C
+from frn_b200 import _lib
+lib = _lib.load()
+if hasattr(lib, "frn_debug_gemm_trace"):
+    names = ["ld cp.async wait", "ld bar", "ld wait empty", "ld convert", "mma wait acc_free", "mma wait full",
+             "mma issue", "epi wait acc_full", "epi store", "cvt A", "cvt B", "fence+arrive", "issue"]
+    buf = (C.c_ulonglong * 16)()
+    lib.frn_debug_gemm_trace(buf)          # clear
+    for nm, fn in (("conv", lambda: run_gemm(eng, W, x, out, C_, N, C_, B, (C_, 1, 0), (N, 1, C_ * N), (N, 1, C_ * N))),
+                   ("wgrad", lambda: run_gemm(eng, dy, x, dW, C_, C_, N, B, (N, 1, C_ * N), (1, N, C_ * N), (C_, 1, 0), reduce_batch=1))):
+        t0 = time.time(); fn(); dt = time.time() - t0
+        if lib.frn_debug_gemm_trace(buf):
+            print(nm, f"{dt * 1e3:.3f} ms;", ", ".join(f"{n}: {buf[i] / 1e3:.0f}k" for i, n in enumerate(names)))
