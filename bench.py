@@ -191,12 +191,27 @@ def run_ours(args):
     stage_a = [torch.empty_like(t, device=dev) for t in host_a]
     stage_e = [torch.empty_like(t, device=dev) for t in host_e]
 
+    copy_stream = torch.cuda.Stream(device=dev)
+    order = sorted(range(len(levels)), key=lambda k: host_a[k].numel())      # smallest level first
+
     def step_e2e():
+        """Host inputs -> H2D (pinned, on a copy stream, smallest level first so that the 315 MB of level 1
+        travel while levels 4-2 compute) -> fwd+bwd through the public modules -> allreduce -> D2H of the result."""
         bucket.zero()
-        for m, ha, he, sa, se, go in zip(mods, host_a, host_e, stage_a, stage_e, douts):
-            sa.copy_(ha, non_blocking=True); se.copy_(he, non_blocking=True)     # H2D from pinned memory
-            a = sa.detach().requires_grad_(True); e = se.detach().requires_grad_(True)
-            m(a, e).backward(go)
+        main = torch.cuda.current_stream()
+        copy_stream.wait_stream(main)                  # staging buffers are free again
+        ready = []
+        with torch.cuda.stream(copy_stream):
+            for k in order:
+                stage_a[k].copy_(host_a[k], non_blocking=True)
+                stage_e[k].copy_(host_e[k], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+                ready.append(ev)
+        for k, ev in zip(order, ready):
+            main.wait_event(ev)
+            a = stage_a[k].detach().requires_grad_(True); e = stage_e[k].detach().requires_grad_(True)
+            mods[k](a, e).backward(douts[k])
         bucket.allreduce(average=True)
         norm_host.copy_(torch.linalg.vector_norm(bucket.flat).reshape(1), non_blocking=True)   # D2H result
         torch.cuda.current_stream().synchronize()
@@ -229,19 +244,24 @@ def run_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    lib.frn_timing_enable(1)
-    for cls in range(5):
-        lib.frn_timing_read(cls, C.byref(C.c_double()), C.byref(C.c_long()))
     launches0 = lib.frn_launch_count()
     ms_total = timed(step_resident, args.steps)
     launches = lib.frn_launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- profiling pass (not the reported value): the same steps with the library's per-class CUDA-event
+    # hooks on; with the hooks on the two attention-backward kernels run back to back instead of overlapped,
+    # so that the dominant kernel's own launch duration is measured -------------------------------------
+    lib.frn_timing_enable(1)
+    for cls in range(5):
+        lib.frn_timing_read(cls, C.byref(C.c_double()), C.byref(C.c_long()))
+    ms_prof = timed(step_resident, args.steps)
     classes = {}
     for name, cls in (("attn_fwd", 0), ("attn_bwd", 1), ("gemm", 2), ("rows", 3), ("attn_dkv", 4)):
         ms, n = C.c_double(), C.c_long()
         lib.frn_timing_read(cls, C.byref(ms), C.byref(n))
         classes[name] = {"ms": ms.value, "launches": n.value}
     lib.frn_timing_enable(0)
-    clocks = sampler.stop() if rank == 0 else None
 
     # ---- timed region 2: end to end through the public modules, host inputs ------------
     for _ in range(2):
@@ -268,12 +288,12 @@ def run_ours(args):
     t_dkv = classes["attn_dkv"]["ms"] / 1e3 / args.steps
     if tc_attn and t_dkv > 0:
         kname, ach, share = ("attn_dkv_tc_kernel (tcgen05 attention backward, dK/dV half, levels 1-2)",
-                             fl_dkv / t_dkv / 1e12, classes["attn_dkv"]["ms"] / ms_total)
+                             fl_dkv / t_dkv / 1e12, classes["attn_dkv"]["ms"] / ms_prof)
         nl = max(classes["attn_dkv"]["launches"], 1)
         per_launch = {"flops_per_launch": fl_dkv * args.steps / nl, "ms_per_launch": classes["attn_dkv"]["ms"] / nl}
     else:
         kname, ach, share = ("attn_bwd_kernel (FFMA streaming-softmax attention backward, levels 1-2)",
-                             fl_bwd / t_bwd / 1e12 if t_bwd > 0 else 0.0, classes["attn_bwd"]["ms"] / ms_total)
+                             fl_bwd / t_bwd / 1e12 if t_bwd > 0 else 0.0, classes["attn_bwd"]["ms"] / ms_prof)
         per_launch = {}
     roofline = {"bound": "tensor", "kernel": kname,
                 "achieved": ach, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
@@ -286,6 +306,7 @@ def run_ours(args):
                 "attn_bwd_tflops": fl_bwd / t_bwd / 1e12 if t_bwd > 0 else 0.0,
                 "attn_fwd_tflops": fl_fwd / t_fwd / 1e12 if t_fwd > 0 else 0.0,
                 "class_ms_per_step": {k: v["ms"] / args.steps for k, v in classes.items()},
+                "profiling_pass_ms_per_step": ms_prof / args.steps,
                 "block_hbm_frac": HBM_BYTES_PER_SAMPLE * value / world / 1e9 / peaks["hbm_gbs"],
                 "block_tensor_frac": (FLOPS_FWD + FLOPS_BWD) * value / world / 1e12 / peaks["tf_sustained"]}
     roofline.update(per_launch)

@@ -21,6 +21,7 @@
 //   attn_dkv_tc_kernel   CTA = NKT x 128 keys (ping-pong), 32-query tiles: S^T, dP^T -> P^T, dS^T
 //                        -> dV, dK   (d = 64: one 32-channel half of dV / dK per CTA)
 // No atomics anywhere: the backward is deterministic.
+#include <mutex>
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -428,15 +429,18 @@ template <int DPAD, int NQ> struct DqCfg {
   static constexpr int kSub = DPAD / 32;
   static constexpr int kOperBytes = kSub * 128 * 128;          // one 128-row pos tile, hi or lo
   static constexpr int kResBytes = 4 * kOperBytes;             // Q hi, Q lo, dY hi, dY lo
-  static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile, hi or lo
-  static constexpr int kChanBytes = DPAD * 128;                // streamed chan block, hi or lo
+  // keys per streamed tile: 64 for d <= 32 (every tcgen05.mma costs >= ~45 cycles however small its N is, so
+  // the S / dP products are issued at N = 64), 32 for d = 64 (shared memory)
+  static constexpr int T = DPAD == 32 ? 64 : 32;
+  static constexpr int kPosBytes = kSub * T * 128;             // streamed pos tile, hi or lo
+  static constexpr int kChanBytes = (T / 32) * DPAD * 128;     // streamed chan blocks, hi or lo
   static constexpr int kStageBytes = 4 * kPosBytes + 2 * kChanBytes;   // K pos hi/lo, V pos hi/lo, K chan hi/lo
-  static constexpr int kStages = DPAD == 32 ? 3 : 2;
+  static constexpr int kStages = 2;
   static constexpr int kSmem = NQ * kResBytes + kStages * kStageBytes + 1024 + 256;
   static constexpr int kTmemCols = 256 * NQ;
   static constexpr int kThreads = (4 * NQ + 2) * 32;
   // TMEM columns of one query tile
-  static constexpr int kS = 0 /* S, then dS hi */, kSs = 32 /* dS lo */, kP = 64 /* dP */, kAcc = 128;
+  static constexpr int kS = 0 /* S, then dS hi */, kSs = T /* dS lo */, kP = 2 * T /* dP */, kAcc = 3 * T;
 };
 
 template <int DPAD, int NQ>
@@ -461,7 +465,8 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.y;
   const int nqt = NP / 128;                          // query tiles per sample
-  const int TK = (N + BT - 1) / BT;                  // key tiles
+  constexpr int T = Cfg::T;
+  const int TK = (N + T - 1) / T;                    // key tiles
   const int qt0 = blockIdx.x * NQ;
 
   if (tid == 0) {
@@ -500,13 +505,13 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
         mbar_expect_tx(&kv_full[stage], Cfg::kStageBytes);
 #pragma unroll
         for (int s = 0; s < Cfg::kSub; s++) {
-          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * BT) * 32;
-          bulk_g2s(st + s * BT * 128, Ki.pos_hi + o, BT * 128, &kv_full[stage]);
-          bulk_g2s(st + Cfg::kPosBytes + s * BT * 128, Ki.pos_lo + o, BT * 128, &kv_full[stage]);
-          bulk_g2s(st + 2 * Cfg::kPosBytes + s * BT * 128, Vi.pos_hi + o, BT * 128, &kv_full[stage]);
-          bulk_g2s(st + 3 * Cfg::kPosBytes + s * BT * 128, Vi.pos_lo + o, BT * 128, &kv_full[stage]);
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * T) * 32;
+          bulk_g2s(st + s * T * 128, Ki.pos_hi + o, T * 128, &kv_full[stage]);
+          bulk_g2s(st + Cfg::kPosBytes + s * T * 128, Ki.pos_lo + o, T * 128, &kv_full[stage]);
+          bulk_g2s(st + 2 * Cfg::kPosBytes + s * T * 128, Vi.pos_hi + o, T * 128, &kv_full[stage]);
+          bulk_g2s(st + 3 * Cfg::kPosBytes + s * T * 128, Vi.pos_lo + o, T * 128, &kv_full[stage]);
         }
-        const long oc = (((long)b * (NP / 32) + j) * DPAD) * 32;
+        const long oc = (((long)b * (NP / 32) + (long)j * (T / 32)) * DPAD) * 32;
         bulk_g2s(st + 4 * Cfg::kPosBytes, Ki.chan_hi + oc, Cfg::kChanBytes, &kv_full[stage]);
         bulk_g2s(st + 4 * Cfg::kPosBytes + Cfg::kChanBytes, Ki.chan_lo + oc, Cfg::kChanBytes, &kv_full[stage]);
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -515,7 +520,7 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
   } else if (warp == 4 * NQ) {
     // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
     {
-      constexpr uint32_t idesc_s = umma_idesc_tf32(128, BT);
+      constexpr uint32_t idesc_s = umma_idesc_tf32(128, T);
       constexpr uint32_t idesc_q = umma_idesc_tf32(128, DPAD);
       int nact = 0;
       for (int h = 0; h < NQ; h++)
@@ -535,8 +540,13 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
             if (elect_one()) {
               const uint32_t kc =
                   smem_u32(sStage + ((j - 1) % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
-              mma_corr_ts(tb + Cfg::kAcc, tb + Cfg::kS, tb + Cfg::kSs, kc, kc + Cfg::kChanBytes, idesc_q, true);
-              mma_main_ts(tb + Cfg::kAcc, tb + Cfg::kS, kc, idesc_q);
+#pragma unroll
+              for (int sb = 0; sb < T / 32; sb++)      // 32 keys per chan block
+                mma_corr_ts(tb + Cfg::kAcc, tb + Cfg::kS + 32 * sb, tb + Cfg::kSs + 32 * sb, kc + sb * DPAD * 128,
+                            kc + Cfg::kChanBytes + sb * DPAD * 128, idesc_q, sb == 0);
+#pragma unroll
+              for (int sb = 0; sb < T / 32; sb++)
+                mma_main_ts(tb + Cfg::kAcc, tb + Cfg::kS + 32 * sb, kc + sb * DPAD * 128, idesc_q);
               if (h == nact - 1) umma_commit(&kv_empty[(j - 1) % Cfg::kStages]);
             }
             __syncwarp();
@@ -546,19 +556,19 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
             const uint32_t st = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes);
 #pragma unroll
             for (int s = 0; s < Cfg::kSub; s++)
-              mma_corr_ss(tb + Cfg::kS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
-                          st + Cfg::kPosBytes + s * BT * 128, idesc_s, s == 0);
+              mma_corr_ss(tb + Cfg::kS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * T * 128,
+                          st + Cfg::kPosBytes + s * T * 128, idesc_s, s == 0);
 #pragma unroll
             for (int s = 0; s < Cfg::kSub; s++)
-              mma_main_ss(tb + Cfg::kS, r + s * 16384, st + s * BT * 128, idesc_s);
+              mma_main_ss(tb + Cfg::kS, r + s * 16384, st + s * T * 128, idesc_s);
 #pragma unroll
             for (int s = 0; s < Cfg::kSub; s++)
               mma_corr_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, r + 3 * Cfg::kOperBytes + s * 16384,
-                          st + 2 * Cfg::kPosBytes + s * BT * 128, st + 3 * Cfg::kPosBytes + s * BT * 128, idesc_s,
+                          st + 2 * Cfg::kPosBytes + s * T * 128, st + 3 * Cfg::kPosBytes + s * T * 128, idesc_s,
                           s == 0);
 #pragma unroll
             for (int s = 0; s < Cfg::kSub; s++)
-              mma_main_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128,
+              mma_main_ss(tb + Cfg::kP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * T * 128,
                           idesc_s);
             umma_commit(&sdp_full[h]);
           } else {
@@ -595,9 +605,9 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
         mbar_wait(&sdp_full[h], j & 1);
         tc_fence_after();
         if (j > 0) promote();
-        const int j0 = j * BT;
+        const int j0 = j * T;
 #pragma unroll
-        for (int c0 = 0; c0 < BT; c0 += 16) {
+        for (int c0 = 0; c0 < T; c0 += 16) {
           float p[16], hi[16], lo[16];
           {
             float a[16], g[16];
@@ -908,27 +918,60 @@ int launch_fwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   return FRN_OK;
 }
 
+// The dQ kernel and the dK/dV kernel are independent (same inputs, different outputs) and each leaves a
+// ragged last wave (600 CTAs on 148 SMs at DSEC level 1 = 4.05 waves), so the dQ kernel is forked onto a
+// per-device side stream and joined back with events: the two tails fill each other.  The side streams
+// are the only cached objects of this file (created once per device, never destroyed); with the
+// measurement hooks on, the kernels run back to back on the caller's stream so that their times stay separable.
+cudaStream_t side_stream() {
+  static std::mutex mu;
+  static cudaStream_t streams[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!streams[dev] && cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking) != cudaSuccess)
+    streams[dev] = nullptr;
+  return streams[dev];
+}
+
 template <int DPAD, int NT>
 int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
                   const SplitImage& V, const SplitImage& dY, const float* lse_pad, const float* delta_pad,
                   float* dQp, float* dKp, float* dVp) {
   const int NP = attn_tc_np(N);
+  using CfgK = DkvCfg<DPAD, NT>;
+  using CfgQ = DqCfg<DPAD, NT>;
+  auto kern_kv = attn_dkv_tc_kernel<DPAD, NT>;
+  auto kern_q = attn_dq_tc_kernel<DPAD, NT>;
+  FRN_TRY(set_smem(kern_kv, CfgK::kSmem));
+  FRN_TRY(set_smem(kern_q, CfgQ::kSmem));
+  const dim3 grid_kv(cdiv(NP / 128, NT), B, cdiv(d, 32)), grid_q(cdiv(NP / 128, NT), B);
   ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
-  {
-    using Cfg = DkvCfg<DPAD, NT>;
-    auto kern = attn_dkv_tc_kernel<DPAD, NT>;
-    FRN_TRY(set_smem(kern, Cfg::kSmem));
-    dim3 grid(cdiv(NP / 128, NT), B, cdiv(d, 32));
-    ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
-    kern<<<grid, Cfg::kThreads, Cfg::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+  cudaStream_t side = timing_enabled() ? nullptr : side_stream();
+  cudaEvent_t fork = nullptr, join = nullptr;
+  if (side && (cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) != cudaSuccess ||
+               cudaEventCreateWithFlags(&join, cudaEventDisableTiming) != cudaSuccess)) {
+    if (fork) cudaEventDestroy(fork);
+    side = nullptr;
+  }
+  if (side) {
+    cudaEventRecord(fork, st);
+    cudaStreamWaitEvent(side, fork, 0);
+    kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, side>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
     FRN_LAUNCH_CHECK();
+    cudaEventRecord(join, side);
   }
   {
-    using Cfg = DqCfg<DPAD, NT>;
-    auto kern = attn_dq_tc_kernel<DPAD, NT>;
-    FRN_TRY(set_smem(kern, Cfg::kSmem));
-    dim3 grid(cdiv(NP / 128, NT), B);
-    kern<<<grid, Cfg::kThreads, Cfg::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+    ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
+    kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+    FRN_LAUNCH_CHECK();
+  }
+  if (side) {
+    cudaStreamWaitEvent(st, join, 0);
+    cudaEventDestroy(fork);        // destruction is deferred until the recorded work has completed
+    cudaEventDestroy(join);
+  } else {
+    kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
     FRN_LAUNCH_CHECK();
   }
   return FRN_OK;

@@ -29,6 +29,8 @@ struct ScopedTimer {
   ~ScopedTimer();
 };
 
+bool timing_enabled();    // measurement hooks on (include/frn_b200.h)
+
 static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 

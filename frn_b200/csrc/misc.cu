@@ -220,6 +220,8 @@ std::mutex g_timing_mu;
 std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events[FRN_TIME_CLASSES];
 }  // namespace
 
+bool timing_enabled() { return g_timing_on.load(std::memory_order_relaxed) != 0; }
+
 ScopedTimer::ScopedTimer(cudaStream_t s, int c) : st(s), cls(c), e0(nullptr), on(false) {
   if (!g_timing_on.load(std::memory_order_relaxed)) return;
   if (cudaEventCreate(&e0) != cudaSuccess) return;

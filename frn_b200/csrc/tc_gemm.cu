@@ -47,12 +47,14 @@ __device__ unsigned long long g_trace[16];
 
 template <int BN> struct TcCfg {
   static constexpr int kStages = BN == 128 ? 2 : 3;        // split (hi / lo) operand stages feeding the MMAs
-  static constexpr int kRaw = 3;                           // raw fp32 stages in flight (cp.async)
+  static constexpr int kRaw = BN == 32 ? 3 : 2;            // raw fp32 stages (cp.async ring)
+  static constexpr int kEpiBytes = 8 * 32 * 32 * 4;        // one 32 x 32 transposition tile per epilogue warp
   static constexpr int kABytes = TBM * TBK * 4;            // one of hi / lo
   static constexpr int kBBytes = BN * TBK * 4;
   static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
   static constexpr int kRawBytes = kABytes + kBBytes;
-  static constexpr int kSmem = kStages * kStageBytes + kRaw * kRawBytes + 1024 /*align*/ + 1024 /*barriers, scratch*/;
+  static constexpr int kSmem = kStages * kStageBytes + kRaw * kRawBytes + kEpiBytes + 1024 /*align*/ +
+                               1024 /*barriers, scratch*/;
   static constexpr int kTmemCols = 4 * BN;               // 2 buffers x (hi*hi | lo*hi + hi*lo + lo*lo)
 };
 
@@ -381,6 +383,7 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
         const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
         const float bm = (!partial && p.bias_m) ? __ldg(p.bias_m + boff + gm) : 0.f;
         const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+        if (!vec) {                             // n-contiguous aligned outputs take the coalesced path below
 #pragma unroll
         for (int c0 = 0; c0 < HC; c0 += 4) {
           float o[4];
@@ -403,6 +406,71 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
                 float* d1 = dst + (long)j * sCn;
                 *d1 = o[j] + (acc_out ? *d1 : 0.f);
               }
+          }
+        }
+        }
+      }
+      if (EPI == GEMM_EPI_STORE) {
+        // Coalesced path for n-contiguous outputs: thread = row is the TMEM read layout, but a warp-wide store
+        // of 16 bytes per ROW touches 32 different lines (measured: the epilogue, not the MMAs, bounded every
+        // K = 32 GEMM of the backward pass).  Each warp transposes 32 x 32 blocks through a swizzled shared
+        // tile and writes whole 128-byte row segments, four rows per instruction.
+        float* Cb; long sCm, sCn;
+        if (partial) { Cb = aux + (long)z * p.M * p.N; sCm = p.N; sCn = 1; }
+        else { Cb = p.C + (p.reduce_batch ? 0 : (long)z * p.sCb); sCm = p.sCm; sCn = p.sCn; }
+        const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+        if (vec) {
+          constexpr int W = HC < 32 ? HC : 32;      // block width (columns)
+          constexpr int CPR = W / 4;                // 16-byte chunks per row
+          constexpr int RPI = 32 / CPR;             // rows per store instruction
+          float* tile = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 1024 +
+                                                 Cfg::kRaw * Cfg::kRawBytes) + e * 1024;
+          const bool acc_out = !partial && p.accumulate;
+          const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
+          const float bm = (!partial && p.bias_m && gm < p.M) ? __ldg(p.bias_m + boff + gm) : 0.f;
+          const int rsub = lane / CPR, csub = lane % CPR;
+#pragma unroll
+          for (int cb = 0; cb < HC; cb += W) {
+#pragma unroll
+            for (int c = 0; c < CPR; c++) {         // thread = row `lane` of the warp's 32
+              float4 q = make_float4(fmaf(p.alpha, acc[cb + 4 * c], bm), fmaf(p.alpha, acc[cb + 4 * c + 1], bm),
+                                     fmaf(p.alpha, acc[cb + 4 * c + 2], bm), fmaf(p.alpha, acc[cb + 4 * c + 3], bm));
+              *reinterpret_cast<float4*>(tile + lane * 32 + ((c ^ (lane & 7)) << 2)) = q;
+            }
+            __syncwarp();
+            const int gn = nb + cb + 4 * csub;
+            float4 bn4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (!partial && p.bias_n && gn + 3 < p.N) bn4 = __ldg(reinterpret_cast<const float4*>(p.bias_n + boff + gn));
+            float4 prev[32 / RPI];                  // C += : all reads of a block in flight before the first use
+            if (acc_out) {
+#pragma unroll
+              for (int it = 0; it < 32 / RPI; it++) {
+                const int grow = tl.m0 + quad * 32 + it * RPI + rsub;
+                prev[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (grow < p.M && gn + 3 < p.N) prev[it] = *reinterpret_cast<const float4*>(Cb + (long)grow * sCm + gn);
+              }
+            }
+#pragma unroll
+            for (int it = 0; it < 32 / RPI; it++) {
+              const int rr = it * RPI + rsub;
+              const int grow = tl.m0 + quad * 32 + rr;
+              float4 q = *reinterpret_cast<const float4*>(tile + rr * 32 + ((csub ^ (rr & 7)) << 2));
+              if (grow < p.M && gn < p.N) {
+                float* dst = Cb + (long)grow * sCm + gn;
+                if (gn + 3 < p.N) {
+                  q.x += bn4.x; q.y += bn4.y; q.z += bn4.z; q.w += bn4.w;
+                  if (acc_out) { q.x += prev[it].x; q.y += prev[it].y; q.z += prev[it].z; q.w += prev[it].w; }
+                  *reinterpret_cast<float4*>(dst) = q;
+                } else {
+                  const float o[4] = {q.x, q.y, q.z, q.w};
+                  for (int j = 0; j < 4 && gn + j < p.N; j++) {
+                    const float bn = (!partial && p.bias_n) ? __ldg(p.bias_n + boff + gn + j) : 0.f;
+                    dst[j] = o[j] + bn + (acc_out ? dst[j] : 0.f);
+                  }
+                }
+              }
+            }
+            __syncwarp();
           }
         }
       }

@@ -40,6 +40,18 @@ timeit("wgrad", lambda: run_gemm(eng, dy, x, dW, C, C, N, B, (N, 1, C * N), (1, 
 timeit("proj ", lambda: run_gemm(eng, Wg, x, outp, d, N, C, B, (C, 1, 0), (N, 1, C * N), (N, 1, d * N)),
        2.0 * d * C * N * B, 4.0 * B * (C + d) * N)
 
+# K = d = 32 shapes of the backward pass (HBM-bound by arithmetic: one (B, C, N) tensor written or updated)
+Wb = torch.randn(B, C_, d, generator=g).to(DEV)            # per-sample scaled W (style path)
+Yc = torch.randn(B, d, N, generator=g).to(DEV)
+dVp = torch.randn(B, N, d, generator=g).to(DEV)            # position-major projection gradient
+timeit("dT   ", lambda: run_gemm(eng, Wb, Yc, out, C_, N, d, B, (d, 1, C_ * d), (N, 1, d * N), (N, 1, C_ * N)),
+       2.0 * C_ * d * N * B, 4.0 * B * (C_ + d) * N)
+timeit("dgrad", lambda: run_gemm(eng, Wg, dVp, out, C_, N, d, B, (1, C_, 0), (1, d, N * d), (N, 1, C_ * N), accumulate=1),
+       2.0 * C_ * d * N * B, 4.0 * B * (2 * C_ + d) * N)
+timeit("pwgrd", lambda: run_gemm(eng, dVp, x, outp[0], d, C_, N, B, (1, d, N * d), (1, N, C_ * N), (C_, 1, 0), reduce_batch=1),
+       2.0 * C_ * d * N * B, 4.0 * B * (C_ + d) * N)
+
+# role cycle counters (library built with -DFRN_GEMM_TRACE only)
 import ctypes as C
 from frn_b200 import _lib
 lib = _lib.load()
@@ -47,9 +59,11 @@ if hasattr(lib, "frn_debug_gemm_trace"):
     names = ["ld cp.async wait", "ld bar", "ld wait empty", "ld convert", "mma wait acc_free", "mma wait full",
              "mma issue", "epi wait acc_full", "epi store", "cvt A", "cvt B", "fence+arrive", "issue"]
     buf = (C.c_ulonglong * 16)()
-    lib.frn_debug_gemm_trace(buf)          # clear
-    for nm, fn in (("conv", lambda: run_gemm(eng, W, x, out, C_, N, C_, B, (C_, 1, 0), (N, 1, C_ * N), (N, 1, C_ * N))),
-                   ("wgrad", lambda: run_gemm(eng, dy, x, dW, C_, C_, N, B, (N, 1, C_ * N), (1, N, C_ * N), (C_, 1, 0), reduce_batch=1))):
-        t0 = time.time(); fn(); dt = time.time() - t0
-        if lib.frn_debug_gemm_trace(buf):
+    if lib.frn_debug_gemm_trace(buf):
+        for nm, fn in (("conv", lambda: run_gemm(eng, W, x, out, C_, N, C_, B, (C_, 1, 0), (N, 1, C_ * N), (N, 1, C_ * N))),
+                       ("dT", lambda: run_gemm(eng, Wb, Yc, out, C_, N, d, B, (d, 1, C_ * d), (N, 1, d * N), (N, 1, C_ * N))),
+                       ("dgrad", lambda: run_gemm(eng, Wg, dVp, out, C_, N, d, B, (1, C_, 0), (1, d, N * d), (N, 1, C_ * N), accumulate=1))):
+            lib.frn_debug_gemm_trace(buf)
+            t0 = time.time(); fn(); dt = time.time() - t0
+            lib.frn_debug_gemm_trace(buf)
             print(nm, f"{dt * 1e3:.3f} ms;", ", ".join(f"{n}: {buf[i] / 1e3:.0f}k" for i, n in enumerate(names)))
