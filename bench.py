@@ -55,6 +55,23 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
+    capture (profiles/r1_b_attn_ncu_full.txt: B = 8, DSEC level 1, the shape the roofline line is quoted on)."""
+    path = os.path.join(ROOT, "profiles", "r1_b_attn_ncu_full.txt")
+    try:
+        total, on, unit = 0.0, False, {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+        for line in open(path):
+            if line.startswith("=="):
+                on = kernel in line
+            elif on and ("dram__bytes_read.sum " in line or "dram__bytes_write.sum " in line):
+                parts = line.split()
+                total += float(parts[1]) * unit.get(parts[2], 1.0)
+        return (total if total > 0 else None), "profiles/r1_b_attn_ncu_full.txt (B=8, DSEC level 1, one launch)"
+    except OSError:
+        return None, "no ncu capture found"
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -310,6 +327,8 @@ def run_ours(args):
                 "block_hbm_frac": HBM_BYTES_PER_SAMPLE * value / world / 1e9 / peaks["hbm_gbs"],
                 "block_tensor_frac": (FLOPS_FWD + FLOPS_BWD) * value / world / 1e12 / peaks["tf_sustained"]}
     roofline.update(per_launch)
+    if tc_attn:
+        roofline["traffic"], roofline["traffic_source"] = ncu_traffic("attn_dkv_tc_kernel")
     cores = os.cpu_count() or 1
     cpu_s = cpu_port_step(levels, 1, cores) if not args.no_cpu else None
     if cpu_s is not None:
