@@ -30,6 +30,14 @@ struct ScopedTimer {
 };
 
 bool timing_enabled();    // measurement hooks on (include/frn_b200.h)
+long shape_log_dump(char* buf, long cap);
+
+// Debug: per-shape GEMM times (FRN_GEMM_LOG=1 and the measurement hooks on); read with frn_debug_gemm_log.
+struct ShapeTimer {
+  cudaStream_t st; cudaEvent_t e0; bool on; char key[96];
+  ShapeTimer(cudaStream_t s, const char* engine, int M, int N, int K, int batch, int flags);
+  ~ShapeTimer();
+};
 
 static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }

@@ -42,16 +42,10 @@ int run_gemm(Ctx& c, const GemmDesc& d) {
   }
   return gemm(c.st, d, c.splitk, c.splitk_cap);
 }
-// The materialised attention of levels 3-4 (d > 64, 1.5 % of the block's FLOPs) stays on the FFMA
-// GEMM: its logits are exponentiated and its dQ / dK sums cancel heavily, so the tensor core's
-// truncation bias (tc_gemm.cu) shows up amplified in the theta / phi gradients.
-int run_gemm_exact(Ctx& c, const GemmDesc& d) {
-  if (c.dry) {
-    c.splitk_need = std::max(c.splitk_need, gemm_workspace_bytes(d));
-    return FRN_OK;
-  }
-  return ffma_gemm(c.st, d, c.splitk, c.splitk_cap);
-}
+// The materialised attention of levels 3-4 (d > 64, 1.5 % of the block's FLOPs): its logits are
+// exponentiated and its dQ sums cancel heavily, so the keys are centred over positions first (as in the
+// streaming engine); with that the split-TF32 GEMM holds the 1e-5 gate and no exact-FFMA detour is needed.
+int run_gemm_exact(Ctx& c, const GemmDesc& d) { return run_gemm(c, d); }
 
 GemmDesc desc(const float* A, const float* B, float* C, int M, int N, int K, int batch) {
   GemmDesc d{};
@@ -169,10 +163,16 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
   }
   int ch = chunk_for_scores(B, N, 1);
   float* S = c.ws.take<float>((size_t)ch * N * N);
+  // keys centred over positions, as in the streaming engine: softmax_j is unchanged by it
+  float* Kz = c.ws.take<float>((size_t)B * d * N);
+  float* kbar = c.ws.take<float>((size_t)B * d);
+  float* ksd = c.ws.take<float>((size_t)B * d);
+  RUN(c, row_mean_std(c.st, (long)B * d, N, s.Kc, kEps, kbar, ksd));
+  RUN(c, center_rows(c.st, (long)B * d, N, s.Kc, kbar, Kz));
   for (int b0 = 0; b0 < B; b0 += ch) {
     int nb = std::min(ch, B - b0);
     long o = (long)b0 * d * N;
-    GemmDesc g = desc(s.Qc + o, s.Kc + o, S, N, N, d, nb);      // S[i][j] = sum_c Q[c][i] K[c][j]
+    GemmDesc g = desc(s.Qc + o, Kz + o, S, N, N, d, nb);        // S[i][j] = sum_c Q[c][i] K[c][j]
     g.sAm = 1; g.sAk = N; g.sAb = (long)d * N;
     g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
     g.sCm = N; g.sCn = 1; g.sCb = (long)N * N;
@@ -267,10 +267,15 @@ int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* d
   float* P = c.ws.take<float>((size_t)ch * N * N);
   float* dS = c.ws.take<float>((size_t)ch * N * N);
   const long dn = (long)d * N, nn = (long)N * N;
+  float* Kz = c.ws.take<float>((size_t)B * d * N);                  // centred keys (see attention_fwd)
+  float* kbar = c.ws.take<float>((size_t)B * d);
+  float* ksd = c.ws.take<float>((size_t)B * d);
+  RUN(c, row_mean_std(c.st, (long)B * d, N, s.Kc, kEps, kbar, ksd));
+  RUN(c, center_rows(c.st, (long)B * d, N, s.Kc, kbar, Kz));
   for (int b0 = 0; b0 < B; b0 += ch) {
     int nb = std::min(ch, B - b0);
     long o = (long)b0 * dn;
-    GemmDesc g = desc(s.Qc + o, s.Kc + o, P, N, N, d, nb);          // S = Q K
+    GemmDesc g = desc(s.Qc + o, Kz + o, P, N, N, d, nb);            // S = Q K
     g.sAm = 1; g.sAk = N; g.sAb = dn;
     g.sBk = N; g.sBn = 1; g.sBb = dn;
     g.sCm = N; g.sCn = 1; g.sCb = nn;
@@ -287,7 +292,7 @@ int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* d
     p.sCm = N; p.sCn = 1; p.sCb = nn;
     FRN_TRY(run_gemm_exact(c, p));
     RUN(c, ds_from_p(c.st, (long)nb * N, N, P, dS, delta + (long)b0 * N));  // dS = P (dP - delta)
-    GemmDesc q = desc(dS, s.Kc + o, dQp + o, N, d, N, nb);          // dQ[i][k] = sum_j dS[i][j] K[k][j]
+    GemmDesc q = desc(dS, Kz + o, dQp + o, N, d, N, nb);            // dQ[i][k] = sum_j dS[i][j] K[k][j]  (rows of dS sum to 0)
     q.sAm = N; q.sAk = 1; q.sAb = nn;
     q.sBk = 1; q.sBn = N; q.sBb = dn;
     q.sCm = d; q.sCn = 1; q.sCb = dn;

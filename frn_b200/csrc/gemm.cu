@@ -284,6 +284,8 @@ int ffma_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
   if ((d.sAm != 1 && d.sAk != 1) || (d.sBn != 1 && d.sBk != 1)) return FRN_ERR_UNSUPPORTED;
   Plan pl = make_plan(d);
   ScopedTimer tm(st, FRN_TIME_GEMM);
+  ShapeTimer sh(st, "ffma", d.M, d.N, d.K, d.batch,
+                (d.reduce_batch ? 1 : 0) | (d.accumulate ? 2 : 0) | (d.sAk == 1 ? 4 : 0) | (d.sBn == 1 ? 8 : 0));
   if (d.reduce_batch && pl.nsplit > 1) {
     size_t need = (size_t)pl.nsplit * d.M * d.N * sizeof(float);
     if (!ws || ws_bytes < need) return FRN_ERR_WORKSPACE;

@@ -1,7 +1,12 @@
 // Small glue kernels: per-(sample, channel) coefficient math, bias-gradient
 // row sums, transposes, and the row softmax used by the materialised
 // attention path for d > 64 (retinanet/Attention.py:30).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
 #include <mutex>
+#include <string>
 #include <utility>
 #include <vector>
 #include "common.cuh"
@@ -237,6 +242,61 @@ ScopedTimer::~ScopedTimer() {
   g_events[cls].emplace_back(e0, e1);
 }
 
+namespace {
+struct ShapeRec { std::string key; cudaEvent_t e0, e1; };
+std::vector<ShapeRec> g_shape_log;
+int g_shape_on = -1;
+}  // namespace
+
+ShapeTimer::ShapeTimer(cudaStream_t s, const char* engine, int M, int N, int K, int batch, int flags)
+    : st(s), e0(nullptr), on(false) {
+  if (!g_timing_on.load(std::memory_order_relaxed)) return;
+  if (g_shape_on < 0) g_shape_on = getenv("FRN_GEMM_LOG") ? 1 : 0;
+  if (!g_shape_on) return;
+  snprintf(key, sizeof key, "%s M=%d N=%d K=%d b=%d f=%d", engine, M, N, K, batch, flags);
+  if (cudaEventCreate(&e0) != cudaSuccess) return;
+  cudaEventRecord(e0, st);
+  on = true;
+}
+ShapeTimer::~ShapeTimer() {
+  if (!on) return;
+  cudaEvent_t e1;
+  if (cudaEventCreate(&e1) != cudaSuccess) { cudaEventDestroy(e0); return; }
+  cudaEventRecord(e1, st);
+  std::lock_guard<std::mutex> lk(g_timing_mu);
+  g_shape_log.push_back({key, e0, e1});
+}
+
+long shape_log_dump(char* buf, long cap) {
+  std::vector<ShapeRec> ev;
+  {
+    std::lock_guard<std::mutex> lk(g_timing_mu);
+    ev.swap(g_shape_log);
+  }
+  std::map<std::string, std::pair<long, double>> agg;
+  for (auto& r : ev) {
+    float t = 0.f;
+    cudaEventSynchronize(r.e1);
+    cudaEventElapsedTime(&t, r.e0, r.e1);
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+    auto& a = agg[r.key];
+    a.first += 1; a.second += t;
+  }
+  std::string out;
+  char line[160];
+  for (auto& kv : agg) {
+    snprintf(line, sizeof line, "%s | %ld | %.4f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    out += line;
+  }
+  if (buf && cap > 0) {
+    long n = (long)out.size() < cap - 1 ? (long)out.size() : cap - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+  }
+  return (long)out.size();
+}
+
 int style_coeffs(cudaStream_t st, long rows, int N, const float* g1, const float* g2, const float* sd_t,
                  float* alpha, float* beta) {
   style_coeffs_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(rows, N, g1, g2, sd_t, alpha, beta);
@@ -351,6 +411,7 @@ int ds_from_p(cudaStream_t st, long rows, int N, const float* P, float* dP, cons
 #pragma GCC visibility push(default)
 extern "C" {
 void frn_timing_enable(int on) { frn::g_timing_on.store(on ? 1 : 0); }
+long frn_debug_gemm_log(char* buf, long cap) { return frn::shape_log_dump(buf, cap); }
 int frn_timing_read(int cls, double* ms, long* launches) {
   if (cls < 0 || cls >= FRN_TIME_CLASSES || !ms || !launches) return FRN_ERR_BAD_SHAPE;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;

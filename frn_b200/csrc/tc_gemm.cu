@@ -568,6 +568,8 @@ int tc_gemm(cudaStream_t st, const GemmDesc& in, void* ws, size_t ws_bytes) {
   if ((in.sAm != 1 && in.sAk != 1) || (in.sBn != 1 && in.sBk != 1)) return FRN_ERR_UNSUPPORTED;
   TcPlan pl = tc_plan(in, true);
   ScopedTimer tm(st, FRN_TIME_GEMM);
+  ShapeTimer sh(st, "tc", in.M, in.N, in.K, in.batch,
+                (in.reduce_batch ? 1 : 0) | (in.accumulate ? 2 : 0) | (in.sAk == 1 ? 4 : 0) | (in.sBn == 1 ? 8 : 0));
   if (in.reduce_batch && pl.nsplit > 1) {
     size_t need = (size_t)pl.nsplit * in.M * in.N * sizeof(float);
     if (!ws || ws_bytes < need) return FRN_ERR_WORKSPACE;
@@ -589,6 +591,7 @@ int tc_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
   TcPlan pl = tc_plan(d, false);
   pl.bn = 128;                     // gemm_rowsumsq_parts(N) == cdiv(N, 128) column tiles
   ScopedTimer tm(st, FRN_TIME_GEMM);
+  ShapeTimer sh(st, "tc-rowsumsq", d.M, d.N, d.K, d.batch, 0);
   return tc_launch_bn<128, GEMM_EPI_ROWSUMSQ>(st, pl, out_partial);
 }
 
