@@ -162,6 +162,22 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
   lo = x - hi;
 }
 
+// explicit shared-space accesses by 32-bit address (a generic pointer whose offset is only known at run time
+// compiles to generic LD / ST, which take the slower L1TEX path)
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float lds32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, float x, float y, float z, float w) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+
 // float offset of 16-byte chunk `chunk` (0..7) of row `row` inside a SWIZZLE_128B tile of 128-byte rows
 __device__ __forceinline__ int sw128_chunk_offset(int row, int chunk) {
   return row * 32 + ((chunk ^ (row & 7)) << 2);

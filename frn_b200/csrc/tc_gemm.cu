@@ -59,11 +59,11 @@ template <int BN> struct TcCfg {
 };
 
 // ---- cp.async (LDGSTS) with zero fill: copies src_bytes (<= 16 or 4) and zero-fills the rest ----
-__device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async4(void* dst, const void* src, int src_bytes) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() {
@@ -74,82 +74,87 @@ template <int N> __device__ __forceinline__ void cp_async_wait() {
 // without index arithmetic (the generic-stride address math cost ~65 instructions per 16-byte chunk when it
 // lived inside the loop and made the staging warps, not the tensor pipe, the bottleneck).
 // Raw layout: k contiguous ([r][32]) when ks == 1 (KFAST), else r contiguous ([k][ROWS]).  Chunk = 4
-// consecutive elements along the unit-stride axis; thread t owns chunks t, t + 256, ...
+// consecutive elements along the unit-stride axis; thread t owns chunks t, t + 256, ...: everything about
+// chunk i is LINEAR in i (outer index, global offset, swizzled destination), so the plan is a handful of
+// registers (the first version kept four arrays per operand and spilled them into the stage loop).
 template <int ROWS> struct OperandPlan {
   static constexpr int CH = ROWS * 8 / kLoaders;
-  long goff[CH];        // global element offset of the chunk from the tile origin
-  int outer[CH];        // index along the strided axis (row if KFAST else k)
-  int inner[CH];        // first index along the unit-stride axis (k if KFAST else row)
-  int dst[CH];          // float offset of the (row, 4 k) chunk in the swizzled hi / lo tiles
+  static constexpr int IPO = ROWS / 4;      // chunks per outer index when the rows are contiguous
+  long goff0, gstep;    // global element offset of chunk 0 from the tile origin; step per chunk
+  int outer0, ostep;    // index along the strided axis (row if KFAST else k) of chunk 0; step per chunk
+  int inner;            // first index along the unit-stride axis (k if KFAST else row), same for all chunks
+  uint32_t dst0;        // KFAST: byte offset of chunk 0 in the swizzled hi / lo tiles (+ 32 rows per chunk)
   bool kfast;
   __device__ __forceinline__ void init(long rs, long ks, int t) {
     kfast = (ks == 1);
     const long os = kfast ? rs : ks;
-#pragma unroll
-    for (int i = 0; i < CH; i++) {
-      const int idx = t + i * kLoaders;
-      if (kfast) { inner[i] = (idx & 7) * 4; outer[i] = idx >> 3; dst[i] = sw128_chunk_offset(outer[i], idx & 7); }
-      else {
-        inner[i] = (idx % (ROWS / 4)) * 4; outer[i] = idx / (ROWS / 4);
-        dst[i] = 0;   // conversion of this layout re-maps threads, see convert_tile
-      }
-      goff[i] = (long)outer[i] * os + inner[i];
-    }
+    if (kfast) { inner = (t & 7) * 4; outer0 = t >> 3; ostep = kLoaders / 8; }
+    else { inner = (t % IPO) * 4; outer0 = t / IPO; ostep = kLoaders / IPO; }
+    dst0 = (uint32_t)sw128_chunk_offset(t >> 3, t & 7) * 4u;
+    goff0 = (long)outer0 * os + inner;
+    gstep = (long)ostep * os;
   }
 };
 
 template <int ROWS>
-__device__ __forceinline__ void issue_raw(float* __restrict__ raw, const float* __restrict__ g,
-                                          const OperandPlan<ROWS>& pl, long os, int rows, int kvalid, int t) {
+__device__ __forceinline__ void issue_raw(uint32_t raw, const float* __restrict__ g, const OperandPlan<ROWS>& pl,
+                                          long os, int rows, int kvalid, int t) {
   constexpr int CH = OperandPlan<ROWS>::CH;
   const bool vec = ((os & 3) == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0);
-  const int n_in = pl.kfast ? kvalid : rows, n_out = pl.kfast ? rows : kvalid;
   const bool interior = rows >= ROWS && kvalid >= TBK;
+  const float* src = g + pl.goff0;
+  uint32_t dst = raw + (uint32_t)t * 16u;
   if (interior && vec) {
 #pragma unroll
-    for (int i = 0; i < CH; i++) cp_async16(raw + (t + i * kLoaders) * 4, g + pl.goff[i], 16);
+    for (int i = 0; i < CH; i++, src += pl.gstep, dst += kLoaders * 16) cp_async16(dst, src, 16);
     return;
   }
+  const int n_in = pl.kfast ? kvalid : rows, n_out = pl.kfast ? rows : kvalid;
+  int valid0 = n_in - pl.inner;
+  valid0 = valid0 < 0 ? 0 : (valid0 > 4 ? 4 : valid0);
 #pragma unroll
-  for (int i = 0; i < CH; i++) {
-    float* dst = raw + (t + i * kLoaders) * 4;
-    const float* src = g + pl.goff[i];
-    int valid = pl.outer[i] < n_out ? n_in - pl.inner[i] : 0;
-    valid = valid < 0 ? 0 : (valid > 4 ? 4 : valid);
+  for (int i = 0; i < CH; i++, src += pl.gstep, dst += kLoaders * 16) {
+    const int valid = (pl.outer0 + i * pl.ostep) < n_out ? valid0 : 0;
     if (vec) {
       cp_async16(dst, valid ? src : g, valid * 4);
     } else {
 #pragma unroll
-      for (int q = 0; q < 4; q++) cp_async4(dst + q, q < valid ? src + q : g, q < valid ? 4 : 0);
+      for (int q = 0; q < 4; q++) cp_async4(dst + q * 4, q < valid ? src + q : g, q < valid ? 4 : 0);
     }
   }
 }
 
-// raw tile -> tf32 hi / lo split -> SWIZZLE_128B K-major tiles
+// raw tile -> tf32 hi / lo split -> SWIZZLE_128B K-major tiles (all by 32-bit shared addresses)
 template <int ROWS, bool KFAST>
-__device__ __forceinline__ void convert_tile(float* __restrict__ hi, float* __restrict__ lo,
-                                             const float* __restrict__ raw, const OperandPlan<ROWS>& pl, int t) {
+__device__ __forceinline__ void convert_tile(uint32_t hi, uint32_t lo, uint32_t raw, const OperandPlan<ROWS>& pl,
+                                             int t) {
   constexpr int CH = OperandPlan<ROWS>::CH;
+  float v[CH][4];
+  uint32_t o[CH];
+  if (KFAST) {
+#pragma unroll
+    for (int i = 0; i < CH; i++) {             // all loads of the tile first, then the arithmetic
+      const float4 x = lds128(raw + (uint32_t)(t + i * kLoaders) * 16u);
+      v[i][0] = x.x; v[i][1] = x.y; v[i][2] = x.z; v[i][3] = x.w;
+      o[i] = pl.dst0 + (uint32_t)i * (kLoaders / 8) * 128u;      // + 32 rows of 128 bytes
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < CH; i++) {
+      const int idx = t + i * kLoaders;
+      const int r = idx % ROWS, c = idx / ROWS;            // ROWS is a power of two: shifts and masks
+#pragma unroll
+      for (int q = 0; q < 4; q++) v[i][q] = lds32(raw + (uint32_t)((c * 4 + q) * ROWS + r) * 4u);
+      o[i] = (uint32_t)sw128_chunk_offset(r, c) * 4u;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < CH; i++) {
-    float v[4];
-    int o;
-    if (KFAST) {
-      const float4 x = *reinterpret_cast<const float4*>(raw + (t + i * kLoaders) * 4);
-      v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
-      o = pl.dst[i];
-    } else {
-      const int idx = t + i * kLoaders;
-      const int r = idx % ROWS, c = idx / ROWS;          // ROWS is a power of two: shifts and masks
-#pragma unroll
-      for (int q = 0; q < 4; q++) v[q] = raw[(c * 4 + q) * ROWS + r];
-      o = sw128_chunk_offset(r, c);
-    }
     float h[4], l[4];
 #pragma unroll
-    for (int q = 0; q < 4; q++) split_tf32(v[q], h[q], l[q]);
-    *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+    for (int q = 0; q < 4; q++) split_tf32(v[i][q], h[q], l[q]);
+    sts128(hi + o[i], h[0], h[1], h[2], h[3]);
+    sts128(lo + o[i], l[0], l[1], l[2], l[3]);
   }
 }
 
@@ -177,8 +182,8 @@ __device__ __forceinline__ TcTile tc_tile(const GemmDesc& p, int id, int gx, int
 // Persistent: gridDim.x CTAs (one per SM) walk the gx*gy*gz output tiles; the shared-memory stage ring
 // and the two TMEM accumulator buffers keep running across tiles, so the staging of tile i+1 and its
 // first MMAs overlap the drain / global stores of tile i.
-template <int BN, int EPI>
-__global__ void __launch_bounds__(kTcThreads, 1)
+template <int BN, int EPI, bool ACC>      // ACC: C += (a separate instantiation keeps the read-modify-write
+__global__ void __launch_bounds__(kTcThreads, 1)    // registers out of the plain-store kernels)
 tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_split, int nsplit, int gx, int gy,
                int gz) {
   using Cfg = TcCfg<BN>;
@@ -208,7 +213,8 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
 
   if (warp < kMmaWarp) {
     // ===== operand staging: cp.async raw tiles kRaw - 1 stages ahead, then split into the MMA stage ring =====
-    uint8_t* raw_base = smem + Cfg::kStages * Cfg::kStageBytes + 1024;
+    const uint32_t raw_base = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes + 1024);
+    const uint32_t stage_base = smem_u32(smem);
     OperandPlan<TBM> planA;
     OperandPlan<BN> planB;
     planA.init(p.sAm, p.sAk, tid);
@@ -227,8 +233,8 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       const int t = tl.t_begin + c.i;
       const int b = tl.b_fixed >= 0 ? tl.b_fixed : t / ktiles;
       const int k0 = (tl.b_fixed >= 0 ? t : t % ktiles) * TBK;
-      float* rA = reinterpret_cast<float*>(raw_base + (it % Cfg::kRaw) * Cfg::kRawBytes);
-      float* rB = rA + TBM * TBK;
+      const uint32_t rA = raw_base + (uint32_t)(it % Cfg::kRaw) * Cfg::kRawBytes;
+      const uint32_t rB = rA + Cfg::kABytes;
       issue_raw<TBM>(rA, p.A + (long)b * p.sAb + (long)tl.m0 * p.sAm + (long)k0 * p.sAk, planA, osA,
                      p.M - tl.m0, p.K - k0, tid);
       issue_raw<BN>(rB, p.B + (long)b * p.sBb + (long)tl.n0 * p.sBn + (long)k0 * p.sBk, planB, osB,
@@ -260,12 +266,12 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       mbar_wait(&empty[stage], phase ^ 1);
       TRACE_ADD(2); }
       TRACE_T0();
-      const float* rA = reinterpret_cast<const float*>(raw_base + (it % Cfg::kRaw) * Cfg::kRawBytes);
-      const float* rB = rA + TBM * TBK;
-      float* sA = reinterpret_cast<float*>(smem + stage * Cfg::kStageBytes);
-      float* sAl = sA + TBM * TBK;
-      float* sB = sAl + TBM * TBK;
-      float* sBl = sB + BN * TBK;
+      const uint32_t rA = raw_base + (uint32_t)(it % Cfg::kRaw) * Cfg::kRawBytes;
+      const uint32_t rB = rA + Cfg::kABytes;
+      const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes;
+      const uint32_t sAl = sA + Cfg::kABytes;
+      const uint32_t sB = sAl + Cfg::kABytes;
+      const uint32_t sBl = sB + Cfg::kBBytes;
       { TRACE_T0();
       if (planA.kfast) convert_tile<TBM, true>(sA, sAl, rA, planA, tid);
       else convert_tile<TBM, false>(sA, sAl, rA, planA, tid);
@@ -379,7 +385,7 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
         float* Cb; long sCm, sCn;
         if (partial) { Cb = aux + (long)z * p.M * p.N; sCm = p.N; sCn = 1; }
         else { Cb = p.C + (p.reduce_batch ? 0 : (long)z * p.sCb); sCm = p.sCm; sCn = p.sCn; }
-        const bool acc_out = !partial && p.accumulate;
+        const bool acc_out = ACC && !partial;
         const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
         const float bm = (!partial && p.bias_m) ? __ldg(p.bias_m + boff + gm) : 0.f;
         const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
@@ -423,9 +429,9 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
           constexpr int W = HC < 32 ? HC : 32;      // block width (columns)
           constexpr int CPR = W / 4;                // 16-byte chunks per row
           constexpr int RPI = 32 / CPR;             // rows per store instruction
-          float* tile = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 1024 +
-                                                 Cfg::kRaw * Cfg::kRawBytes) + e * 1024;
-          const bool acc_out = !partial && p.accumulate;
+          const uint32_t tile = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes + 1024 +
+                                         Cfg::kRaw * Cfg::kRawBytes) + (uint32_t)e * 4096u;
+          const bool acc_out = ACC && !partial;
           const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
           const float bm = (!partial && p.bias_m && gm < p.M) ? __ldg(p.bias_m + boff + gm) : 0.f;
           const int rsub = lane / CPR, csub = lane % CPR;
@@ -433,34 +439,33 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
           for (int cb = 0; cb < HC; cb += W) {
 #pragma unroll
             for (int c = 0; c < CPR; c++) {         // thread = row `lane` of the warp's 32
-              float4 q = make_float4(fmaf(p.alpha, acc[cb + 4 * c], bm), fmaf(p.alpha, acc[cb + 4 * c + 1], bm),
-                                     fmaf(p.alpha, acc[cb + 4 * c + 2], bm), fmaf(p.alpha, acc[cb + 4 * c + 3], bm));
-              *reinterpret_cast<float4*>(tile + lane * 32 + ((c ^ (lane & 7)) << 2)) = q;
+              sts128(tile + (uint32_t)(lane * 32 + ((c ^ (lane & 7)) << 2)) * 4u,
+                     fmaf(p.alpha, acc[cb + 4 * c], bm), fmaf(p.alpha, acc[cb + 4 * c + 1], bm),
+                     fmaf(p.alpha, acc[cb + 4 * c + 2], bm), fmaf(p.alpha, acc[cb + 4 * c + 3], bm));
             }
             __syncwarp();
             const int gn = nb + cb + 4 * csub;
             float4 bn4 = make_float4(0.f, 0.f, 0.f, 0.f);
             if (!partial && p.bias_n && gn + 3 < p.N) bn4 = __ldg(reinterpret_cast<const float4*>(p.bias_n + boff + gn));
-            float4 prev[32 / RPI];                  // C += : all reads of a block in flight before the first use
-            if (acc_out) {
-#pragma unroll
-              for (int it = 0; it < 32 / RPI; it++) {
-                const int grow = tl.m0 + quad * 32 + it * RPI + rsub;
-                prev[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (grow < p.M && gn + 3 < p.N) prev[it] = *reinterpret_cast<const float4*>(Cb + (long)grow * sCm + gn);
-              }
-            }
+            // C += goes out as a vector reduction (red.global.add.v4.f32): the add happens in L2, nothing is
+            // read back into the SM and no registers hold old values (a prefetch array spilled to local memory
+            // and every store then waited on a local load -- ncu: the top stall of the K = 32 GEMMs).  Each
+            // element receives exactly one add per launch, so the result does not depend on any ordering.
 #pragma unroll
             for (int it = 0; it < 32 / RPI; it++) {
               const int rr = it * RPI + rsub;
               const int grow = tl.m0 + quad * 32 + rr;
-              float4 q = *reinterpret_cast<const float4*>(tile + rr * 32 + ((csub ^ (rr & 7)) << 2));
+              float4 q = lds128(tile + (uint32_t)(rr * 32 + ((csub ^ (rr & 7)) << 2)) * 4u);
               if (grow < p.M && gn < p.N) {
                 float* dst = Cb + (long)grow * sCm + gn;
                 if (gn + 3 < p.N) {
                   q.x += bn4.x; q.y += bn4.y; q.z += bn4.z; q.w += bn4.w;
-                  if (acc_out) { q.x += prev[it].x; q.y += prev[it].y; q.z += prev[it].z; q.w += prev[it].w; }
-                  *reinterpret_cast<float4*>(dst) = q;
+                  if (acc_out) {
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(q.x), "f"(q.y),
+                                 "f"(q.z), "f"(q.w) : "memory");
+                  } else {
+                    *reinterpret_cast<float4*>(dst) = q;
+                  }
                 } else {
                   const float o[4] = {q.x, q.y, q.z, q.w};
                   for (int j = 0; j < 4 && gn + j < p.N; j++) {
@@ -521,10 +526,10 @@ TcPlan tc_plan(const GemmDesc& in, bool allow_swap) {
   return pl;
 }
 
-template <int BN, int EPI>
-int tc_launch_bn(cudaStream_t st, const TcPlan& pl, float* aux) {
+template <int BN, int EPI, bool ACC>
+int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
   using Cfg = TcCfg<BN>;
-  auto kern = tc_gemm_kernel<BN, EPI>;
+  auto kern = tc_gemm_kernel<BN, EPI, ACC>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem);
   if (e != cudaSuccess) return (int)e;
   const GemmDesc& d = pl.d;
@@ -534,6 +539,14 @@ int tc_launch_bn(cudaStream_t st, const TcPlan& pl, float* aux) {
   kern<<<ctas, kTcThreads, Cfg::kSmem, st>>>(d, aux, pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
+}
+
+template <int BN, int EPI>
+int tc_launch_bn(cudaStream_t st, const TcPlan& pl, float* aux) {
+  // split-K partials are plain stores; the accumulation then happens in splitk_reduce_kernel
+  const bool acc = EPI == GEMM_EPI_STORE && pl.d.accumulate && !(pl.d.reduce_batch && pl.nsplit > 1);
+  if (EPI == GEMM_EPI_STORE && acc) return tc_launch_acc<BN, GEMM_EPI_STORE, true>(st, pl, aux);
+  return tc_launch_acc<BN, EPI, false>(st, pl, aux);
 }
 
 template <int EPI>
