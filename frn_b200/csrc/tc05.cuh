@@ -56,6 +56,18 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
 // One lane of a CONVERGED warp (elect.sync).  tcgen05.mma / commit must be issued from code the
 // compiler can prove warp-uniform: under `if (lane == 0)` it wraps every UTCHMMA in an
 // ELECT / BRA.U.ANY convergence loop (~40 cycles per instruction, measured: 80 cycles per MMA).
+// TMA tile load (cp.async.bulk.tensor, 3-D tensor map): box -> dense shared memory, completion on an mbarrier
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const void* tmap, int c0, int c1, int c2,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst_smem), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

@@ -17,6 +17,12 @@
 // So no accumulation chain is longer than kChunk = 4 stages (K = 128): the accumulators are
 // double buffered in TMEM and each finished chunk is added into fp32 registers by the drain
 // warps while the next chunk is being multiplied.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include <cstdlib>
+#include <cstring>
+
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -185,7 +191,7 @@ __device__ __forceinline__ TcTile tc_tile(const GemmDesc& p, int id, int gx, int
 template <int BN, int EPI, bool ACC>      // ACC: C += (a separate instantiation keeps the read-modify-write
 __global__ void __launch_bounds__(kTcThreads, 1)    // registers out of the plain-store kernels)
 tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_split, int nsplit, int gx, int gy,
-               int gz) {
+               int gz, int use_tma, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB) {
   using Cfg = TcCfg<BN>;
   constexpr int HC = BN / 2;          // columns per drain thread
   extern __shared__ uint8_t smem_raw[];
@@ -194,7 +200,8 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
   uint64_t* empty = full + Cfg::kStages;
   uint64_t* acc_full = empty + Cfg::kStages;     // 2
   uint64_t* acc_free = acc_full + 2;             // 2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_free + 2);
+  uint64_t* raw_full = acc_free + 2;             // kRaw (TMA path)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(raw_full + Cfg::kRaw);
   float* red = reinterpret_cast<float*>(tmem_slot + 4);   // 128 floats (row-sum-of-squares epilogue)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -203,6 +210,8 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
   if (tid == 0) {
     for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&full[s], kLoaders); mbar_init(&empty[s], 1); }
     for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_free[s], kEpiThreads); }
+    for (int s = 0; s < Cfg::kRaw; s++) mbar_init(&raw_full[s], 1);
+    if (use_tma) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
     mbar_init_fence();
   }
   if (warp == kMmaWarp) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
@@ -220,43 +229,69 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
     planA.init(p.sAm, p.sAk, tid);
     planB.init(p.sBn, p.sBk, tid);
     const long osA = planA.kfast ? p.sAm : p.sAk, osB = planB.kfast ? p.sBn : p.sBk;
-    struct Cursor { int id, i; TcTile tl; };
-    auto settle = [&](Cursor& c) {                 // move to the next tile that has stages left
+    // Tile cursor.  The tile decomposition (integer divisions) runs once per TILE, and the (batch entry,
+    // k tile) pair of the split-K walk advances incrementally: recomputing both per stage cost the staging
+    // warps ~850 cycles per stage, as much as the conversion itself.
+    struct Cursor { int id, i, b, kt; TcTile tl; };
+    auto enter = [&](Cursor& c) {                  // c.id: a new tile, or past the end; skips empty tiles
       while (c.id < total) {
         c.tl = tc_tile(p, c.id, gx, gy, ktiles, tiles_per_split, BN);
-        if (c.i < c.tl.ntiles) return;
-        c.id += gridDim.x; c.i = 0;
+        if (c.tl.ntiles > 0) break;
+        c.id += gridDim.x;
       }
+      c.i = 0; c.b = 0; c.kt = 0;
+      if (c.id < total) {
+        if (c.tl.b_fixed >= 0) c.b = c.tl.b_fixed;
+        else { c.b = c.tl.t_begin / ktiles; c.kt = c.tl.t_begin - c.b * ktiles; }
+      }
+    };
+    auto advance = [&](Cursor& c) {
+      c.i++; c.kt++;
+      if (c.tl.b_fixed < 0 && c.kt == ktiles) { c.kt = 0; c.b++; }
+      if (c.i >= c.tl.ntiles) { c.id += gridDim.x; enter(c); }
     };
     auto issue = [&](const Cursor& c, long it) {
       const TcTile& tl = c.tl;
-      const int t = tl.t_begin + c.i;
-      const int b = tl.b_fixed >= 0 ? tl.b_fixed : t / ktiles;
-      const int k0 = (tl.b_fixed >= 0 ? t : t % ktiles) * TBK;
-      const uint32_t rA = raw_base + (uint32_t)(it % Cfg::kRaw) * Cfg::kRawBytes;
+      const int b = c.b, k0 = c.kt * TBK;
+      const int slot = (int)(it % Cfg::kRaw);
+      const uint32_t rA = raw_base + (uint32_t)slot * Cfg::kRawBytes;
       const uint32_t rB = rA + Cfg::kABytes;
+      if (use_tma) {
+        // TMA: one thread asks for the two boxes (rows x 32 k, any strides, zero fill past the edges); the
+        // 256 staging threads issue no loads at all (cp.async cost them as much time as the conversion)
+        if (tid == 0) {
+          mbar_expect_tx(&raw_full[slot], Cfg::kRawBytes);
+          const int ba = p.sAb ? b : 0, bb = p.sBb ? b : 0;
+          if (planA.kfast) tma_load_3d(rA, &tmA, k0, tl.m0, ba, &raw_full[slot]);
+          else tma_load_3d(rA, &tmA, tl.m0, k0, ba, &raw_full[slot]);
+          if (planB.kfast) tma_load_3d(rB, &tmB, k0, tl.n0, bb, &raw_full[slot]);
+          else tma_load_3d(rB, &tmB, tl.n0, k0, bb, &raw_full[slot]);
+        }
+        return;
+      }
       issue_raw<TBM>(rA, p.A + (long)b * p.sAb + (long)tl.m0 * p.sAm + (long)k0 * p.sAk, planA, osA,
                      p.M - tl.m0, p.K - k0, tid);
       issue_raw<BN>(rB, p.B + (long)b * p.sBb + (long)tl.n0 * p.sBn + (long)k0 * p.sBk, planB, osB,
                     p.N - tl.n0, p.K - k0, tid);
     };
-    Cursor ci{(int)blockIdx.x, 0, {}}, cc{(int)blockIdx.x, 0, {}};
-    settle(ci); settle(cc);
+    Cursor ci{(int)blockIdx.x, 0, 0, 0, {}}, cc{(int)blockIdx.x, 0, 0, 0, {}};
+    enter(ci); enter(cc);
     long it_issue = 0;
     for (int r = 0; r < Cfg::kRaw - 1; r++) {      // prologue
-      if (ci.id < total) { issue(ci, it_issue); ci.i++; settle(ci); }
+      if (ci.id < total) { issue(ci, it_issue); advance(ci); }
       it_issue++;
       cp_async_commit();
     }
     for (long it = 0; cc.id < total; it++) {
       { TRACE_T0();
       cp_async_wait<Cfg::kRaw - 2>();              // this thread's copies of stage `it` have landed
+      if (use_tma) mbar_wait(&raw_full[it % Cfg::kRaw], (uint32_t)((it / Cfg::kRaw) & 1));
       TRACE_ADD(0); }
       { TRACE_T0();
       asm volatile("bar.sync 2, 256;" ::: "memory");  // ... everyone's have, and everyone is done with stage it-1
       TRACE_ADD(1); }
       { TRACE_T0();
-      if (ci.id < total) { issue(ci, it_issue); ci.i++; settle(ci); }
+      if (ci.id < total) { issue(ci, it_issue); advance(ci); }
       it_issue++;
       cp_async_commit();
       TRACE_ADD(12); }
@@ -285,7 +320,7 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       mbar_arrive(&full[stage]);
       TRACE_ADD(11); }
       TRACE_ADD(3);
-      cc.i++; settle(cc);
+      advance(cc);
     }
     cp_async_wait<0>();
   } else if (warp == kMmaWarp) {
@@ -526,6 +561,45 @@ TcPlan tc_plan(const GemmDesc& in, bool allow_swap) {
   return pl;
 }
 
+// ---- TMA tensor maps for the operands -------------------------------------------------
+// An operand is a (rows, K, batch) view with element strides (rs, ks, bs), one of rs / ks being 1.  TMA needs
+// a 16-byte aligned base and byte strides that are multiples of 16; anything else (odd map sizes such as
+// 17 positions) takes the cp.async path of the same kernel.
+PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(f);
+  }();
+  return fn;
+}
+
+bool make_operand_map(CUtensorMap* tm, const float* base, int rows, int K, int batch, long rs, long ks, long bs,
+                      int box_rows) {
+  auto enc = tensor_map_encoder();
+  if (!enc) return false;
+  if (reinterpret_cast<uintptr_t>(base) & 15) return false;
+  const bool kfast = (ks == 1);
+  const long os = kfast ? rs : ks;                       // stride of the non-contiguous axis
+  const int nb = (bs == 0 || batch == 1) ? 1 : batch;
+  if (os <= 0 || (os & 3) || (nb > 1 && (bs <= 0 || (bs & 3)))) return false;
+  cuuint64_t dims[3] = {(cuuint64_t)(kfast ? K : rows), (cuuint64_t)(kfast ? rows : K), (cuuint64_t)nb};
+  // an unused batch axis still needs a legal stride
+  cuuint64_t strides[2] = {(cuuint64_t)os * 4, (cuuint64_t)(nb > 1 ? bs : os * (long)dims[1]) * 4};
+  cuuint32_t box[3] = {(cuuint32_t)(kfast ? TBK : box_rows), (cuuint32_t)(kfast ? box_rows : TBK), 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  if (strides[0] >= (1ull << 40) || strides[1] >= (1ull << 40)) return false;
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+int g_tma_mode = -1;      // FRN_GEMM_TMA=0 forces the cp.async staging path (debug / comparison)
+
 template <int BN, int EPI, bool ACC>
 int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
   using Cfg = TcCfg<BN>;
@@ -536,7 +610,18 @@ int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
   const int gx = cdiv(d.N, BN), gy = cdiv(d.M, TBM), gz = d.reduce_batch ? pl.nsplit : d.batch;
   const long total = (long)gx * gy * gz;
   const int ctas = (int)(total < kSmCount ? total : kSmCount);      // persistent: one CTA per SM
-  kern<<<ctas, kTcThreads, Cfg::kSmem, st>>>(d, aux, pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz);
+  if (g_tma_mode < 0) {
+    const char* s = getenv("FRN_GEMM_TMA");
+    g_tma_mode = (s && s[0] == '0') ? 0 : 1;
+  }
+  alignas(64) CUtensorMap tmA, tmB;
+  memset(&tmA, 0, sizeof tmA);
+  memset(&tmB, 0, sizeof tmB);
+  const int use_tma = g_tma_mode &&
+                      make_operand_map(&tmA, d.A, d.M, d.K, d.batch, d.sAm, d.sAk, d.sAb, TBM) &&
+                      make_operand_map(&tmB, d.B, d.N, d.K, d.batch, d.sBn, d.sBk, d.sBb, BN);
+  kern<<<ctas, kTcThreads, Cfg::kSmem, st>>>(d, aux, pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz, use_tma,
+                                             tmA, tmB);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }
