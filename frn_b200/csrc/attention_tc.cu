@@ -109,6 +109,15 @@ __global__ void attn_bwd_prep_kernel(int N, int NP, int d, const float* __restri
   delta_pad[(long)b * NP + n] = dl;
 }
 
+// 2^x on the special-function unit alone (ex2.approx.ftz: 2 ulp; exp2f() wraps the same instruction in a
+// denormal-range rescale of four more instructions, and the softmax / dS warps -- one or two per scheduler --
+// are what bounds these kernels, not the tensor pipe).  Arguments here are <= 0; -inf gives 0.
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // 3xTF32 products of one 32-deep K sub-tile (4 K = 8 slices of 32 bytes each) into ONE fp32
 // accumulator.  The 2^-11-sized correction terms a_lo.b_hi + a_hi.b_lo of ALL sub-tiles are issued
 // first and the main terms a_hi.b_hi after them: the tensor core truncates the smaller addend when
@@ -198,7 +207,8 @@ __device__ __forceinline__ void mma2_ts(uint32_t d0, uint32_t a0_hi, uint32_t a0
 // ------------------------------------------------------------------------------------------------
 constexpr int ABM = 128;   // query rows per CTA (UMMA M)
 constexpr int ABN = 64;    // keys per tile
-constexpr int kFwdThreads = 192;   // warps 0-3 softmax, 4 MMA issue, 5 bulk-copy producer
+constexpr int kFwdThreads = 320;   // warps 0-3 / 4-7: softmax groups (even / odd key tiles), 8 MMA issue, 9 producer
+constexpr int kFwdMmaWarp = 8;
 
 template <int DPAD> struct FwdCfg {
   static constexpr int kSub = DPAD / 32;                    // 32-channel sub-tiles
@@ -244,13 +254,13 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     }
     mbar_init_fence();
   }
-  if (warp == 4) tmem_alloc<512>(tmem_slot);
+  if (warp == kFwdMmaWarp) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 5) {
+  if (warp == kFwdMmaWarp + 1) {
     // ======================= bulk-copy producer =======================
     if (lane == 0) {
       mbar_expect_tx(q_full, Cfg::kQBytes);
@@ -278,7 +288,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == kFwdMmaWarp) {
     // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
     {
       constexpr uint32_t idesc_s = umma_idesc_tf32(ABM, ABN);
@@ -328,15 +338,20 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     }
   } else {
     // ======================= softmax + promotion (thread = query row) =======================
-    const int row = tid;                               // 0..127
-    const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+    // Two groups of four warps: group g owns the key tiles j = g (mod 2), i.e. TMEM buffer g, with its own
+    // running max / sum / accumulator, and the two partial softmax states are merged at the end.  With one
+    // group the four softmax warps (one per scheduler, nothing to hide their latencies behind) took twice as
+    // long per tile as the tensor pipe; the groups need no exchange inside the loop.
+    const int grp = warp >> 2;
+    const int row = tid & 127;                         // 0..127
+    const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
     float m = -INFINITY, l = 0.f, corr_prev = 0.f;
     float y[DPAD];
 #pragma unroll
     for (int c = 0; c < DPAD; c++) y[c] = 0.f;
+    const int buf = grp;
 
     auto promote = [&](int j, float corr) {            // y = y * corr + Y_tile(j)
-      const int buf = j & 1;
       mbar_wait(&y_full[buf], (j >> 1) & 1);
       tc_fence_after();
 #pragma unroll
@@ -351,8 +366,9 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       mbar_arrive(&y_free[buf]);
     };
 
-    for (int j = 0; j < T; j++) {
-      const int buf = j & 1, j0 = j * ABN;
+    int jlast = -1;
+    for (int j = grp; j < T; j += 2) {
+      const int j0 = j * ABN;
       mbar_wait(&s_full[buf], (j >> 1) & 1);
       tc_fence_after();
       float s[ABN];
@@ -372,14 +388,14 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
 #pragma unroll
       for (int q = 0; q < ABN; q++) mx = fmaxf(mx, s[q]);
       const float m_new = fmaxf(m, mx);
-      const float corr = exp2f((m - m_new) * kLog2e);
+      const float corr = ex2_fast((m - m_new) * kLog2e);
       float sum = 0.f;
 #pragma unroll
       for (int c0 = 0; c0 < ABN; c0 += 16) {
         float hi[16], lo[16];
 #pragma unroll
         for (int q = 0; q < 16; q++) {
-          float p = exp2f((s[c0 + q] - m_new) * kLog2e);
+          float p = ex2_fast((s[c0 + q] - m_new) * kLog2e);
           sum += p;
           split_tf32(p, hi[q], lo[q]);
         }
@@ -391,30 +407,47 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(&p_full[buf]);
-      if (j >= 1) promote(j - 1, corr_prev);
+      if (jlast >= 0) promote(jlast, corr_prev);
       corr_prev = corr;
+      jlast = j;
     }
-    promote(T - 1, corr_prev);
+    if (jlast >= 0) promote(jlast, corr_prev);
 
+    // merge the two groups' states (all MMAs are complete once both groups have promoted their last tile)
+    float* xch = reinterpret_cast<float*>(sQ);         // [DPAD + 2][128], the Q tile is dead by now
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (grp == 1) {
+      xch[row] = m;
+      xch[128 + row] = l;
+#pragma unroll
+      for (int c = 0; c < DPAD; c++) xch[(2 + c) * 128 + row] = y[c];
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     const int gi = i0 + row;
-    if (gi < N) {
+    if (grp == 0 && gi < N) {
+      const float m1 = xch[row], l1 = xch[128 + row];
+      const float mm = fmaxf(m, m1);
+      const float a0 = ex2_fast((m - mm) * kLog2e), a1 = ex2_fast((m1 - mm) * kLog2e);
+      l = l * a0 + l1 * a1;
       const float inv = 1.f / l;
-      lse[(long)b * N + gi] = m + logf(l);
+      lse[(long)b * N + gi] = mm + logf(l);
       float* dst = Y + ((long)b * N + gi) * d;
+#pragma unroll
+      for (int c = 0; c < DPAD; c++) y[c] = (y[c] * a0 + xch[(2 + c) * 128 + row] * a1) * inv;
       if ((d & 3) == 0) {
 #pragma unroll
         for (int c = 0; c < DPAD; c += 4)
-          if (c < d) *reinterpret_cast<float4*>(dst + c) = make_float4(y[c] * inv, y[c + 1] * inv, y[c + 2] * inv, y[c + 3] * inv);
+          if (c < d) *reinterpret_cast<float4*>(dst + c) = make_float4(y[c], y[c + 1], y[c + 2], y[c + 3]);
       } else {
 #pragma unroll
         for (int c = 0; c < DPAD; c++)
-          if (c < d) dst[c] = y[c] * inv;
+          if (c < d) dst[c] = y[c];
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc<512>(tmem);
+  if (warp == kFwdMmaWarp) tmem_dealloc<512>(tmem);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -616,7 +649,7 @@ attn_dq_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage
             tmem_wait_ld();
 #pragma unroll
             for (int q = 0; q < 16; q++) {
-              p[q] = exp2f((a[q] - lse_i) * kLog2e);
+              p[q] = ex2_fast((a[q] - lse_i) * kLog2e);
               if (j0 + c0 + q >= N) p[q] = 0.f;
               split_tf32(p[q] * (g[q] - delta_i), hi[q], lo[q]);
             }
@@ -843,7 +876,7 @@ attn_dkv_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
             tmem_wait_ld();
 #pragma unroll
             for (int q = 0; q < 16; q++) {
-              p[q] = exp2f((a[q] - rw[c0 + q]) * kLog2e);
+              p[q] = ex2_fast((a[q] - rw[c0 + q]) * kLog2e);
               split_tf32(p[q], hi[q], lo[q]);
             }
           }
