@@ -22,6 +22,8 @@
 //                        -> dV, dK   (d = 64: one 32-channel half of dV / dK per CTA)
 // No atomics anywhere: the backward is deterministic.
 #include <mutex>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -919,6 +921,250 @@ attn_dkv_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
 }
 
 // ------------------------------------------------------------------------------------------------
+// backward, part 2, second design (the default): one tile of 128 keys per CTA, the S^T / dP^T
+// accumulators double buffered and EIGHT compute warps.
+// In the ping-pong design above every tile is a serial chain  S^T,dP^T MMAs -> exp / dS warps -> dV,dK
+// MMAs -> next S^T (it overwrites P^T in place), and two tiles in flight could not hide a chain that is
+// three times longer than its tensor-pipe share (measured ~4600 cycles per 32-query step against 2700 of
+// tcgen05.mma time, tools/mma_cost_probe.cu).  Here S^T(j+1), dP^T(j+1) go to a second pair of TMEM
+// buffers and are issued BEFORE dV(j), dK(j), so the tensor pipe works on tile j+1 while the compute warps
+// handle tile j; the compute work of a tile is split over two warps per lane quadrant (16 of the 32 query
+// columns each, and 16 of the 32 accumulator channels each at promotion time).
+// TMEM: S^T[2] 0,32 | dP^T[2] 64,96 | P^T hi 128, lo 160 | dS^T hi 192, lo 224 | dV 256 | dK 288.
+// ------------------------------------------------------------------------------------------------
+#ifdef FRN_ATTN_TRACE
+__device__ unsigned long long g_attn_trace[16];
+#define ATR_T0() const long long atr0__ = clock64()
+#define ATR_ADD(slot) do { if (blockIdx.x == 0 && blockIdx.y == 0 && (threadIdx.x & 31) == 0) atomicAdd(&g_attn_trace[slot], (unsigned long long)(clock64() - atr0__)); } while (0)
+#else
+#define ATR_T0() do {} while (0)
+#define ATR_ADD(slot) do {} while (0)
+#endif
+
+template <int DPAD> struct Dkv2Cfg {
+  static constexpr int kSub = DPAD / 32;
+  static constexpr int kOperBytes = kSub * 128 * 128;          // one 128-row pos tile, hi or lo
+  static constexpr int kResBytes = 4 * kOperBytes;             // K hi, K lo, V hi, V lo
+  static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile, hi or lo
+  static constexpr int kChanBytes = 32 * 128;                  // one 32-channel group of a chan block
+  static constexpr int kStageBytes = 4 * kPosBytes + 4 * kChanBytes;  // Q pos, dY pos, dY chan, Q chan (hi/lo each)
+  static constexpr int kStages = DPAD == 32 ? 4 : 2;
+  static constexpr int kRowBytes = kStages * 2 * BT * 4;       // lse, delta of the tile's queries
+  static constexpr int kSmem = kResBytes + kStages * kStageBytes + kRowBytes + 1024 + 256;
+  static constexpr int kThreads = 10 * 32;                     // warps 0-7 compute, 8 MMA issue, 9 producer
+  static constexpr int kS = 0, kP = 64, kPhi = 128, kPlo = 160, kDhi = 192, kDlo = 224, kV = 256, kK = 288;
+};
+
+template <int DPAD>
+__global__ void __launch_bounds__(Dkv2Cfg<DPAD>::kThreads, 1)
+attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, SplitImage dYi,
+                    const float* __restrict__ lse_pad, const float* __restrict__ delta_pad,
+                    float* __restrict__ dKp, float* __restrict__ dVp) {
+  using Cfg = Dkv2Cfg<DPAD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sRes = smem;
+  uint8_t* sStage = smem + Cfg::kResBytes;
+  float* sRows = reinterpret_cast<float*>(sStage + Cfg::kStages * Cfg::kStageBytes);   // [stage][lse BT | delta BT]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sRows) + Cfg::kRowBytes);
+  uint64_t* res_full = bars;                       // 1
+  uint64_t* q_full = res_full + 1;                 // kStages
+  uint64_t* q_empty = q_full + Cfg::kStages;       // kStages
+  uint64_t* sdp_full = q_empty + Cfg::kStages;     // 2   S^T, dP^T of a tile are in TMEM buffer (j & 1)
+  uint64_t* s_free = sdp_full + 2;                 // 2   ... and have been read into registers (256 arrivals)
+  uint64_t* ds_full = s_free + 2;                  // 1   P^T, dS^T written, previous dV / dK promoted (256)
+  uint64_t* pv_done = ds_full + 1;                 // 1   dV, dK MMAs of a tile complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, cg = blockIdx.z;          // cg: 32-channel group of dV / dK
+  const int kt = blockIdx.x;                          // key tile
+  const int TQ = (N + BT - 1) / BT;                   // query tiles
+
+  if (tid == 0) {
+    mbar_init(res_full, 1); mbar_init(ds_full, 256); mbar_init(pv_done, 1);
+    for (int s = 0; s < 2; s++) { mbar_init(&sdp_full[s], 1); mbar_init(&s_free[s], 256); }
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+    mbar_init_fence();
+  }
+  if (warp == 8) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 9) {
+    // ======================= bulk-copy producer =======================
+    if (lane == 0) {
+      mbar_expect_tx(res_full, Cfg::kResBytes);
+#pragma unroll
+      for (int s = 0; s < Cfg::kSub; s++) {
+        const long o = (((long)b * Cfg::kSub + s) * NP + (long)kt * 128) * 32;
+        bulk_g2s(sRes + s * 16384, Ki.pos_hi + o, 16384, res_full);
+        bulk_g2s(sRes + Cfg::kOperBytes + s * 16384, Ki.pos_lo + o, 16384, res_full);
+        bulk_g2s(sRes + 2 * Cfg::kOperBytes + s * 16384, Vi.pos_hi + o, 16384, res_full);
+        bulk_g2s(sRes + 3 * Cfg::kOperBytes + s * 16384, Vi.pos_lo + o, 16384, res_full);
+      }
+      int stage = 0; uint32_t phase = 0;
+      for (int j = 0; j < TQ; j++) {
+        mbar_wait(&q_empty[stage], phase ^ 1);
+        uint8_t* st = sStage + stage * Cfg::kStageBytes;
+        mbar_expect_tx(&q_full[stage], Cfg::kStageBytes + 2 * BT * 4);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * BT) * 32;
+          bulk_g2s(st + s * BT * 128, Qi.pos_hi + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + Cfg::kPosBytes + s * BT * 128, Qi.pos_lo + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + 2 * Cfg::kPosBytes + s * BT * 128, dYi.pos_hi + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + 3 * Cfg::kPosBytes + s * BT * 128, dYi.pos_lo + o, BT * 128, &q_full[stage]);
+        }
+        const long oc = (((long)b * (NP / 32) + j) * DPAD + cg * 32) * 32;
+        uint8_t* sc = st + 4 * Cfg::kPosBytes;
+        bulk_g2s(sc, dYi.chan_hi + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + Cfg::kChanBytes, dYi.chan_lo + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + 2 * Cfg::kChanBytes, Qi.chan_hi + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + 3 * Cfg::kChanBytes, Qi.chan_lo + oc, Cfg::kChanBytes, &q_full[stage]);
+        float* rw = sRows + stage * 2 * BT;
+        bulk_g2s(rw, lse_pad + (long)b * NP + (long)j * BT, BT * 4, &q_full[stage]);
+        bulk_g2s(rw + BT, delta_pad + (long)b * NP + (long)j * BT, BT * 4, &q_full[stage]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 8) {
+    // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
+    constexpr uint32_t idesc = umma_idesc_tf32(128, BT);     // every product here is 128 x 32
+    const uint32_t r = smem_u32(sRes);
+    auto issue_sdp = [&](int t) {                            // S^T(t) = K.Q^T ; dP^T(t) = V.dY^T
+      { ATR_T0();
+      mbar_wait(&q_full[t % Cfg::kStages], (t / Cfg::kStages) & 1);
+      ATR_ADD(0); }
+      { ATR_T0();
+      if (t >= 2) mbar_wait(&s_free[t & 1], ((t - 2) >> 1) & 1);
+      ATR_ADD(1); }
+      tc_fence_after();
+      ATR_T0();
+      if (elect_one()) {
+        const uint32_t st = smem_u32(sStage + (t % Cfg::kStages) * Cfg::kStageBytes);
+        const uint32_t dS = tmem + Cfg::kS + (t & 1) * BT, dP = tmem + Cfg::kP + (t & 1) * BT;
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++)
+          mma2_corr_ss(dS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
+                       st + Cfg::kPosBytes + s * BT * 128,
+                       dP, r + 2 * Cfg::kOperBytes + s * 16384, r + 3 * Cfg::kOperBytes + s * 16384,
+                       st + 2 * Cfg::kPosBytes + s * BT * 128, st + 3 * Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++)
+          mma2_main_ss(dS, r + s * 16384, st + s * BT * 128,
+                       dP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128, idesc);
+        umma_commit(&sdp_full[t & 1]);
+      }
+      __syncwarp();
+      ATR_ADD(2);
+    };
+    mbar_wait(res_full, 0);
+    tc_fence_after();
+    issue_sdp(0);
+    for (int j = 0; j < TQ; j++) {
+      if (j + 1 < TQ) issue_sdp(j + 1);
+      { ATR_T0();
+      mbar_wait(ds_full, j & 1);                             // dV(j) = P^T.dY ; dK(j) = dS^T.Q
+      ATR_ADD(3); }
+      tc_fence_after();
+      ATR_T0();
+      if (elect_one()) {
+        const uint32_t sc = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
+        mma2_ts(tmem + Cfg::kV, tmem + Cfg::kPhi, tmem + Cfg::kPlo, sc, sc + Cfg::kChanBytes,
+                tmem + Cfg::kK, tmem + Cfg::kDhi, tmem + Cfg::kDlo, sc + 2 * Cfg::kChanBytes, sc + 3 * Cfg::kChanBytes,
+                idesc);
+        umma_commit(pv_done);
+        umma_commit(&q_empty[j % Cfg::kStages]);
+      }
+      __syncwarp();
+      ATR_ADD(4);
+    }
+  } else {
+    // ======================= P^T, dS^T + promotion (thread = key row, half of the columns) =======================
+    const int quad = warp & 3, half = warp >> 2;
+    const int row = quad * 32 + lane;
+    const int gj = kt * 128 + row;
+    const uint32_t tb = tmem + (((uint32_t)(quad * 32)) << 16) + half * 16;
+    float dv[16], dk[16];
+#pragma unroll
+    for (int c = 0; c < 16; c++) { dv[c] = 0.f; dk[c] = 0.f; }
+    auto promote = [&]() {                                  // channels [16 half, 16 half + 16) of this row
+      float a[16], s[16];
+      tmem_ld16(tb + Cfg::kV, a);
+      tmem_ld16(tb + Cfg::kK, s);
+      tmem_wait_ld();
+#pragma unroll
+      for (int q = 0; q < 16; q++) { dv[q] += a[q]; dk[q] += s[q]; }
+    };
+    for (int j = 0; j < TQ; j++) {
+      { ATR_T0();
+      mbar_wait(&sdp_full[j & 1], (j >> 1) & 1);
+      ATR_ADD(5); }
+      tc_fence_after();
+      ATR_T0();
+      float a[16], g[16];
+      tmem_ld16(tb + Cfg::kS + (j & 1) * BT, a);
+      tmem_ld16(tb + Cfg::kP + (j & 1) * BT, g);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&s_free[j & 1]);
+      mbar_wait(&q_full[j % Cfg::kStages], (j / Cfg::kStages) & 1);   // lse / delta of the tile have landed
+      const float* rw = sRows + (j % Cfg::kStages) * 2 * BT + half * 16;
+      float phi[16], plo[16], dhi[16], dlo[16];
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        const float p = ex2_fast((a[q] - rw[q]) * kLog2e);
+        split_tf32(p, phi[q], plo[q]);
+        split_tf32(p * (g[q] - rw[BT + q]), dhi[q], dlo[q]);
+      }
+      ATR_ADD(6);
+      if (j > 0) {                                           // dV(j-1), dK(j-1) complete: promote, then reuse P^T / dS^T
+        { ATR_T0();
+        mbar_wait(pv_done, (j - 1) & 1);
+        ATR_ADD(7); }
+        tc_fence_after();
+        promote();
+      }
+      { ATR_T0();
+      tmem_st16(tb + Cfg::kPhi, phi);
+      tmem_st16(tb + Cfg::kPlo, plo);
+      tmem_st16(tb + Cfg::kDhi, dhi);
+      tmem_st16(tb + Cfg::kDlo, dlo);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(ds_full);
+      ATR_ADD(8); }
+    }
+    mbar_wait(pv_done, (TQ - 1) & 1);
+    tc_fence_after();
+    promote();
+    if (gj < N) {
+      const int c0 = cg * 32 + half * 16;                  // first channel of this thread
+      float* dv_dst = dVp + ((long)b * N + gj) * d + c0;
+      float* dk_dst = dKp + ((long)b * N + gj) * d + c0;
+      if ((d & 3) == 0) {
+#pragma unroll
+        for (int c = 0; c < 16; c += 4)
+          if (c0 + c < d) {
+            *reinterpret_cast<float4*>(dv_dst + c) = make_float4(dv[c], dv[c + 1], dv[c + 2], dv[c + 3]);
+            *reinterpret_cast<float4*>(dk_dst + c) = make_float4(dk[c], dk[c + 1], dk[c + 2], dk[c + 3]);
+          }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 16; c++)
+          if (c0 + c < d) { dv_dst[c] = dv[c]; dk_dst[c] = dk[c]; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 template <typename K>
@@ -974,11 +1220,16 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   const int NP = attn_tc_np(N);
   using CfgK = DkvCfg<DPAD, NT>;
   using CfgQ = DqCfg<DPAD, NT>;
+  using CfgK2 = Dkv2Cfg<DPAD>;
   auto kern_kv = attn_dkv_tc_kernel<DPAD, NT>;
+  auto kern_kv2 = attn_dkv2_tc_kernel<DPAD>;
   auto kern_q = attn_dq_tc_kernel<DPAD, NT>;
+  static const int dkv_design = [] { const char* e = getenv("FRN_DKV_DESIGN"); return (e && e[0] == '1') ? 1 : 2; }();
   FRN_TRY(set_smem(kern_kv, CfgK::kSmem));
+  FRN_TRY(set_smem(kern_kv2, CfgK2::kSmem));
   FRN_TRY(set_smem(kern_q, CfgQ::kSmem));
   const dim3 grid_kv(cdiv(NP / 128, NT), B, cdiv(d, 32)), grid_q(cdiv(NP / 128, NT), B);
+  const dim3 grid_kv2(NP / 128, B, cdiv(d, 32));
   ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
   cudaStream_t side = timing_enabled() ? nullptr : side_stream();
   cudaEvent_t fork = nullptr, join = nullptr;
@@ -996,7 +1247,10 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   }
   {
     ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
-    kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+    if (dkv_design == 2)
+      kern_kv2<<<grid_kv2, CfgK2::kThreads, CfgK2::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+    else
+      kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
     FRN_LAUNCH_CHECK();
   }
   if (side) {
@@ -1011,6 +1265,18 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
 }
 
 }  // namespace
+
+int attn_tc_trace_read(unsigned long long* out16) {
+#ifdef FRN_ATTN_TRACE
+  unsigned long long z[16] = {0};
+  cudaMemcpyFromSymbol(out16, g_attn_trace, sizeof(z));
+  cudaMemcpyToSymbol(g_attn_trace, z, sizeof(z));
+  return 1;
+#else
+  (void)out16;
+  return 0;
+#endif
+}
 
 int attn_tc_np(int N) { return (N + 127) / 128 * 128; }
 
