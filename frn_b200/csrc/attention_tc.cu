@@ -1247,7 +1247,7 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   }
   {
     ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
-    if (dkv_design == 2)
+    if (dkv_design == 2 && DPAD == 32)    // d = 64 leaves room for two query stages only: the ping-pong design is faster there
       kern_kv2<<<grid_kv2, CfgK2::kThreads, CfgK2::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
     else
       kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
