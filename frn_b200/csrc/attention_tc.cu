@@ -948,10 +948,14 @@ template <int DPAD> struct Dkv2Cfg {
   static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile, hi or lo
   static constexpr int kChanBytes = 32 * 128;                  // one 32-channel group of a chan block
   static constexpr int kStageBytes = 4 * kPosBytes + 4 * kChanBytes;  // Q pos, dY pos, dY chan, Q chan (hi/lo each)
-  static constexpr int kStages = DPAD == 32 ? 4 : 2;
+  // d <= 32: K and V (tf32 hi / lo) live in TMEM as the A operand of S^T / dP^T (TS form, which runs at the
+  // math rate: 16 cycles per N = 32 instruction instead of the 40 of a shared-memory A operand)
+  static constexpr bool kTS = DPAD == 32;
+  static constexpr int kStages = DPAD == 32 ? 6 : 2;
   static constexpr int kRowBytes = kStages * 2 * BT * 4;       // lse, delta of the tile's queries
-  static constexpr int kSmem = kResBytes + kStages * kStageBytes + kRowBytes + 1024 + 256;
-  static constexpr int kThreads = 10 * 32;                     // warps 0-7 compute, 8 MMA issue, 9 producer
+  static constexpr int kSmem = (kTS ? 0 : kResBytes) + kStages * kStageBytes + kRowBytes + 1024 + 256;
+  static constexpr int kKh = 320, kKl = 352, kVh = 384, kVl = 416;   // TMEM columns of the resident operands (kTS)
+  static constexpr int kThreads = 11 * 32;                     // warps 0-7 compute, 8 S^T/dP^T issue, 9 producer, 10 dV/dK issue
   static constexpr int kS = 0, kP = 64, kPhi = 128, kPlo = 160, kDhi = 192, kDlo = 224, kV = 256, kK = 288;
 };
 
@@ -964,7 +968,7 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sRes = smem;
-  uint8_t* sStage = smem + Cfg::kResBytes;
+  uint8_t* sStage = smem + (Cfg::kTS ? 0 : Cfg::kResBytes);
   float* sRows = reinterpret_cast<float*>(sStage + Cfg::kStages * Cfg::kStageBytes);   // [stage][lse BT | delta BT]
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sRows) + Cfg::kRowBytes);
   uint64_t* res_full = bars;                       // 1
@@ -982,7 +986,7 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
   const int TQ = (N + BT - 1) / BT;                   // query tiles
 
   if (tid == 0) {
-    mbar_init(res_full, 1); mbar_init(ds_full, 256); mbar_init(pv_done, 1);
+    mbar_init(res_full, Cfg::kTS ? 256 : 1); mbar_init(ds_full, 256); mbar_init(pv_done, 1);
     for (int s = 0; s < 2; s++) { mbar_init(&sdp_full[s], 1); mbar_init(&s_free[s], 256); }
     for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
     mbar_init_fence();
@@ -996,14 +1000,16 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
   if (warp == 9) {
     // ======================= bulk-copy producer =======================
     if (lane == 0) {
-      mbar_expect_tx(res_full, Cfg::kResBytes);
+      if (!Cfg::kTS) {
+        mbar_expect_tx(res_full, Cfg::kResBytes);
 #pragma unroll
-      for (int s = 0; s < Cfg::kSub; s++) {
-        const long o = (((long)b * Cfg::kSub + s) * NP + (long)kt * 128) * 32;
-        bulk_g2s(sRes + s * 16384, Ki.pos_hi + o, 16384, res_full);
-        bulk_g2s(sRes + Cfg::kOperBytes + s * 16384, Ki.pos_lo + o, 16384, res_full);
-        bulk_g2s(sRes + 2 * Cfg::kOperBytes + s * 16384, Vi.pos_hi + o, 16384, res_full);
-        bulk_g2s(sRes + 3 * Cfg::kOperBytes + s * 16384, Vi.pos_lo + o, 16384, res_full);
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)kt * 128) * 32;
+          bulk_g2s(sRes + s * 16384, Ki.pos_hi + o, 16384, res_full);
+          bulk_g2s(sRes + Cfg::kOperBytes + s * 16384, Ki.pos_lo + o, 16384, res_full);
+          bulk_g2s(sRes + 2 * Cfg::kOperBytes + s * 16384, Vi.pos_hi + o, 16384, res_full);
+          bulk_g2s(sRes + 3 * Cfg::kOperBytes + s * 16384, Vi.pos_lo + o, 16384, res_full);
+        }
       }
       int stage = 0; uint32_t phase = 0;
       for (int j = 0; j < TQ; j++) {
@@ -1046,6 +1052,10 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
       if (elect_one()) {
         const uint32_t st = smem_u32(sStage + (t % Cfg::kStages) * Cfg::kStageBytes);
         const uint32_t dS = tmem + Cfg::kS + (t & 1) * BT, dP = tmem + Cfg::kP + (t & 1) * BT;
+        if (Cfg::kTS) {
+          mma2_ts(dS, tmem + Cfg::kKh, tmem + Cfg::kKl, st, st + Cfg::kPosBytes,
+                  dP, tmem + Cfg::kVh, tmem + Cfg::kVl, st + 2 * Cfg::kPosBytes, st + 3 * Cfg::kPosBytes, idesc);
+        } else {
 #pragma unroll
         for (int s = 0; s < Cfg::kSub; s++)
           mma2_corr_ss(dS, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + s * BT * 128,
@@ -1056,16 +1066,21 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
         for (int s = 0; s < Cfg::kSub; s++)
           mma2_main_ss(dS, r + s * 16384, st + s * BT * 128,
                        dP, r + 2 * Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128, idesc);
+        }
         umma_commit(&sdp_full[t & 1]);
       }
       __syncwarp();
       ATR_ADD(2);
     };
+    // Two issuing warps: this one feeds S^T / dP^T, warp 10 feeds dV / dK.  A single issuing thread spent a
+    // quarter of every step in the latency of its four (already satisfied) barrier waits, with the tensor
+    // pipe idle meanwhile; the two streams only depend on each other through the barriers below.
     mbar_wait(res_full, 0);
     tc_fence_after();
-    issue_sdp(0);
+    for (int t = 0; t < TQ; t++) issue_sdp(t);
+  } else if (warp == 10) {
+    constexpr uint32_t idesc = umma_idesc_tf32(128, BT);
     for (int j = 0; j < TQ; j++) {
-      if (j + 1 < TQ) issue_sdp(j + 1);
       { ATR_T0();
       mbar_wait(ds_full, j & 1);                             // dV(j) = P^T.dY ; dK(j) = dS^T.Q
       ATR_ADD(3); }
@@ -1077,6 +1092,7 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
                 tmem + Cfg::kK, tmem + Cfg::kDhi, tmem + Cfg::kDlo, sc + 2 * Cfg::kChanBytes, sc + 3 * Cfg::kChanBytes,
                 idesc);
         umma_commit(pv_done);
+        // S^T(j), dP^T(j) (warp 8) completed before compute(j) could release ds_full(j): the stage is free
         umma_commit(&q_empty[j % Cfg::kStages]);
       }
       __syncwarp();
@@ -1091,6 +1107,26 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
     float dv[16], dk[16];
 #pragma unroll
     for (int c = 0; c < 16; c++) { dv[c] = 0.f; dk[c] = 0.f; }
+    if (Cfg::kTS) {
+      // this thread's key row, channels [16 half, 16 half + 16) of K and V (hi, lo): packed image -> TMEM.
+      // The image rows are SWIZZLE_128B: 16-byte chunk c of row n sits at chunk position c ^ (n & 7).
+      const long ro = ((long)b * NP + gj) * 32;
+      const float* src[4] = {Ki.pos_hi + ro, Ki.pos_lo + ro, Vi.pos_hi + ro, Vi.pos_lo + ro};
+      const int col[4] = {Cfg::kKh, Cfg::kKl, Cfg::kVh, Cfg::kVl};
+#pragma unroll
+      for (int o = 0; o < 4; o++) {
+        float v[16];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          const float4 x = __ldg(reinterpret_cast<const float4*>(src[o] + (((4 * half + c) ^ (gj & 7)) << 2)));
+          v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
+        }
+        tmem_st16(tb + col[o], v);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(res_full);
+    }
     auto promote = [&]() {                                  // channels [16 half, 16 half + 16) of this row
       float a[16], s[16];
       tmem_ld16(tb + Cfg::kV, a);
