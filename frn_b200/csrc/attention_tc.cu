@@ -1201,6 +1201,196 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
 }
 
 // ------------------------------------------------------------------------------------------------
+// backward, part 1, second design (d <= 32): the mirror image of attn_dkv2_tc_kernel.  CTA = 128 queries
+// (lanes = queries), Q and dY resident in TMEM as the A operands of S = Q.K^T and dP = dY.V^T (TS form),
+// 32-key tiles streamed through shared memory (K pos, V pos, K chan), S / dP double buffered, eight
+// compute warps (16 key columns each), one warp issuing S / dP and one issuing dQ = dS.K.
+// TMEM: S[2] 0,32 | dP[2] 64,96 | dS hi 128, lo 160 | dQ 192 | Q hi 224, lo 256 | dY hi 288, lo 320.
+// ------------------------------------------------------------------------------------------------
+struct Dq2Cfg {
+  static constexpr int kPosBytes = BT * 128;                   // streamed pos tile (32 keys x 32 channels), hi or lo
+  static constexpr int kChanBytes = 32 * 128;                  // streamed chan block (32 channels x 32 keys), hi or lo
+  static constexpr int kStageBytes = 4 * kPosBytes + 2 * kChanBytes;   // K pos hi/lo, V pos hi/lo, K chan hi/lo
+  static constexpr int kStages = 8;
+  static constexpr int kSmem = kStages * kStageBytes + 1024 + 256;
+  static constexpr int kThreads = 11 * 32;                     // warps 0-7 compute, 8 S/dP issue, 9 producer, 10 dQ issue
+  static constexpr int kS = 0, kP = 64, kDhi = 128, kDlo = 160, kAcc = 192, kQh = 224, kQl = 256, kYh = 288, kYl = 320;
+};
+
+__global__ void __launch_bounds__(Dq2Cfg::kThreads, 1)
+attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, SplitImage dYi,
+                   const float* __restrict__ lse_pad, const float* __restrict__ delta_pad,
+                   float* __restrict__ dQp) {
+  using Cfg = Dq2Cfg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sStage = smem;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sStage + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* res_full = bars;                       // 1   Q, dY are in TMEM (256 arrivals)
+  uint64_t* kv_full = res_full + 1;                // kStages
+  uint64_t* kv_empty = kv_full + Cfg::kStages;     // kStages
+  uint64_t* sdp_full = kv_empty + Cfg::kStages;    // 2   S, dP of a tile are in TMEM buffer (j & 1)
+  uint64_t* s_free = sdp_full + 2;                 // 2   ... and have been read into registers (256 arrivals)
+  uint64_t* ds_full = s_free + 2;                  // 1   dS written, previous dQ tile promoted (256)
+  uint64_t* dq_done = ds_full + 1;                 // 1   dQ MMAs of a tile complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_done + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, qt = blockIdx.x;          // query tile
+  const int TK = (N + BT - 1) / BT;                   // key tiles
+
+  if (tid == 0) {
+    mbar_init(res_full, 256); mbar_init(ds_full, 256); mbar_init(dq_done, 1);
+    for (int s = 0; s < 2; s++) { mbar_init(&sdp_full[s], 1); mbar_init(&s_free[s], 256); }
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    mbar_init_fence();
+  }
+  if (warp == 8) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 9) {
+    // ======================= bulk-copy producer =======================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int j = 0; j < TK; j++) {
+        mbar_wait(&kv_empty[stage], phase ^ 1);
+        uint8_t* st = sStage + stage * Cfg::kStageBytes;
+        mbar_expect_tx(&kv_full[stage], Cfg::kStageBytes);
+        const long o = ((long)b * NP + (long)j * BT) * 32;
+        bulk_g2s(st, Ki.pos_hi + o, Cfg::kPosBytes, &kv_full[stage]);
+        bulk_g2s(st + Cfg::kPosBytes, Ki.pos_lo + o, Cfg::kPosBytes, &kv_full[stage]);
+        bulk_g2s(st + 2 * Cfg::kPosBytes, Vi.pos_hi + o, Cfg::kPosBytes, &kv_full[stage]);
+        bulk_g2s(st + 3 * Cfg::kPosBytes, Vi.pos_lo + o, Cfg::kPosBytes, &kv_full[stage]);
+        const long oc = (((long)b * (NP / 32) + j) * 32) * 32;
+        bulk_g2s(st + 4 * Cfg::kPosBytes, Ki.chan_hi + oc, Cfg::kChanBytes, &kv_full[stage]);
+        bulk_g2s(st + 4 * Cfg::kPosBytes + Cfg::kChanBytes, Ki.chan_lo + oc, Cfg::kChanBytes, &kv_full[stage]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 8) {
+    // ======================= S = Q.K^T, dP = dY.V^T issue =======================
+    constexpr uint32_t idesc = umma_idesc_tf32(128, BT);
+    mbar_wait(res_full, 0);
+    tc_fence_after();
+    for (int t = 0; t < TK; t++) {
+      mbar_wait(&kv_full[t % Cfg::kStages], (t / Cfg::kStages) & 1);
+      if (t >= 2) mbar_wait(&s_free[t & 1], ((t - 2) >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t st = smem_u32(sStage + (t % Cfg::kStages) * Cfg::kStageBytes);
+        mma2_ts(tmem + Cfg::kS + (t & 1) * BT, tmem + Cfg::kQh, tmem + Cfg::kQl, st, st + Cfg::kPosBytes,
+                tmem + Cfg::kP + (t & 1) * BT, tmem + Cfg::kYh, tmem + Cfg::kYl, st + 2 * Cfg::kPosBytes,
+                st + 3 * Cfg::kPosBytes, idesc);
+        umma_commit(&sdp_full[t & 1]);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 10) {
+    // ======================= dQ = dS.K issue =======================
+    constexpr uint32_t idesc = umma_idesc_tf32(128, 32);
+    for (int j = 0; j < TK; j++) {
+      mbar_wait(ds_full, j & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t kc = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
+        mma_corr_ts(tmem + Cfg::kAcc, tmem + Cfg::kDhi, tmem + Cfg::kDlo, kc, kc + Cfg::kChanBytes, idesc, true);
+        mma_main_ts(tmem + Cfg::kAcc, tmem + Cfg::kDhi, kc, idesc);
+        umma_commit(dq_done);
+        umma_commit(&kv_empty[j % Cfg::kStages]);    // S(j), dP(j) completed before ds_full(j) could fire
+      }
+      __syncwarp();
+    }
+  } else {
+    // ======================= dS + promotion (thread = query row, half of the key columns) =======================
+    const int quad = warp & 3, half = warp >> 2;
+    const int row = quad * 32 + lane;
+    const int gi = qt * 128 + row;
+    const uint32_t tb = tmem + (((uint32_t)(quad * 32)) << 16) + half * 16;
+    {
+      // this thread's query row, channels [16 half, 16 half + 16) of Q and dY (hi, lo): packed image -> TMEM
+      const long ro = ((long)b * NP + gi) * 32;
+      const float* src[4] = {Qi.pos_hi + ro, Qi.pos_lo + ro, dYi.pos_hi + ro, dYi.pos_lo + ro};
+      const int col[4] = {Cfg::kQh, Cfg::kQl, Cfg::kYh, Cfg::kYl};
+#pragma unroll
+      for (int o = 0; o < 4; o++) {
+        float v[16];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          const float4 x = __ldg(reinterpret_cast<const float4*>(src[o] + (((4 * half + c) ^ (gi & 7)) << 2)));
+          v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
+        }
+        tmem_st16(tb + col[o], v);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(res_full);
+    }
+    const float lse_i = __ldg(lse_pad + (long)b * NP + gi);
+    const float delta_i = __ldg(delta_pad + (long)b * NP + gi);
+    float dq[16];
+#pragma unroll
+    for (int c = 0; c < 16; c++) dq[c] = 0.f;
+    auto promote = [&]() {                                  // channels [16 half, 16 half + 16) of this row
+      float a[16];
+      tmem_ld16(tb + Cfg::kAcc, a);
+      tmem_wait_ld();
+#pragma unroll
+      for (int q = 0; q < 16; q++) dq[q] += a[q];
+    };
+    for (int j = 0; j < TK; j++) {
+      mbar_wait(&sdp_full[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      float a[16], g[16];
+      tmem_ld16(tb + Cfg::kS + (j & 1) * BT, a);
+      tmem_ld16(tb + Cfg::kP + (j & 1) * BT, g);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&s_free[j & 1]);
+      const int j0 = j * BT + half * 16;                      // first key of this thread's columns
+      float hi[16], lo[16];
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        float p = ex2_fast((a[q] - lse_i) * kLog2e);
+        if (j0 + q >= N) p = 0.f;
+        split_tf32(p * (g[q] - delta_i), hi[q], lo[q]);
+      }
+      if (j > 0) {                                           // dQ(j-1) complete: promote, then reuse the dS columns
+        mbar_wait(dq_done, (j - 1) & 1);
+        tc_fence_after();
+        promote();
+      }
+      tmem_st16(tb + Cfg::kDhi, hi);
+      tmem_st16(tb + Cfg::kDlo, lo);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(ds_full);
+    }
+    mbar_wait(dq_done, (TK - 1) & 1);
+    tc_fence_after();
+    promote();
+    if (gi < N) {
+      const int c0 = half * 16;
+      float* dst = dQp + ((long)b * N + gi) * d + c0;
+      if ((d & 3) == 0) {
+#pragma unroll
+        for (int c = 0; c < 16; c += 4)
+          if (c0 + c < d) *reinterpret_cast<float4*>(dst + c) = make_float4(dq[c], dq[c + 1], dq[c + 2], dq[c + 3]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 16; c++)
+          if (c0 + c < d) dst[c] = dq[c];
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 template <typename K>
@@ -1266,6 +1456,16 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   FRN_TRY(set_smem(kern_q, CfgQ::kSmem));
   const dim3 grid_kv(cdiv(NP / 128, NT), B, cdiv(d, 32)), grid_q(cdiv(NP / 128, NT), B);
   const dim3 grid_kv2(NP / 128, B, cdiv(d, 32));
+  static const int dq_design = [] { const char* e = getenv("FRN_DQ_DESIGN"); return (e && e[0] == '1') ? 1 : 2; }();
+  const bool dq2 = dq_design == 2 && DPAD == 32;
+  if (dq2) FRN_TRY(set_smem(attn_dq2_tc_kernel, Dq2Cfg::kSmem));
+  const dim3 grid_q2(NP / 128, B);
+  auto launch_q = [&](cudaStream_t s_) {
+    if (dq2)
+      attn_dq2_tc_kernel<<<grid_q2, Dq2Cfg::kThreads, Dq2Cfg::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+    else
+      kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+  };
   ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
   cudaStream_t side = timing_enabled() ? nullptr : side_stream();
   cudaEvent_t fork = nullptr, join = nullptr;
@@ -1277,7 +1477,7 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   if (side) {
     cudaEventRecord(fork, st);
     cudaStreamWaitEvent(side, fork, 0);
-    kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, side>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+    launch_q(side);
     FRN_LAUNCH_CHECK();
     cudaEventRecord(join, side);
   }
@@ -1294,7 +1494,7 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
     cudaEventDestroy(fork);        // destruction is deferred until the recorded work has completed
     cudaEventDestroy(join);
   } else {
-    kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+    launch_q(st);
     FRN_LAUNCH_CHECK();
   }
   return FRN_OK;
