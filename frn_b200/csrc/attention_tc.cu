@@ -209,8 +209,7 @@ __device__ __forceinline__ void mma2_ts(uint32_t d0, uint32_t a0_hi, uint32_t a0
 // ------------------------------------------------------------------------------------------------
 constexpr int ABM = 128;   // query rows per CTA (UMMA M)
 constexpr int ABN = 64;    // keys per tile
-constexpr int kFwdThreads = 320;   // warps 0-3 / 4-7: softmax groups (even / odd key tiles), 8 MMA issue, 9 producer
-constexpr int kFwdMmaWarp = 8;
+// warps [4g, 4g + 4): softmax group g (key tiles j = g mod kGroups), then one MMA-issue warp and one producer warp
 
 template <int DPAD> struct FwdCfg {
   static constexpr int kSub = DPAD / 32;                    // 32-channel sub-tiles
@@ -218,14 +217,17 @@ template <int DPAD> struct FwdCfg {
   static constexpr int kKBytes = 2 * kSub * ABN * 128;
   static constexpr int kVBytes = 2 * 2 * DPAD * 128;        // two 32-key blocks, hi + lo
   static constexpr int kStageBytes = kKBytes + kVBytes;
-  static constexpr int kStages = DPAD == 32 ? 4 : 2;
+  static constexpr int kGroups = DPAD == 32 ? 3 : 2;        // softmax groups = S / P / Y buffers in TMEM
+  static constexpr int kStages = DPAD == 32 ? 5 : 2;
   static constexpr int kSmem = kQBytes + kStages * kStageBytes + 1024 + 256;
-  // TMEM columns
-  static constexpr int kSMain = 0 /* S, then P hi */, kSSmall = 128 /* P lo */, kYMain = 256;
+  static constexpr int kMmaWarp = 4 * kGroups;
+  static constexpr int kThreads = (4 * kGroups + 3) * 32;   // softmax groups, S issue, producer, P.V issue
+  // TMEM columns (per buffer g: + g * ABN, + g * ABN, + g * DPAD)
+  static constexpr int kSMain = 0 /* S, then P hi */, kSSmall = kGroups * ABN /* P lo */, kYMain = 2 * kGroups * ABN;
 };
 
 template <int DPAD>
-__global__ void __launch_bounds__(kFwdThreads, 1)
+__global__ void __launch_bounds__(FwdCfg<DPAD>::kThreads, 1)
 attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, float* __restrict__ Y,
                    float* __restrict__ lse) {
   using Cfg = FwdCfg<DPAD>;
@@ -237,11 +239,12 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
   uint64_t* q_full = bars;                 // 1
   uint64_t* kv_full = bars + 1;            // kStages
   uint64_t* kv_empty = kv_full + Cfg::kStages;
-  uint64_t* s_full = kv_empty + Cfg::kStages;   // 2
-  uint64_t* p_full = s_full + 2;                // 2
-  uint64_t* y_full = p_full + 2;                // 2
-  uint64_t* y_free = y_full + 2;                // 2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(y_free + 2);
+  constexpr int NG = Cfg::kGroups;
+  uint64_t* s_full = kv_empty + Cfg::kStages;   // NG
+  uint64_t* p_full = s_full + NG;               // NG
+  uint64_t* y_full = p_full + NG;               // NG
+  uint64_t* y_free = y_full + NG;               // NG
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(y_free + NG);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.y, i0 = blockIdx.x * ABM;
@@ -250,19 +253,19 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
   if (tid == 0) {
     mbar_init(q_full, 1);
     for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
-    for (int s = 0; s < 2; s++) {
+    for (int s = 0; s < NG; s++) {
       mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 128);
       mbar_init(&y_full[s], 1); mbar_init(&y_free[s], 128);
     }
     mbar_init_fence();
   }
-  if (warp == kFwdMmaWarp) tmem_alloc<512>(tmem_slot);
+  if (warp == Cfg::kMmaWarp) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == kFwdMmaWarp + 1) {
+  if (warp == Cfg::kMmaWarp + 1) {
     // ======================= bulk-copy producer =======================
     if (lane == 0) {
       mbar_expect_tx(q_full, Cfg::kQBytes);
@@ -290,38 +293,19 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == kFwdMmaWarp) {
-    // ======================= MMA issue (whole warp waits, one elected lane issues) =======================
-    {
-      constexpr uint32_t idesc_s = umma_idesc_tf32(ABM, ABN);
-      constexpr uint32_t idesc_y = umma_idesc_tf32(ABM, DPAD);
-      const uint32_t q_base = smem_u32(sQ);
-      auto issue_pv = [&](int j) {
-        const int buf = j & 1, stage = j % Cfg::kStages;
-        mbar_wait(&p_full[buf], (j >> 1) & 1);
-        if (j >= 2) mbar_wait(&y_free[buf], ((j - 2) >> 1) & 1);
-        tc_fence_after();
-        if (elect_one()) {
-        const uint32_t v_base = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKBytes);
-        const uint32_t p_hi = tmem + Cfg::kSMain + buf * ABN, p_lo = tmem + Cfg::kSSmall + buf * ABN;
-        const uint32_t y_acc = tmem + Cfg::kYMain + buf * DPAD;
-#pragma unroll
-        for (int s = 0; s < 2; s++)
-          mma_corr_ts(y_acc, p_hi + s * 32, p_lo + s * 32, v_base + s * DPAD * 128,
-                      v_base + (2 + s) * DPAD * 128, idesc_y, s == 0);
-#pragma unroll
-        for (int s = 0; s < 2; s++) mma_main_ts(y_acc, p_hi + s * 32, v_base + s * DPAD * 128, idesc_y);
-        umma_commit(&y_full[buf]);
-        umma_commit(&kv_empty[stage]);
-        }
-        __syncwarp();
-      };
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < T; j++) {
-        const int buf = j & 1, stage = j % Cfg::kStages;
-        mbar_wait(&kv_full[stage], (j / Cfg::kStages) & 1);
-        tc_fence_after();
-        if (elect_one()) {
+  } else if (warp == Cfg::kMmaWarp) {
+    // ======================= S = Q.K^T issue (whole warp waits, one elected lane issues) =======================
+    // Two issuing warps (this one: S; warp kMmaWarp + 2: P.V): a single issuing thread spent as long in the
+    // latencies of its barrier waits and issue prologues as the tensor pipe needed for the tile.
+    constexpr uint32_t idesc_s = umma_idesc_tf32(ABM, ABN);
+    const uint32_t q_base = smem_u32(sQ);
+    mbar_wait(q_full, 0);
+    for (int j = 0; j < T; j++) {
+      const int buf = j % NG, stage = j % Cfg::kStages;
+      mbar_wait(&kv_full[stage], (j / Cfg::kStages) & 1);
+      if (j >= NG) mbar_wait(&y_full[buf], ((j - NG) / NG) & 1);   // P.V(j - NG) has read the P this S overwrites
+      tc_fence_after();
+      if (elect_one()) {
         const uint32_t k_base = smem_u32(sKV + stage * Cfg::kStageBytes);
         const uint32_t s_acc = tmem + Cfg::kSMain + buf * ABN;
 #pragma unroll
@@ -332,16 +316,36 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         for (int s = 0; s < Cfg::kSub; s++)
           mma_main_ss(s_acc, q_base + s * ABM * 128, k_base + s * ABN * 128, idesc_s);
         umma_commit(&s_full[buf]);
-        }
-        __syncwarp();
-        if (j >= 1) issue_pv(j - 1);
       }
-      issue_pv(T - 1);
+      __syncwarp();
+    }
+  } else if (warp == Cfg::kMmaWarp + 2) {
+    // ======================= Y += P.V issue =======================
+    constexpr uint32_t idesc_y = umma_idesc_tf32(ABM, DPAD);
+    for (int j = 0; j < T; j++) {
+      const int buf = j % NG, stage = j % Cfg::kStages;
+      mbar_wait(&p_full[buf], (j / NG) & 1);
+      if (j >= NG) mbar_wait(&y_free[buf], ((j - NG) / NG) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t v_base = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKBytes);
+        const uint32_t p_hi = tmem + Cfg::kSMain + buf * ABN, p_lo = tmem + Cfg::kSSmall + buf * ABN;
+        const uint32_t y_acc = tmem + Cfg::kYMain + buf * DPAD;
+#pragma unroll
+        for (int s = 0; s < 2; s++)
+          mma_corr_ts(y_acc, p_hi + s * 32, p_lo + s * 32, v_base + s * DPAD * 128,
+                      v_base + (2 + s) * DPAD * 128, idesc_y, s == 0);
+#pragma unroll
+        for (int s = 0; s < 2; s++) mma_main_ts(y_acc, p_hi + s * 32, v_base + s * DPAD * 128, idesc_y);
+        umma_commit(&y_full[buf]);
+        umma_commit(&kv_empty[stage]);               // S(j) (the other warp) completed before p_full(j) could fire
+      }
+      __syncwarp();
     }
   } else {
     // ======================= softmax + promotion (thread = query row) =======================
-    // Two groups of four warps: group g owns the key tiles j = g (mod 2), i.e. TMEM buffer g, with its own
-    // running max / sum / accumulator, and the two partial softmax states are merged at the end.  With one
+    // NG groups of four warps: group g owns the key tiles j = g (mod NG), i.e. TMEM buffer g, with its own
+    // running max / sum / accumulator, and the partial softmax states are merged at the end.  With one
     // group the four softmax warps (one per scheduler, nothing to hide their latencies behind) took twice as
     // long per tile as the tensor pipe; the groups need no exchange inside the loop.
     const int grp = warp >> 2;
@@ -354,7 +358,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     const int buf = grp;
 
     auto promote = [&](int j, float corr) {            // y = y * corr + Y_tile(j)
-      mbar_wait(&y_full[buf], (j >> 1) & 1);
+      mbar_wait(&y_full[buf], (j / NG) & 1);
       tc_fence_after();
 #pragma unroll
       for (int c0 = 0; c0 < DPAD; c0 += 16) {
@@ -369,9 +373,9 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     };
 
     int jlast = -1;
-    for (int j = grp; j < T; j += 2) {
+    for (int j = grp; j < T; j += NG) {
       const int j0 = j * ABN;
-      mbar_wait(&s_full[buf], (j >> 1) & 1);
+      mbar_wait(&s_full[buf], (j / NG) & 1);
       tc_fence_after();
       float s[ABN];
 #pragma unroll
@@ -415,27 +419,41 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     }
     if (jlast >= 0) promote(jlast, corr_prev);
 
-    // merge the two groups' states (all MMAs are complete once both groups have promoted their last tile)
-    float* xch = reinterpret_cast<float*>(sQ);         // [DPAD + 2][128], the Q tile is dead by now
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    if (grp == 1) {
-      xch[row] = m;
-      xch[128 + row] = l;
+    // merge the groups' states (all MMAs are complete and all stages consumed once every group has promoted
+    // its last tile, so the Q tile and the K / V stages behind it are dead)
+    constexpr int XS = (DPAD + 2) * 128;               // floats per exchanged state: [DPAD + 2][128]
+    float* xch = reinterpret_cast<float*>(sQ);
+    asm volatile("bar.sync 1, %0;" ::"n"(128 * NG) : "memory");
+    if (grp > 0) {
+      float* x = xch + (grp - 1) * XS;
+      x[row] = m;
+      x[128 + row] = l;
 #pragma unroll
-      for (int c = 0; c < DPAD; c++) xch[(2 + c) * 128 + row] = y[c];
+      for (int c = 0; c < DPAD; c++) x[(2 + c) * 128 + row] = y[c];
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(128 * NG) : "memory");
     const int gi = i0 + row;
     if (grp == 0 && gi < N) {
-      const float m1 = xch[row], l1 = xch[128 + row];
-      const float mm = fmaxf(m, m1);
-      const float a0 = ex2_fast((m - mm) * kLog2e), a1 = ex2_fast((m1 - mm) * kLog2e);
-      l = l * a0 + l1 * a1;
+      float mm = m;
+#pragma unroll
+      for (int g = 1; g < NG; g++) mm = fmaxf(mm, xch[(g - 1) * XS + row]);
+      const float a0 = ex2_fast((m - mm) * kLog2e);
+      l *= a0;
+#pragma unroll
+      for (int c = 0; c < DPAD; c++) y[c] *= a0;
+#pragma unroll
+      for (int g = 1; g < NG; g++) {
+        const float* x = xch + (g - 1) * XS;
+        const float ag = ex2_fast((x[row] - mm) * kLog2e);
+        l = fmaf(x[128 + row], ag, l);
+#pragma unroll
+        for (int c = 0; c < DPAD; c++) y[c] = fmaf(x[(2 + c) * 128 + row], ag, y[c]);
+      }
       const float inv = 1.f / l;
       lse[(long)b * N + gi] = mm + logf(l);
       float* dst = Y + ((long)b * N + gi) * d;
 #pragma unroll
-      for (int c = 0; c < DPAD; c++) y[c] = (y[c] * a0 + xch[(2 + c) * 128 + row] * a1) * inv;
+      for (int c = 0; c < DPAD; c++) y[c] *= inv;
       if ((d & 3) == 0) {
 #pragma unroll
         for (int c = 0; c < DPAD; c += 4)
@@ -449,7 +467,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kFwdMmaWarp) tmem_dealloc<512>(tmem);
+  if (warp == Cfg::kMmaWarp) tmem_dealloc<512>(tmem);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1418,7 +1436,7 @@ int launch_fwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   FRN_TRY(set_smem(kern, Cfg::kSmem));
   dim3 grid(cdiv(N, ABM), B);
   ScopedTimer tm(st, FRN_TIME_ATTN_FWD);
-  kern<<<grid, kFwdThreads, Cfg::kSmem, st>>>(N, attn_tc_np(N), d, Q, K, V, Y, lse);
+  kern<<<grid, Cfg::kThreads, Cfg::kSmem, st>>>(N, attn_tc_np(N), d, Q, K, V, Y, lse);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }
