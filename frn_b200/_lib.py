@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfrn_b200.so")
+# FRN_B200_LIB: instrumented builds of the same library (tools/prof_*.py); the default is the in-tree product build
+LIB_PATH = os.environ.get("FRN_B200_LIB") or os.path.join(_HERE, "libfrn_b200.so")
 
 c_float_p = C.c_void_p  # raw device pointers travel as integers
 

@@ -1225,21 +1225,26 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
 // compute warps (16 key columns each), one warp issuing S / dP and one issuing dQ = dS.K.
 // TMEM: S[2] 0,32 | dP[2] 64,96 | dS hi 128, lo 160 | dQ 192 | Q hi 224, lo 256 | dY hi 288, lo 320.
 // ------------------------------------------------------------------------------------------------
-struct Dq2Cfg {
-  static constexpr int kPosBytes = BT * 128;                   // streamed pos tile (32 keys x 32 channels), hi or lo
-  static constexpr int kChanBytes = 32 * 128;                  // streamed chan block (32 channels x 32 keys), hi or lo
+template <int DPAD> struct Dq2Cfg {
+  static constexpr int kSub = DPAD / 32;
+  static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile (32 keys x DPAD channels), hi or lo
+  static constexpr int kChanBytes = DPAD * 128;                // streamed chan block (DPAD channels x 32 keys), hi or lo
   static constexpr int kStageBytes = 4 * kPosBytes + 2 * kChanBytes;   // K pos hi/lo, V pos hi/lo, K chan hi/lo
-  static constexpr int kStages = 8;
+  static constexpr int kStages = DPAD == 32 ? 8 : 4;
   static constexpr int kSmem = kStages * kStageBytes + 1024 + 256;
   static constexpr int kThreads = 11 * 32;                     // warps 0-7 compute, 8 S/dP issue, 9 producer, 10 dQ issue
-  static constexpr int kS = 0, kP = 64, kDhi = 128, kDlo = 160, kAcc = 192, kQh = 224, kQl = 256, kYh = 288, kYl = 320;
+  // TMEM columns (d = 64 uses all 512)
+  static constexpr int kS = 0, kP = 64, kDhi = 128, kDlo = 160, kAcc = 192, kQh = 192 + DPAD, kQl = kQh + DPAD,
+                       kYh = kQl + DPAD, kYl = kYh + DPAD;
+  static constexpr int kCPT = DPAD / 2;                        // channels per compute thread (half a row)
 };
 
-__global__ void __launch_bounds__(Dq2Cfg::kThreads, 1)
+template <int DPAD>
+__global__ void __launch_bounds__(Dq2Cfg<DPAD>::kThreads, 1)
 attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, SplitImage dYi,
                    const float* __restrict__ lse_pad, const float* __restrict__ delta_pad,
                    float* __restrict__ dQp) {
-  using Cfg = Dq2Cfg;
+  using Cfg = Dq2Cfg<DPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sStage = smem;
@@ -1277,12 +1282,15 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         mbar_wait(&kv_empty[stage], phase ^ 1);
         uint8_t* st = sStage + stage * Cfg::kStageBytes;
         mbar_expect_tx(&kv_full[stage], Cfg::kStageBytes);
-        const long o = ((long)b * NP + (long)j * BT) * 32;
-        bulk_g2s(st, Ki.pos_hi + o, Cfg::kPosBytes, &kv_full[stage]);
-        bulk_g2s(st + Cfg::kPosBytes, Ki.pos_lo + o, Cfg::kPosBytes, &kv_full[stage]);
-        bulk_g2s(st + 2 * Cfg::kPosBytes, Vi.pos_hi + o, Cfg::kPosBytes, &kv_full[stage]);
-        bulk_g2s(st + 3 * Cfg::kPosBytes, Vi.pos_lo + o, Cfg::kPosBytes, &kv_full[stage]);
-        const long oc = (((long)b * (NP / 32) + j) * 32) * 32;
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * BT) * 32;
+          bulk_g2s(st + s * BT * 128, Ki.pos_hi + o, BT * 128, &kv_full[stage]);
+          bulk_g2s(st + Cfg::kPosBytes + s * BT * 128, Ki.pos_lo + o, BT * 128, &kv_full[stage]);
+          bulk_g2s(st + 2 * Cfg::kPosBytes + s * BT * 128, Vi.pos_hi + o, BT * 128, &kv_full[stage]);
+          bulk_g2s(st + 3 * Cfg::kPosBytes + s * BT * 128, Vi.pos_lo + o, BT * 128, &kv_full[stage]);
+        }
+        const long oc = (((long)b * (NP / 32) + j) * DPAD) * 32;
         bulk_g2s(st + 4 * Cfg::kPosBytes, Ki.chan_hi + oc, Cfg::kChanBytes, &kv_full[stage]);
         bulk_g2s(st + 4 * Cfg::kPosBytes + Cfg::kChanBytes, Ki.chan_lo + oc, Cfg::kChanBytes, &kv_full[stage]);
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -1299,16 +1307,27 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       tc_fence_after();
       if (elect_one()) {
         const uint32_t st = smem_u32(sStage + (t % Cfg::kStages) * Cfg::kStageBytes);
-        mma2_ts(tmem + Cfg::kS + (t & 1) * BT, tmem + Cfg::kQh, tmem + Cfg::kQl, st, st + Cfg::kPosBytes,
-                tmem + Cfg::kP + (t & 1) * BT, tmem + Cfg::kYh, tmem + Cfg::kYl, st + 2 * Cfg::kPosBytes,
-                st + 3 * Cfg::kPosBytes, idesc);
+        const uint32_t dS = tmem + Cfg::kS + (t & 1) * BT, dP = tmem + Cfg::kP + (t & 1) * BT;
+        // corrections of every 32-channel sub-tile first, then the main terms (one accumulation chain per tile)
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          mma_corr_ts(dS, tmem + Cfg::kQh + 32 * s, tmem + Cfg::kQl + 32 * s, st + s * BT * 128,
+                      st + Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+          mma_corr_ts(dP, tmem + Cfg::kYh + 32 * s, tmem + Cfg::kYl + 32 * s, st + 2 * Cfg::kPosBytes + s * BT * 128,
+                      st + 3 * Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+        }
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          mma_main_ts(dS, tmem + Cfg::kQh + 32 * s, st + s * BT * 128, idesc);
+          mma_main_ts(dP, tmem + Cfg::kYh + 32 * s, st + 2 * Cfg::kPosBytes + s * BT * 128, idesc);
+        }
         umma_commit(&sdp_full[t & 1]);
       }
       __syncwarp();
     }
   } else if (warp == 10) {
     // ======================= dQ = dS.K issue =======================
-    constexpr uint32_t idesc = umma_idesc_tf32(128, 32);
+    constexpr uint32_t idesc = umma_idesc_tf32(128, DPAD);
     for (int j = 0; j < TK; j++) {
       mbar_wait(ds_full, j & 1);
       tc_fence_after();
@@ -1326,21 +1345,29 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     const int quad = warp & 3, half = warp >> 2;
     const int row = quad * 32 + lane;
     const int gi = qt * 128 + row;
-    const uint32_t tb = tmem + (((uint32_t)(quad * 32)) << 16) + half * 16;
+    const uint32_t tl = tmem + (((uint32_t)(quad * 32)) << 16);          // this thread's TMEM lane
+    const uint32_t tb = tl + half * 16;                                  // ... and its 16 key columns
+    constexpr int CPT = Cfg::kCPT;
     {
-      // this thread's query row, channels [16 half, 16 half + 16) of Q and dY (hi, lo): packed image -> TMEM
-      const long ro = ((long)b * NP + gi) * 32;
-      const float* src[4] = {Qi.pos_hi + ro, Qi.pos_lo + ro, dYi.pos_hi + ro, dYi.pos_lo + ro};
+      // this thread's query row, channels [CPT half, CPT half + CPT) of Q and dY (hi, lo): packed image -> TMEM.
+      // Image rows are SWIZZLE_128B per 32-channel sub-tile: chunk c of row n sits at chunk position c ^ (n & 7).
+      const float* src[4] = {Qi.pos_hi, Qi.pos_lo, dYi.pos_hi, dYi.pos_lo};
       const int col[4] = {Cfg::kQh, Cfg::kQl, Cfg::kYh, Cfg::kYl};
 #pragma unroll
       for (int o = 0; o < 4; o++) {
-        float v[16];
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-          const float4 x = __ldg(reinterpret_cast<const float4*>(src[o] + (((4 * half + c) ^ (gi & 7)) << 2)));
-          v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
+        for (int c16 = 0; c16 < CPT / 16; c16++) {
+          const int ch0 = half * CPT + c16 * 16;                         // first channel of this 16-column piece
+          const int sub = ch0 >> 5, chunk0 = (ch0 & 31) >> 2;
+          const float* rp = src[o] + (((long)b * Cfg::kSub + sub) * NP + gi) * 32;
+          float v[16];
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            const float4 x = __ldg(reinterpret_cast<const float4*>(rp + (((chunk0 + c) ^ (gi & 7)) << 2)));
+            v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
+          }
+          tmem_st16(tl + col[o] + ch0, v);
         }
-        tmem_st16(tb + col[o], v);
       }
       tmem_wait_st();
       tc_fence_before();
@@ -1348,15 +1375,18 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     }
     const float lse_i = __ldg(lse_pad + (long)b * NP + gi);
     const float delta_i = __ldg(delta_pad + (long)b * NP + gi);
-    float dq[16];
+    float dq[CPT];
 #pragma unroll
-    for (int c = 0; c < 16; c++) dq[c] = 0.f;
-    auto promote = [&]() {                                  // channels [16 half, 16 half + 16) of this row
-      float a[16];
-      tmem_ld16(tb + Cfg::kAcc, a);
-      tmem_wait_ld();
+    for (int c = 0; c < CPT; c++) dq[c] = 0.f;
+    auto promote = [&]() {                                  // channels [CPT half, CPT half + CPT) of this row
 #pragma unroll
-      for (int q = 0; q < 16; q++) dq[q] += a[q];
+      for (int c0 = 0; c0 < CPT; c0 += 16) {
+        float a[16];
+        tmem_ld16(tl + Cfg::kAcc + half * CPT + c0, a);
+        tmem_wait_ld();
+#pragma unroll
+        for (int q = 0; q < 16; q++) dq[c0 + q] += a[q];
+      }
     };
     for (int j = 0; j < TK; j++) {
       mbar_wait(&sdp_full[j & 1], (j >> 1) & 1);
@@ -1390,15 +1420,15 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
     tc_fence_after();
     promote();
     if (gi < N) {
-      const int c0 = half * 16;
+      const int c0 = half * CPT;
       float* dst = dQp + ((long)b * N + gi) * d + c0;
       if ((d & 3) == 0) {
 #pragma unroll
-        for (int c = 0; c < 16; c += 4)
+        for (int c = 0; c < CPT; c += 4)
           if (c0 + c < d) *reinterpret_cast<float4*>(dst + c) = make_float4(dq[c], dq[c + 1], dq[c + 2], dq[c + 3]);
       } else {
 #pragma unroll
-        for (int c = 0; c < 16; c++)
+        for (int c = 0; c < CPT; c++)
           if (c0 + c < d) dst[c] = dq[c];
       }
     }
@@ -1475,12 +1505,13 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   const dim3 grid_kv(cdiv(NP / 128, NT), B, cdiv(d, 32)), grid_q(cdiv(NP / 128, NT), B);
   const dim3 grid_kv2(NP / 128, B, cdiv(d, 32));
   static const int dq_design = [] { const char* e = getenv("FRN_DQ_DESIGN"); return (e && e[0] == '1') ? 1 : 2; }();
-  const bool dq2 = dq_design == 2 && DPAD == 32;
-  if (dq2) FRN_TRY(set_smem(attn_dq2_tc_kernel, Dq2Cfg::kSmem));
+  const bool dq2 = dq_design == 2;
+  if (dq2) FRN_TRY(set_smem(attn_dq2_tc_kernel<DPAD>, Dq2Cfg<DPAD>::kSmem));
   const dim3 grid_q2(NP / 128, B);
   auto launch_q = [&](cudaStream_t s_) {
     if (dq2)
-      attn_dq2_tc_kernel<<<grid_q2, Dq2Cfg::kThreads, Dq2Cfg::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+      attn_dq2_tc_kernel<DPAD><<<grid_q2, Dq2Cfg<DPAD>::kThreads, Dq2Cfg<DPAD>::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad,
+                                                                                              delta_pad, dQp);
     else
       kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
   };

@@ -124,8 +124,21 @@ col_partial_sum_kernel(int N, int d, int rows_per_block, const float* __restrict
   const int lanes = 256 / d * d;                 // threads used: a whole number of rows per pass
   const int tid = threadIdx.x, k = tid % d, r = tid / d, rstep = 256 / d;
   float s = 0.f;
-  if (tid < lanes)
-    for (int n = n0 + r; n < n1; n += rstep) s += __ldg(x + ((long)b * N + n) * d + k);
+  if (tid < lanes) {
+    // four independent partial sums: the loads of a thread are 128 * rstep bytes apart and a single dependent
+    // accumulator kept only one or two of them in flight
+    const float* xp = x + (long)b * N * d + k;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int n = n0 + r;
+    for (; n + 3 * rstep < n1; n += 4 * rstep) {
+      s0 += __ldg(xp + (long)n * d);
+      s1 += __ldg(xp + (long)(n + rstep) * d);
+      s2 += __ldg(xp + (long)(n + 2 * rstep) * d);
+      s3 += __ldg(xp + (long)(n + 3 * rstep) * d);
+    }
+    for (; n < n1; n += rstep) s0 += __ldg(xp + (long)n * d);
+    s = (s0 + s1) + (s2 + s3);
+  }
   red[tid] = tid < lanes ? s : 0.f;
   __syncthreads();
   if (tid < d) {
