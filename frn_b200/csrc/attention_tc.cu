@@ -1219,6 +1219,250 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
 }
 
 // ------------------------------------------------------------------------------------------------
+// backward, part 2 for 32 < d <= 64: the second design with ALL 64 channels of dV / dK in one CTA (the
+// ping-pong kernel ran one CTA per 32-channel group and recomputed S^T / dP^T in each).  TMEM holds K
+// (tf32 hi / lo, 128 columns) as the A operand of S^T; V stays in shared memory (dP^T in the SS form) -
+// there is no room for both:
+//   S^T[2] 0,32 | dP^T[2] 64,96 | P^T hi 128, lo 160 | dS^T hi 192, lo 224 | dV 256 (64) | dK 320 (64) |
+//   K hi 384 (64) | K lo 448 (64)                                                       = 512 columns.
+// Per 32-query step: 24 TS (S^T) + 24 SS (dP^T) at N = 32 and 2 x 12 TS at N = 64 = 2112 cycles of
+// tcgen05.mma time against 2 x 2304 in the ping-pong kernel.
+// ------------------------------------------------------------------------------------------------
+struct Dkv3Cfg {
+  static constexpr int DPAD = 64, kSub = 2;
+  static constexpr int kOperBytes = kSub * 128 * 128;          // V pos tile (128 keys), hi or lo
+  static constexpr int kResBytes = 2 * kOperBytes;             // V hi, V lo
+  static constexpr int kPosBytes = kSub * BT * 128;            // streamed pos tile, hi or lo
+  static constexpr int kChanBytes = DPAD * 128;                // streamed chan block (64 channels x 32 queries), hi or lo
+  static constexpr int kStageBytes = 4 * kPosBytes + 4 * kChanBytes;  // Q pos, dY pos, dY chan, Q chan (hi/lo each)
+  static constexpr int kStages = 2;
+  static constexpr int kRowBytes = kStages * 2 * BT * 4;
+  static constexpr int kSmem = kResBytes + kStages * kStageBytes + kRowBytes + 1024 + 256;
+  static constexpr int kThreads = 11 * 32;                     // warps 0-7 compute, 8 S^T/dP^T issue, 9 producer, 10 dV/dK issue
+  static constexpr int kS = 0, kP = 64, kPhi = 128, kPlo = 160, kDhi = 192, kDlo = 224, kV = 256, kK = 320,
+                       kKh = 384, kKl = 448;
+};
+
+__global__ void __launch_bounds__(Dkv3Cfg::kThreads, 1)
+attn_dkv3_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, SplitImage dYi,
+                    const float* __restrict__ lse_pad, const float* __restrict__ delta_pad,
+                    float* __restrict__ dKp, float* __restrict__ dVp) {
+  using Cfg = Dkv3Cfg;
+  constexpr int DPAD = Cfg::DPAD;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sRes = smem;
+  uint8_t* sStage = smem + Cfg::kResBytes;
+  float* sRows = reinterpret_cast<float*>(sStage + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sRows) + Cfg::kRowBytes);
+  uint64_t* res_full = bars;                       // 1   K is in TMEM (256 arrivals)
+  uint64_t* v_full = res_full + 1;                 // 1   V is in shared memory
+  uint64_t* q_full = v_full + 1;                   // kStages
+  uint64_t* q_empty = q_full + Cfg::kStages;       // kStages
+  uint64_t* sdp_full = q_empty + Cfg::kStages;     // 2
+  uint64_t* s_free = sdp_full + 2;                 // 2
+  uint64_t* ds_full = s_free + 2;                  // 1
+  uint64_t* pv_done = ds_full + 1;                 // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, kt = blockIdx.x;
+  const int TQ = (N + BT - 1) / BT;
+
+  if (tid == 0) {
+    mbar_init(res_full, 256); mbar_init(v_full, 1); mbar_init(ds_full, 256); mbar_init(pv_done, 1);
+    for (int s = 0; s < 2; s++) { mbar_init(&sdp_full[s], 1); mbar_init(&s_free[s], 256); }
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+    mbar_init_fence();
+  }
+  if (warp == 8) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 9) {
+    // ======================= bulk-copy producer =======================
+    if (lane == 0) {
+      mbar_expect_tx(v_full, Cfg::kResBytes);
+#pragma unroll
+      for (int s = 0; s < Cfg::kSub; s++) {
+        const long o = (((long)b * Cfg::kSub + s) * NP + (long)kt * 128) * 32;
+        bulk_g2s(sRes + s * 16384, Vi.pos_hi + o, 16384, v_full);
+        bulk_g2s(sRes + Cfg::kOperBytes + s * 16384, Vi.pos_lo + o, 16384, v_full);
+      }
+      int stage = 0; uint32_t phase = 0;
+      for (int j = 0; j < TQ; j++) {
+        mbar_wait(&q_empty[stage], phase ^ 1);
+        uint8_t* st = sStage + stage * Cfg::kStageBytes;
+        mbar_expect_tx(&q_full[stage], Cfg::kStageBytes + 2 * BT * 4);
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + (long)j * BT) * 32;
+          bulk_g2s(st + s * BT * 128, Qi.pos_hi + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + Cfg::kPosBytes + s * BT * 128, Qi.pos_lo + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + 2 * Cfg::kPosBytes + s * BT * 128, dYi.pos_hi + o, BT * 128, &q_full[stage]);
+          bulk_g2s(st + 3 * Cfg::kPosBytes + s * BT * 128, dYi.pos_lo + o, BT * 128, &q_full[stage]);
+        }
+        const long oc = (((long)b * (NP / 32) + j) * DPAD) * 32;
+        uint8_t* sc = st + 4 * Cfg::kPosBytes;
+        bulk_g2s(sc, dYi.chan_hi + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + Cfg::kChanBytes, dYi.chan_lo + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + 2 * Cfg::kChanBytes, Qi.chan_hi + oc, Cfg::kChanBytes, &q_full[stage]);
+        bulk_g2s(sc + 3 * Cfg::kChanBytes, Qi.chan_lo + oc, Cfg::kChanBytes, &q_full[stage]);
+        float* rw = sRows + stage * 2 * BT;
+        bulk_g2s(rw, lse_pad + (long)b * NP + (long)j * BT, BT * 4, &q_full[stage]);
+        bulk_g2s(rw + BT, delta_pad + (long)b * NP + (long)j * BT, BT * 4, &q_full[stage]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 8) {
+    // ======================= S^T = K.Q^T (TS), dP^T = V.dY^T (SS) issue =======================
+    constexpr uint32_t idesc = umma_idesc_tf32(128, BT);
+    const uint32_t r = smem_u32(sRes);
+    mbar_wait(res_full, 0);
+    mbar_wait(v_full, 0);
+    tc_fence_after();
+    for (int t = 0; t < TQ; t++) {
+      mbar_wait(&q_full[t % Cfg::kStages], (t / Cfg::kStages) & 1);
+      if (t >= 2) mbar_wait(&s_free[t & 1], ((t - 2) >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t st = smem_u32(sStage + (t % Cfg::kStages) * Cfg::kStageBytes);
+        const uint32_t dS = tmem + Cfg::kS + (t & 1) * BT, dP = tmem + Cfg::kP + (t & 1) * BT;
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          mma_corr_ts(dS, tmem + Cfg::kKh + 32 * s, tmem + Cfg::kKl + 32 * s, st + s * BT * 128,
+                      st + Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+          mma_corr_ss(dP, r + s * 16384, r + Cfg::kOperBytes + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128,
+                      st + 3 * Cfg::kPosBytes + s * BT * 128, idesc, s == 0);
+        }
+#pragma unroll
+        for (int s = 0; s < Cfg::kSub; s++) {
+          mma_main_ts(dS, tmem + Cfg::kKh + 32 * s, st + s * BT * 128, idesc);
+          mma_main_ss(dP, r + s * 16384, st + 2 * Cfg::kPosBytes + s * BT * 128, idesc);
+        }
+        umma_commit(&sdp_full[t & 1]);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 10) {
+    // ======================= dV = P^T.dY, dK = dS^T.Q issue (N = 64 channels) =======================
+    constexpr uint32_t idesc = umma_idesc_tf32(128, DPAD);
+    for (int j = 0; j < TQ; j++) {
+      mbar_wait(ds_full, j & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sc = smem_u32(sStage + (j % Cfg::kStages) * Cfg::kStageBytes + 4 * Cfg::kPosBytes);
+        mma2_ts(tmem + Cfg::kV, tmem + Cfg::kPhi, tmem + Cfg::kPlo, sc, sc + Cfg::kChanBytes,
+                tmem + Cfg::kK, tmem + Cfg::kDhi, tmem + Cfg::kDlo, sc + 2 * Cfg::kChanBytes, sc + 3 * Cfg::kChanBytes,
+                idesc);
+        umma_commit(pv_done);
+        umma_commit(&q_empty[j % Cfg::kStages]);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ======================= P^T, dS^T + promotion (thread = key row) =======================
+    const int quad = warp & 3, half = warp >> 2;
+    const int row = quad * 32 + lane;
+    const int gj = kt * 128 + row;
+    const uint32_t tl = tmem + (((uint32_t)(quad * 32)) << 16);   // this thread's TMEM lane
+    const uint32_t tb = tl + half * 16;                           // ... and its 16 query columns
+    {
+      // K (hi, lo), channels [32 half, 32 half + 32) of this key row: packed image (sub-tile = half) -> TMEM
+      const float* src[2] = {Ki.pos_hi, Ki.pos_lo};
+      const int col[2] = {Cfg::kKh, Cfg::kKl};
+#pragma unroll
+      for (int o = 0; o < 2; o++) {
+        const float* rp = src[o] + (((long)b * Cfg::kSub + half) * NP + gj) * 32;
+#pragma unroll
+        for (int c16 = 0; c16 < 2; c16++) {
+          float v[16];
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            const float4 x = __ldg(reinterpret_cast<const float4*>(rp + (((4 * c16 + c) ^ (gj & 7)) << 2)));
+            v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
+          }
+          tmem_st16(tl + col[o] + 32 * half + 16 * c16, v);
+        }
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(res_full);
+    }
+    float dv[32], dk[32];                                    // channels [32 half, 32 half + 32) of this row
+#pragma unroll
+    for (int c = 0; c < 32; c++) { dv[c] = 0.f; dk[c] = 0.f; }
+    auto promote = [&]() {
+#pragma unroll
+      for (int c0 = 0; c0 < 32; c0 += 16) {
+        float a[16], s2[16];
+        tmem_ld16(tl + Cfg::kV + 32 * half + c0, a);
+        tmem_ld16(tl + Cfg::kK + 32 * half + c0, s2);
+        tmem_wait_ld();
+#pragma unroll
+        for (int q = 0; q < 16; q++) { dv[c0 + q] += a[q]; dk[c0 + q] += s2[q]; }
+      }
+    };
+    for (int j = 0; j < TQ; j++) {
+      mbar_wait(&sdp_full[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      float a[16], g[16];
+      tmem_ld16(tb + Cfg::kS + (j & 1) * BT, a);
+      tmem_ld16(tb + Cfg::kP + (j & 1) * BT, g);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&s_free[j & 1]);
+      mbar_wait(&q_full[j % Cfg::kStages], (j / Cfg::kStages) & 1);   // lse / delta of the tile have landed
+      const float* rw = sRows + (j % Cfg::kStages) * 2 * BT + half * 16;
+      float phi[16], plo[16], dhi[16], dlo[16];
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        const float p = ex2_fast((a[q] - rw[q]) * kLog2e);
+        split_tf32(p, phi[q], plo[q]);
+        split_tf32(p * (g[q] - rw[BT + q]), dhi[q], dlo[q]);
+      }
+      if (j > 0) {
+        mbar_wait(pv_done, (j - 1) & 1);
+        tc_fence_after();
+        promote();
+      }
+      tmem_st16(tb + Cfg::kPhi, phi);
+      tmem_st16(tb + Cfg::kPlo, plo);
+      tmem_st16(tb + Cfg::kDhi, dhi);
+      tmem_st16(tb + Cfg::kDlo, dlo);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(ds_full);
+    }
+    mbar_wait(pv_done, (TQ - 1) & 1);
+    tc_fence_after();
+    promote();
+    if (gj < N) {
+      const int c0 = half * 32;
+      float* dv_dst = dVp + ((long)b * N + gj) * d + c0;
+      float* dk_dst = dKp + ((long)b * N + gj) * d + c0;
+      if ((d & 3) == 0) {
+#pragma unroll
+        for (int c = 0; c < 32; c += 4)
+          if (c0 + c < d) {
+            *reinterpret_cast<float4*>(dv_dst + c) = make_float4(dv[c], dv[c + 1], dv[c + 2], dv[c + 3]);
+            *reinterpret_cast<float4*>(dk_dst + c) = make_float4(dk[c], dk[c + 1], dk[c + 2], dk[c + 3]);
+          }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+          if (c0 + c < d) { dv_dst[c] = dv[c]; dk_dst[c] = dk[c]; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
 // backward, part 1, second design (d <= 32): the mirror image of attn_dkv2_tc_kernel.  CTA = 128 queries
 // (lanes = queries), Q and dY resident in TMEM as the A operands of S = Q.K^T and dP = dY.V^T (TS form),
 // 32-key tiles streamed through shared memory (K pos, V pos, K chan), S / dP double buffered, eight
@@ -1532,7 +1776,11 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
   }
   {
     ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
-    if (dkv_design == 2 && DPAD == 32)    // d = 64 leaves room for two query stages only: the ping-pong design is faster there
+    if (dkv_design == 2 && DPAD == 64) {
+      FRN_TRY(set_smem(attn_dkv3_tc_kernel, Dkv3Cfg::kSmem));
+      attn_dkv3_tc_kernel<<<dim3(NP / 128, B), Dkv3Cfg::kThreads, Dkv3Cfg::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad,
+                                                                                          delta_pad, dKp, dVp);
+    } else if (dkv_design == 2)
       kern_kv2<<<grid_kv2, CfgK2::kThreads, CfgK2::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
     else
       kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
