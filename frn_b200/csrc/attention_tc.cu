@@ -217,13 +217,20 @@ template <int DPAD> struct FwdCfg {
   static constexpr int kKBytes = 2 * kSub * ABN * 128;
   static constexpr int kVBytes = 2 * 2 * DPAD * 128;        // two 32-key blocks, hi + lo
   static constexpr int kStageBytes = kKBytes + kVBytes;
-  static constexpr int kGroups = DPAD == 32 ? 3 : 2;        // softmax groups = S / P / Y buffers in TMEM
+#ifndef FRN_FWD_TS32
+#define FRN_FWD_TS32 1
+#endif
+  // Q resident in TMEM as the A operand of S (TS form: N / 2 cycles per instruction instead of 32 + N / 4);
+  // it costs 2 DPAD columns, which leaves room for two softmax groups
+  static constexpr bool kTS = DPAD == 64 || FRN_FWD_TS32;
+  static constexpr int kGroups = (DPAD == 32 && !kTS) ? 3 : 2;   // softmax groups = S / P / Y buffers in TMEM
   static constexpr int kStages = DPAD == 32 ? 5 : 2;
   static constexpr int kSmem = kQBytes + kStages * kStageBytes + 1024 + 256;
   static constexpr int kMmaWarp = 4 * kGroups;
   static constexpr int kThreads = (4 * kGroups + 3) * 32;   // softmax groups, S issue, producer, P.V issue
   // TMEM columns (per buffer g: + g * ABN, + g * ABN, + g * DPAD)
   static constexpr int kSMain = 0 /* S, then P hi */, kSSmall = kGroups * ABN /* P lo */, kYMain = 2 * kGroups * ABN;
+  static constexpr int kQh = kYMain + kGroups * DPAD, kQl = kQh + DPAD;     // kTS only
 };
 
 template <int DPAD>
@@ -251,7 +258,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
   const int T = (N + ABN - 1) / ABN;
 
   if (tid == 0) {
-    mbar_init(q_full, 1);
+    mbar_init(q_full, Cfg::kTS ? 128 * NG : 1);
     for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
     for (int s = 0; s < NG; s++) {
       mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 128);
@@ -268,12 +275,14 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
   if (warp == Cfg::kMmaWarp + 1) {
     // ======================= bulk-copy producer =======================
     if (lane == 0) {
-      mbar_expect_tx(q_full, Cfg::kQBytes);
+      if (!Cfg::kTS) {
+        mbar_expect_tx(q_full, Cfg::kQBytes);
 #pragma unroll
-      for (int s = 0; s < Cfg::kSub; s++) {
-        const long o = (((long)b * Cfg::kSub + s) * NP + i0) * 32;
-        bulk_g2s(sQ + s * ABM * 128, Qi.pos_hi + o, ABM * 128, q_full);
-        bulk_g2s(sQ + (Cfg::kSub + s) * ABM * 128, Qi.pos_lo + o, ABM * 128, q_full);
+        for (int s = 0; s < Cfg::kSub; s++) {
+          const long o = (((long)b * Cfg::kSub + s) * NP + i0) * 32;
+          bulk_g2s(sQ + s * ABM * 128, Qi.pos_hi + o, ABM * 128, q_full);
+          bulk_g2s(sQ + (Cfg::kSub + s) * ABM * 128, Qi.pos_lo + o, ABM * 128, q_full);
+        }
       }
       int stage = 0; uint32_t phase = 0;
       for (int j = 0; j < T; j++) {
@@ -308,6 +317,15 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       if (elect_one()) {
         const uint32_t k_base = smem_u32(sKV + stage * Cfg::kStageBytes);
         const uint32_t s_acc = tmem + Cfg::kSMain + buf * ABN;
+        if (Cfg::kTS) {
+#pragma unroll
+          for (int s = 0; s < Cfg::kSub; s++)
+            mma_corr_ts(s_acc, tmem + Cfg::kQh + 32 * s, tmem + Cfg::kQl + 32 * s, k_base + s * ABN * 128,
+                        k_base + (Cfg::kSub + s) * ABN * 128, idesc_s, s == 0);
+#pragma unroll
+          for (int s = 0; s < Cfg::kSub; s++)
+            mma_main_ts(s_acc, tmem + Cfg::kQh + 32 * s, k_base + s * ABN * 128, idesc_s);
+        } else {
 #pragma unroll
         for (int s = 0; s < Cfg::kSub; s++)
           mma_corr_ss(s_acc, q_base + s * ABM * 128, q_base + (Cfg::kSub + s) * ABM * 128,
@@ -315,6 +333,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
 #pragma unroll
         for (int s = 0; s < Cfg::kSub; s++)
           mma_main_ss(s_acc, q_base + s * ABM * 128, k_base + s * ABN * 128, idesc_s);
+        }
         umma_commit(&s_full[buf]);
       }
       __syncwarp();
@@ -356,6 +375,29 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
 #pragma unroll
     for (int c = 0; c < DPAD; c++) y[c] = 0.f;
     const int buf = grp;
+    if (Cfg::kTS) {
+      // this thread's query row of Q into TMEM: group 0 the hi plane, group 1 the lo plane (packed image rows are
+      // SWIZZLE_128B per 32-channel sub-tile: chunk c of row n sits at chunk position c ^ (n & 7))
+      const int gq = i0 + row;
+      const float* plane = grp == 0 ? Qi.pos_hi : Qi.pos_lo;
+      const uint32_t col = grp == 0 ? Cfg::kQh : Cfg::kQl;
+      if (grp < 2) {
+#pragma unroll
+        for (int c16 = 0; c16 < DPAD / 16; c16++) {
+          const float* rp = plane + (((long)b * Cfg::kSub + (c16 >> 1)) * NP + gq) * 32;
+          float v[16];
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            const float4 x = __ldg(reinterpret_cast<const float4*>(rp + (((4 * (c16 & 1) + c) ^ (gq & 7)) << 2)));
+            v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
+          }
+          tmem_st16(tmem + lane_base + col + 16 * c16, v);
+        }
+        tmem_wait_st();
+      }
+      tc_fence_before();
+      mbar_arrive(q_full);
+    }
 
     auto promote = [&](int j, float corr) {            // y = y * corr + Y_tile(j)
       mbar_wait(&y_full[buf], (j / NG) & 1);
