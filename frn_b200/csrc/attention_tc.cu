@@ -15,11 +15,17 @@
 // of ~3e-9 per K = 8 step (tools/tc_error_vs_k.py).  No accumulation chain here is longer than 8
 // steps: every tile product is promoted from TMEM into fp32 register accumulators.
 //
-// Kernels (d <= 64; larger d goes through the GEMM engine, see fusion.cu):
-//   attn_fwd_tc_kernel   CTA = 128 queries, 64-key tiles, double-buffered S, online softmax
-//   attn_dq_tc_kernel    CTA = NQ x 128 queries (ping-pong), 32-key tiles: S, dP -> dS -> dQ
-//   attn_dkv_tc_kernel   CTA = NKT x 128 keys (ping-pong), 32-query tiles: S^T, dP^T -> P^T, dS^T
-//                        -> dV, dK   (d = 64: one 32-channel half of dV / dK per CTA)
+// Kernels (d <= 64; larger d goes through the GEMM engine, see fusion.cu).  All of them: CTA = one tile of 128
+// rows (= TMEM lanes), the resident operand of that tile held in TMEM as tf32 hi / lo and used as the A operand
+// (TS form: a tcgen05.mma then costs N / 2 cycles instead of 32 + N / 4, tools/mma_cost_probe.cu), the other
+// operands streamed through shared memory, score accumulators double buffered in TMEM, separate issuing
+// warps for the score products and for the output products, one bulk-copy producer lane.
+//   attn_fwd_tc_kernel    128 queries, 64-key tiles, softmax groups on alternate key tiles (merged at the end)
+//   attn_dq2_tc_kernel    128 queries, 32-key tiles: S, dP -> dS -> dQ           (eight compute warps)
+//   attn_dkv2_tc_kernel   128 keys, 32-query tiles: S^T, dP^T -> P^T, dS^T -> dV, dK   (d <= 32)
+//   attn_dkv3_tc_kernel   the same for 32 < d <= 64 (K in TMEM, V in shared memory: 512 columns are full)
+//   attn_dq_tc_kernel / attn_dkv_tc_kernel   the first (ping-pong, single issuing warp) designs, kept behind
+//                         FRN_DQ_DESIGN=1 / FRN_DKV_DESIGN=1 for comparison
 // No atomics anywhere: the backward is deterministic.
 #include <mutex>
 #include <cstdlib>

@@ -86,6 +86,9 @@ CASES = [
     ("d32_ddd17_L1", 1, 32, 5655, 1.2),
     ("d64_ddd17_L2", 2, 64, 1452, 0.9),
     ("d32_multi_tile_pairs", 1, 32, 128 * 5 + 3, 1.0),
+    ("d64_dsec_L2", 1, 64, 4800, 0.9),
+    ("d33_first_odd_width_above_32", 2, 33, 100, 1.0),
+    ("d32_two_key_tiles_one_query_step", 1, 32, 31, 1.0),
 ]
 
 
