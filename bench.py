@@ -57,8 +57,8 @@ def measured_peaks():
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
-    capture (profiles/r1_c_attn_ncu_full.txt: B = 8, DSEC level 1, the shape the roofline line is quoted on)."""
-    path = os.path.join(ROOT, "profiles", "r1_c_attn_ncu_full.txt")
+    capture (profiles/r1_d_attn_ncu_full.txt: B = 8, DSEC level 1, the shape the roofline line is quoted on)."""
+    path = os.path.join(ROOT, "profiles", "r1_d_attn_ncu_full.txt")
     try:
         total, on, unit = 0.0, False, {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
         for line in open(path):
@@ -67,7 +67,7 @@ def ncu_traffic(kernel):
             elif on and ("dram__bytes_read.sum " in line or "dram__bytes_write.sum " in line):
                 parts = line.split()
                 total += float(parts[1]) * unit.get(parts[2], 1.0)
-        return (total if total > 0 else None), "profiles/r1_c_attn_ncu_full.txt (B=8, DSEC level 1, one launch)"
+        return (total if total > 0 else None), "profiles/r1_d_attn_ncu_full.txt (B=8, DSEC level 1, one launch)"
     except OSError:
         return None, "no ncu capture found"
 
@@ -304,7 +304,7 @@ def run_ours(args):
     t_fwd = classes["attn_fwd"]["ms"] / 1e3 / args.steps
     t_dkv = classes["attn_dkv"]["ms"] / 1e3 / args.steps
     if tc_attn and t_dkv > 0:
-        kname, ach, share = ("attn_dkv2_tc_kernel<32> / attn_dkv_tc_kernel<64,1> (tcgen05 attention backward, dK/dV half, levels 1-2)",
+        kname, ach, share = ("attn_dkv2_tc_kernel<32> / attn_dkv3_tc_kernel (tcgen05 attention backward, dK/dV half, levels 1-2)",
                              fl_dkv / t_dkv / 1e12, classes["attn_dkv"]["ms"] / ms_prof)
         nl = max(classes["attn_dkv"]["launches"], 1)
         per_launch = {"flops_per_launch": fl_dkv * args.steps / nl, "ms_per_launch": classes["attn_dkv"]["ms"] / nl}
