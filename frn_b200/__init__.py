@@ -3,10 +3,11 @@
 Drop-in replacements for retinanet/fusion.py, retinanet/Attention.py and
 retinanet/AdaIN.py of JinkaiLiu/FRN; see DESIGN.md and INTEGRATION.md.
 """
-from .modules import AdaIN_block, CrossAttentionBlock, REFusion, c2_xavier_fill, fusion_parameters
+from .modules import (AdaIN_block, Conv1x1, CrossAttentionBlock, REFusion, c2_xavier_fill,
+                      convert_fpn_laterals, fusion_parameters)
 from .patch import patch_reference
 from .dist import allreduce_fusion_grads, shard_batch
 
-__all__ = ["AdaIN_block", "CrossAttentionBlock", "REFusion", "c2_xavier_fill", "fusion_parameters",
+__all__ = ["AdaIN_block", "CrossAttentionBlock", "REFusion", "c2_xavier_fill", "fusion_parameters", "Conv1x1", "convert_fpn_laterals",
            "patch_reference", "allreduce_fusion_grads", "shard_batch"]
 __version__ = "0.1.0"

@@ -69,6 +69,9 @@ _SIGNATURES = {
     "frn_attn_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "frn_attn_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_size_t]),
     "frn_attn_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 10 + [C.c_size_t]),
+    "frn_conv1x1_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
+    "frn_conv1x1_forward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 5 + [C.c_size_t]),
+    "frn_conv1x1_backward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 7 + [C.c_size_t]),
     "frn_set_gemm_engine": (None, [C.c_int]),
     "frn_get_gemm_engine": (C.c_int, []),
     "frn_set_attn_engine": (None, [C.c_int]),

@@ -685,5 +685,37 @@ int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, con
   });
 }
 
+// ---- 1x1 convolution (FPN laterals, model.py:28-40) ---------------------------------
+static int conv1x1_fwd_body(Ctx& c, int B, int Cin, int Cout, int N, const float* x, const float* w,
+                            const float* bias, float* y) {
+  return conv1x1(c, w, bias, x, y, B, Cout, Cin, N);
+}
+static int conv1x1_bwd_body(Ctx& c, int B, int Cin, int Cout, int N, const float* x, const float* w,
+                            const float* dy, float* dx, float* dw, float* db) {
+  if (dx) FRN_TRY(conv1x1_dgrad(c, w, dy, N, 1, (long)Cout * N, dx, B, Cout, Cin, N, 0));
+  return conv1x1_wgrad(c, dy, N, 1, (long)Cout * N, x, dw, db, B, Cout, Cin, N);
+}
+size_t frn_conv1x1_workspace_bytes(int B, int Cin, int Cout, int N) {
+  if (B <= 0 || Cin <= 0 || Cout <= 0 || N <= 0) return 0;
+  size_t f = dry_bytes([&](Ctx& c) { return conv1x1_fwd_body(c, B, Cin, Cout, N, nullptr, nullptr, nullptr, nullptr); });
+  size_t b = dry_bytes([&](Ctx& c) {
+    return conv1x1_bwd_body(c, B, Cin, Cout, N, nullptr, nullptr, nullptr, (float*)16, nullptr, (float*)16);
+  });
+  return f > b ? f : b;
+}
+int frn_conv1x1_forward(void* stream, int B, int Cin, int Cout, int N, const float* x, const float* w,
+                        const float* bias, float* y, void* ws, size_t ws_bytes) {
+  if (B <= 0 || Cin <= 0 || Cout <= 0 || N <= 0) return FRN_ERR_BAD_SHAPE;
+  if (!x || !w || !y) return FRN_ERR_NULL_POINTER;
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) { return conv1x1_fwd_body(c, B, Cin, Cout, N, x, w, bias, y); });
+}
+int frn_conv1x1_backward(void* stream, int B, int Cin, int Cout, int N, const float* x, const float* w,
+                         const float* dy, float* dx, float* dw, float* db, void* ws, size_t ws_bytes) {
+  if (B <= 0 || Cin <= 0 || Cout <= 0 || N <= 0) return FRN_ERR_BAD_SHAPE;
+  if (!x || !w || !dy || !dw) return FRN_ERR_NULL_POINTER;
+  return with_ctx(stream, ws, ws_bytes,
+                  [&](Ctx& c) { return conv1x1_bwd_body(c, B, Cin, Cout, N, x, w, dy, dx, dw, db); });
+}
+
 }  // extern "C"
 #pragma GCC visibility pop

@@ -8,6 +8,7 @@ Reference semantics:
     adain / mean_std   retinanet/AdaIN.py:7-26
     cross_attention    retinanet/Attention.py:21-36
     refusion           retinanet/fusion.py:20-36
+    conv1x1            nn.Conv2d(Cin, Cout, 1) of the FPN laterals, retinanet/model.py:28-40 (row f1)
 """
 from __future__ import annotations
 
@@ -215,3 +216,53 @@ class _REFusionFn(torch.autograd.Function):
 def refusion(rgb, evt, conv0, rgb_ca, event_ca):
     """conv0: (rgb_w, rgb_b, evt_w, evt_b); rgb_ca / event_ca: 8 tensors in CAB_PARAM_ORDER."""
     return _REFusionFn.apply(rgb, evt, *conv0, *rgb_ca, *event_ca)
+
+
+# --------------------------------------------------------------------------- 1x1 conv (FPN laterals, row f1)
+class _Conv1x1Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        _check_cuda(x, weight) if bias is None else _check_cuda(x, weight, bias)
+        lib = _lib.load()
+        b, cin, h, w = x.shape
+        cout = weight.shape[0]
+        n = h * w
+        xf, wf = _f32c(x), _f32c(weight)
+        bf = _f32c(bias) if bias is not None else None
+        y = torch.empty((b, cout, h, w), dtype=torch.float32, device=xf.device)
+        with torch.cuda.device(xf.device):
+            ws_bytes = lib.frn_conv1x1_workspace_bytes(b, cin, cout, n)
+            ws = _bytes(ws_bytes, xf.device)
+            _lib.check(lib.frn_conv1x1_forward(_stream(), b, cin, cout, n, _ptr(xf), _ptr(wf),
+                                               _ptr(bf) if bf is not None else None, _ptr(y), _ptr(ws), ws_bytes),
+                       "conv1x1_forward")
+        ctx.save_for_backward(xf, wf)
+        ctx.dims = (b, cin, cout, n)
+        ctx.has_bias = bias is not None
+        ctx.in_dtypes = (x.dtype, weight.dtype, bias.dtype if bias is not None else None)
+        return y.to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        xf, wf = ctx.saved_tensors
+        b, cin, cout, n = ctx.dims
+        g = _f32c(dy)
+        dx = torch.empty_like(xf) if ctx.needs_input_grad[0] else None
+        dw = torch.empty_like(wf)
+        db = torch.empty(cout, dtype=torch.float32, device=xf.device) if ctx.has_bias else None
+        with torch.cuda.device(xf.device):
+            ws_bytes = lib.frn_conv1x1_workspace_bytes(b, cin, cout, n)
+            ws = _bytes(ws_bytes, xf.device)
+            _lib.check(lib.frn_conv1x1_backward(_stream(), b, cin, cout, n, _ptr(xf), _ptr(wf), _ptr(g),
+                                                _ptr(dx) if dx is not None else None, _ptr(dw),
+                                                _ptr(db) if db is not None else None, _ptr(ws), ws_bytes),
+                       "conv1x1_backward")
+        dts = ctx.in_dtypes
+        return (dx.to(dts[0]) if dx is not None else None, dw.to(dts[1]),
+                db.to(dts[2]) if db is not None else None)
+
+
+def conv1x1(x, weight, bias=None):
+    """F.conv2d(x, weight, bias) for a (Cout, Cin, 1, 1) weight, stride 1, no padding (model.py:28-40)."""
+    return _Conv1x1Fn.apply(x, weight, bias)

@@ -4,6 +4,7 @@ state-dict keys, backed by the sm_100a kernels.
     AdaIN_block            retinanet/AdaIN.py:3-26
     CrossAttentionBlock    retinanet/Attention.py:7-36
     REFusion               retinanet/fusion.py:7-36
+    Conv1x1                nn.Conv2d(Cin, Cout, kernel_size=1) of the FPN laterals, retinanet/model.py:28-40
 
 The nn.Conv2d submodules are parameter containers only (their weights keep the
 reference's (out, in, 1, 1) shape so published checkpoints load unchanged,
@@ -87,6 +88,41 @@ class REFusion(nn.Module):
         conv0 = (*_conv_params(self.conv0_rgb), *_conv_params(self.conv0_evt))
         return F.refusion(rgb, evt, conv0, self.rgb_cross_attention.kernel_params(),
                           self.event_cross_attention.kernel_params())
+
+
+class Conv1x1(nn.Conv2d):
+    """nn.Conv2d(in_channels, out_channels, kernel_size=1, stride=1, padding=0) on the library's GEMM
+    engine: the lateral convolutions P{5,4,3,2}_1 that consume the fused maps (model.py:28,32,36,40;
+    SURVEY.md 8.2 row f1).  Same constructor arguments, parameters and state-dict keys as nn.Conv2d;
+    anything but a dense 1x1 stride-1 unpadded convolution is refused."""
+
+    def __init__(self, in_channels, out_channels, kernel_size=1, stride=1, padding=0, bias=True):
+        as2 = lambda v: tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+        if as2(kernel_size) != (1, 1) or as2(stride) != (1, 1) or as2(padding) != (0, 0):
+            raise ValueError("frn_b200.Conv1x1: kernel_size=1, stride=1, padding=0 only")
+        super().__init__(in_channels, out_channels, kernel_size=1, stride=1, padding=0, bias=bias)
+
+    def forward(self, x):
+        assert len(x.size()) == 4
+        return F.conv1x1(x, self.weight, self.bias)
+
+
+def convert_fpn_laterals(model: nn.Module):
+    """Replace the lateral 1x1 convs (attributes P5_1, P4_1, P3_1, P2_1 of a PyramidFeatures-like module,
+    model.py:28-40) by Conv1x1 sharing the same Parameter objects.  Returns the rebound names."""
+    done = []
+    for mod_name, m in model.named_modules():
+        for attr in ("P5_1", "P4_1", "P3_1", "P2_1"):
+            conv = getattr(m, attr, None)
+            if (isinstance(conv, nn.Conv2d) and not isinstance(conv, Conv1x1) and conv.kernel_size == (1, 1)
+                    and conv.stride == (1, 1) and conv.padding == (0, 0) and conv.groups == 1):
+                new = Conv1x1(conv.in_channels, conv.out_channels, bias=conv.bias is not None)
+                new.weight = conv.weight
+                if conv.bias is not None:
+                    new.bias = conv.bias
+                setattr(m, attr, new)
+                done.append(f"{mod_name}.{attr}" if mod_name else attr)
+    return done
 
 
 def fusion_parameters(model: nn.Module):

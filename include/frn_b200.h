@@ -183,6 +183,18 @@ int frn_attn_backward(void* stream, int engine, int B, int N, int d, const float
                       const float* Vc, const float* Y, const float* lse, const float* dY, float* dQ,
                       float* dK, float* dV, void* ws, size_t ws_bytes);
 
+/* ---- 1x1 convolution (the FPN laterals that consume the fused map) -------------
+ * y (B, Cout, N) = w (Cout, Cin) x (B, Cin, N) + bias  -- nn.Conv2d(Cin, Cout, kernel_size=1) of
+ * retinanet/model.py:28,32,36,40 (P{5,4,3,2}_1) on NCHW fp32 tensors viewed as (B, C, N = H*W), run on the
+ * same GEMM engine as the block's own projections (split TF32 on tcgen05 by default).
+ * backward: dx (B, Cin, N) = w^T dy (skipped when dx is NULL), dw (Cout, Cin) = sum_b dy_b x_b^T,
+ * db (Cout) = sum_b sum_n dy (skipped when db is NULL); all three are overwritten. */
+size_t frn_conv1x1_workspace_bytes(int B, int Cin, int Cout, int N);
+int frn_conv1x1_forward(void* stream, int B, int Cin, int Cout, int N, const float* x, const float* w,
+                        const float* bias, float* y, void* ws, size_t ws_bytes);
+int frn_conv1x1_backward(void* stream, int B, int Cin, int Cout, int N, const float* x, const float* w,
+                         const float* dy, float* dx, float* dw, float* db, void* ws, size_t ws_bytes);
+
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
  * launching stream.  Classes: 0 = streaming attention forward, 1 = streaming
