@@ -69,6 +69,9 @@ _SIGNATURES = {
     "frn_attn_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "frn_attn_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_size_t]),
     "frn_attn_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 10 + [C.c_size_t]),
+    "frn_refusion_infer_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
+    "frn_refusion_infer": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p, C.c_void_p,
+                                     C.POINTER(RefusionParams), C.c_void_p, C.c_void_p, C.c_size_t]),
     "frn_conv1x1_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
     "frn_conv1x1_forward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 5 + [C.c_size_t]),
     "frn_conv1x1_backward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 7 + [C.c_size_t]),
@@ -80,6 +83,7 @@ _SIGNATURES = {
     "frn_timing_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]),
 }
 
+FRN_F32, FRN_BF16 = 0, 1
 EXPORTS = tuple(_SIGNATURES)
 _lib = None
 

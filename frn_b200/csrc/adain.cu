@@ -153,6 +153,33 @@ __global__ void __launch_bounds__(256) adain_apply_kernel(long rows, int C, int 
   }
 }
 
+// bf16 output (round to nearest even); W = 4: one 8-byte store
+__device__ __forceinline__ uint32_t bf16_rn(float f) {
+  const uint32_t u = __float_as_uint(f);
+  if ((u & 0x7f800000u) == 0x7f800000u) return (u >> 16) | ((u & 0xffffu) ? 0x40u : 0u);   // inf / nan
+  return (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;
+}
+template <int GS, int W>
+__global__ void __launch_bounds__(256) adain_apply_bf16_kernel(long rows, int C, int N, const float* __restrict__ x,
+                                                               const float* __restrict__ mu_x,
+                                                               const float* __restrict__ sd_x,
+                                                               const float* __restrict__ mu_t,
+                                                               const float* __restrict__ sd_t,
+                                                               uint16_t* __restrict__ out, long ob) {
+  ROW_KERNEL_PROLOGUE();
+  const float* xr = x + row * N;
+  uint16_t* orow = out + (row / C) * ob + (row % C) * (long)N;
+  float mx = mu_x[row], a = sd_t[row] / sd_x[row], mt = mu_t[row];
+  for (int n = lane * W; n < N; n += GS * W) {
+    Vec<W> v; v.load(xr + n);
+    uint32_t h[W];
+#pragma unroll
+    for (int q = 0; q < W; q++) h[q] = bf16_rn(fmaf(v.v[q] - mx, a, mt));
+    if (W == 4) *reinterpret_cast<uint2*>(orow + n) = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3 % W] << 16));
+    else orow[n] = (uint16_t)h[0];
+  }
+}
+
 // ---- AdaIN backward -------------------------------------------------------------
 template <int GS, int W>
 __global__ void __launch_bounds__(256) adain_bwd_reduce_kernel(long rows, int C, int N,
@@ -299,6 +326,14 @@ int adain_apply(cudaStream_t st, int B, int C, int N, const float* x, const floa
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && (ob % 4 == 0) && aligned16(x) && aligned16(out);
   LAUNCH_ROWS(adain_apply_kernel, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
+  return FRN_OK;
+}
+
+int adain_apply_bf16(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x, const float* sd_x,
+                     const float* mu_t, const float* sd_t, uint16_t* out, long ob) {
+  long rows = (long)B * C;
+  bool vec = (N % 4 == 0) && (ob % 4 == 0) && aligned16(x) && ((reinterpret_cast<uintptr_t>(out) & 7) == 0);
+  LAUNCH_ROWS(adain_apply_bf16_kernel, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
   return FRN_OK;
 }
 

@@ -74,7 +74,7 @@ pack_split_kernel(const float* __restrict__ X, const float* __restrict__ sub, lo
       for (int q = 0; q < 4; q++) split_tf32(tile[s * 32 + chunk * 4 + q][nl], h[q], l[q]);
       const long o = (((long)b * kSub + s) * NP + n) * 32 + ((chunk ^ (n & 7)) << 2);
       *reinterpret_cast<float4*>(pos_hi + o) = make_float4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<float4*>(pos_lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+      if (pos_lo) *reinterpret_cast<float4*>(pos_lo + o) = make_float4(l[0], l[1], l[2], l[3]);
     }
   }
   if (chan_hi) {
@@ -85,7 +85,7 @@ pack_split_kernel(const float* __restrict__ X, const float* __restrict__ sub, lo
       for (int q = 0; q < 4; q++) split_tf32(tile[c][chunk * 4 + q], h[q], l[q]);
       const long o = (((long)b * (NP / 32) + blockIdx.x) * DPAD + c) * 32 + ((chunk ^ (c & 7)) << 2);
       *reinterpret_cast<float4*>(chan_hi + o) = make_float4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<float4*>(chan_lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+      if (chan_lo) *reinterpret_cast<float4*>(chan_lo + o) = make_float4(l[0], l[1], l[2], l[3]);
     }
   }
 }
@@ -158,10 +158,11 @@ __device__ __forceinline__ void mma_corr_ts(uint32_t dst, uint32_t a_hi, uint32_
     umma_tf32_ts(dst, a_hi + 8 * k, bl + 2 * k, idesc, true);
   }
 }
-__device__ __forceinline__ void mma_main_ts(uint32_t dst, uint32_t a_hi, uint32_t b_hi, uint32_t idesc) {
+__device__ __forceinline__ void mma_main_ts(uint32_t dst, uint32_t a_hi, uint32_t b_hi, uint32_t idesc,
+                                            bool first = false) {
   const uint64_t bh = umma_desc_sw128(b_hi);
 #pragma unroll
-  for (int k = 0; k < 4; k++) umma_tf32_ts(dst, a_hi + 8 * k, bh + 2 * k, idesc, true);
+  for (int k = 0; k < 4; k++) umma_tf32_ts(dst, a_hi + 8 * k, bh + 2 * k, idesc, !(first && k == 0));
 }
 
 // Two independent products issued interleaved (different accumulators), so that consecutive
@@ -239,11 +240,15 @@ template <int DPAD> struct FwdCfg {
   static constexpr int kQh = kYMain + kGroups * DPAD, kQl = kQh + DPAD;     // kTS only
 };
 
-template <int DPAD>
+// FAST (inference at bf16 tolerance, frn_refusion_infer with FRN_BF16): single-pass TF32 -- only the hi planes
+// are fetched and multiplied (1 tcgen05.mma per product instead of 3), P is rounded to tf32 once and the
+// lo stores disappear.  Relative error ~2^-11 per product; the fp32-parity path (FAST = false) is unchanged.
+template <int DPAD, bool FAST>
 __global__ void __launch_bounds__(FwdCfg<DPAD>::kThreads, 1)
 attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImage Vi, float* __restrict__ Y,
                    float* __restrict__ lse) {
   using Cfg = FwdCfg<DPAD>;
+  static_assert(!FAST || Cfg::kTS, "the single-pass variant keeps Q in TMEM");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sQ = smem;
@@ -295,16 +300,16 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         const int j0 = j * ABN;
         mbar_wait(&kv_empty[stage], phase ^ 1);
         uint8_t* st = sKV + stage * Cfg::kStageBytes;
-        mbar_expect_tx(&kv_full[stage], Cfg::kStageBytes);
+        mbar_expect_tx(&kv_full[stage], FAST ? Cfg::kStageBytes / 2 : Cfg::kStageBytes);
 #pragma unroll
         for (int s = 0; s < Cfg::kSub; s++) {
           const long o = (((long)b * Cfg::kSub + s) * NP + j0) * 32;
           bulk_g2s(st + s * ABN * 128, Ki.pos_hi + o, ABN * 128, &kv_full[stage]);
-          bulk_g2s(st + (Cfg::kSub + s) * ABN * 128, Ki.pos_lo + o, ABN * 128, &kv_full[stage]);
+          if (!FAST) bulk_g2s(st + (Cfg::kSub + s) * ABN * 128, Ki.pos_lo + o, ABN * 128, &kv_full[stage]);
         }
         const long ov = (((long)b * (NP / 32) + (j0 >> 5)) * DPAD) * 32;
         bulk_g2s(st + Cfg::kKBytes, Vi.chan_hi + ov, 2 * DPAD * 128, &kv_full[stage]);
-        bulk_g2s(st + Cfg::kKBytes + 2 * DPAD * 128, Vi.chan_lo + ov, 2 * DPAD * 128, &kv_full[stage]);
+        if (!FAST) bulk_g2s(st + Cfg::kKBytes + 2 * DPAD * 128, Vi.chan_lo + ov, 2 * DPAD * 128, &kv_full[stage]);
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
@@ -323,7 +328,11 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       if (elect_one()) {
         const uint32_t k_base = smem_u32(sKV + stage * Cfg::kStageBytes);
         const uint32_t s_acc = tmem + Cfg::kSMain + buf * ABN;
-        if (Cfg::kTS) {
+        if (FAST) {
+#pragma unroll
+          for (int s = 0; s < Cfg::kSub; s++)
+            mma_main_ts(s_acc, tmem + Cfg::kQh + 32 * s, k_base + s * ABN * 128, idesc_s, s == 0);
+        } else if (Cfg::kTS) {
 #pragma unroll
           for (int s = 0; s < Cfg::kSub; s++)
             mma_corr_ts(s_acc, tmem + Cfg::kQh + 32 * s, tmem + Cfg::kQl + 32 * s, k_base + s * ABN * 128,
@@ -356,12 +365,15 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         const uint32_t v_base = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKBytes);
         const uint32_t p_hi = tmem + Cfg::kSMain + buf * ABN, p_lo = tmem + Cfg::kSSmall + buf * ABN;
         const uint32_t y_acc = tmem + Cfg::kYMain + buf * DPAD;
+        if (!FAST) {
+#pragma unroll
+          for (int s = 0; s < 2; s++)
+            mma_corr_ts(y_acc, p_hi + s * 32, p_lo + s * 32, v_base + s * DPAD * 128,
+                        v_base + (2 + s) * DPAD * 128, idesc_y, s == 0);
+        }
 #pragma unroll
         for (int s = 0; s < 2; s++)
-          mma_corr_ts(y_acc, p_hi + s * 32, p_lo + s * 32, v_base + s * DPAD * 128,
-                      v_base + (2 + s) * DPAD * 128, idesc_y, s == 0);
-#pragma unroll
-        for (int s = 0; s < 2; s++) mma_main_ts(y_acc, p_hi + s * 32, v_base + s * DPAD * 128, idesc_y);
+          mma_main_ts(y_acc, p_hi + s * 32, v_base + s * DPAD * 128, idesc_y, FAST && s == 0);
         umma_commit(&y_full[buf]);
         umma_commit(&kv_empty[stage]);               // S(j) (the other warp) completed before p_full(j) could fire
       }
@@ -387,7 +399,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       const int gq = i0 + row;
       const float* plane = grp == 0 ? Qi.pos_hi : Qi.pos_lo;
       const uint32_t col = grp == 0 ? Cfg::kQh : Cfg::kQl;
-      if (grp < 2) {
+      if (grp < (FAST ? 1 : 2)) {
 #pragma unroll
         for (int c16 = 0; c16 < DPAD / 16; c16++) {
           const float* rp = plane + (((long)b * Cfg::kSub + (c16 >> 1)) * NP + gq) * 32;
@@ -454,7 +466,7 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
           split_tf32(p, hi[q], lo[q]);
         }
         tmem_st16(tmem + lane_base + Cfg::kSMain + buf * ABN + c0, hi);
-        tmem_st16(tmem + lane_base + Cfg::kSSmall + buf * ABN + c0, lo);
+        if (!FAST) tmem_st16(tmem + lane_base + Cfg::kSSmall + buf * ABN + c0, lo);
       }
       l = fmaf(l, corr, sum);
       m = m_new;
@@ -1750,11 +1762,11 @@ int launch_pack(cudaStream_t st, int B, int d, int N, const float* X, const floa
   return FRN_OK;
 }
 
-template <int DPAD>
+template <int DPAD, bool FAST>
 int launch_fwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
                   const SplitImage& V, float* Y, float* lse) {
   using Cfg = FwdCfg<DPAD>;
-  auto kern = attn_fwd_tc_kernel<DPAD>;
+  auto kern = attn_fwd_tc_kernel<DPAD, FAST>;
   FRN_TRY(set_smem(kern, Cfg::kSmem));
   dim3 grid(cdiv(N, ABM), B);
   ScopedTimer tm(st, FRN_TIME_ATTN_FWD);
@@ -1869,17 +1881,22 @@ size_t attn_tc_plane_floats(int B, int N, int d) {
 int attn_tc_pack(cudaStream_t st, int B, int d, int N, const float* X, const float* sub, long bs, long cs,
                  long ns, const SplitImage& img) {
   if (d > 64) return FRN_ERR_UNSUPPORTED;
-  if ((img.pos_hi == nullptr) != (img.pos_lo == nullptr) || (img.chan_hi == nullptr) != (img.chan_lo == nullptr))
-    return FRN_ERR_NULL_POINTER;
+  if ((img.pos_lo && !img.pos_hi) || (img.chan_lo && !img.chan_hi)) return FRN_ERR_NULL_POINTER;
   ScopedTimer tm(st, FRN_TIME_ROWS);
   return d <= 32 ? launch_pack<32>(st, B, d, N, X, sub, bs, cs, ns, img)
                  : launch_pack<64>(st, B, d, N, X, sub, bs, cs, ns, img);
 }
 
 int attn_forward_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
-                    const SplitImage& V, float* Y, float* lse) {
-  if (d <= 32) return launch_fwd_tc<32>(st, B, N, d, Q, K, V, Y, lse);
-  if (d <= 64) return launch_fwd_tc<64>(st, B, N, d, Q, K, V, Y, lse);
+                    const SplitImage& V, float* Y, float* lse, int fast) {
+  if (fast) {
+    if (d <= 32) return launch_fwd_tc<32, true>(st, B, N, d, Q, K, V, Y, lse);
+    if (d <= 64) return launch_fwd_tc<64, true>(st, B, N, d, Q, K, V, Y, lse);
+    return FRN_ERR_UNSUPPORTED;
+  }
+  if (!Q.pos_lo || !K.pos_lo || !V.chan_lo) return FRN_ERR_NULL_POINTER;
+  if (d <= 32) return launch_fwd_tc<32, false>(st, B, N, d, Q, K, V, Y, lse);
+  if (d <= 64) return launch_fwd_tc<64, false>(st, B, N, d, Q, K, V, Y, lse);
   return FRN_ERR_UNSUPPORTED;
 }
 

@@ -107,6 +107,7 @@ struct GemmDesc {
   float alpha;
   int accumulate;        // C += result
   int reduce_batch;
+  int fast;              // tcgen05 engine only: single-pass TF32 (hi * hi), ~2^-11 relative; bf16-tolerance inference
 };
 enum { GEMM_EPI_STORE = 0, GEMM_EPI_ROWSUMSQ = 1 };
 
@@ -148,9 +149,10 @@ size_t attn_tc_plane_floats(int B, int N, int d);
 // to zero), and without the common component the cancellation in dQ no longer amplifies rounding.
 int attn_tc_pack(cudaStream_t st, int B, int d, int N, const float* X, const float* sub, long bs, long cs,
                  long ns, const SplitImage& img);
-// needs Q.pos, K.pos, V.chan
+// needs Q.pos, K.pos, V.chan.  fast != 0: single-pass TF32 (bf16-tolerance inference); only the hi planes
+// are read and the lo planes may be null.
 int attn_forward_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
-                    const SplitImage& V, float* Y, float* lse);
+                    const SplitImage& V, float* Y, float* lse, int fast = 0);
 // lse_pad, delta_pad: (B, attn_tc_np(N)); delta = rowsum(dY * Y)
 int attn_bwd_prep_tc(cudaStream_t st, int B, int N, int d, const float* dYp, const float* Y, const float* lse,
                      float* lse_pad, float* delta_pad);
@@ -178,6 +180,11 @@ int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* 
 // out[b][c][n] = (x - mu_x)/sd_x * sd_t + mu_t   (out has batch stride ob)
 int adain_apply(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x,
                 const float* sd_x, const float* mu_t, const float* sd_t, float* out, long ob);
+// the same with a bf16 output (inference with bf16 activations); ob in elements
+int adain_apply_bf16(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x,
+                     const float* sd_x, const float* mu_t, const float* sd_t, uint16_t* out, long ob);
+// dst[i] = float(src[i]) for bf16 src
+int cast_bf16_to_f32(cudaStream_t st, size_t count, const uint16_t* src, float* dst);
 // g1 = sum_n g, g2 = sum_n g * xhat per (b, c) row; g has batch stride gb.
 int adain_bwd_reduce(cudaStream_t st, int B, int C, int N, const float* g, long gb,
                      const float* x, const float* mu_x, const float* sd_x, float* g1, float* g2);

@@ -25,9 +25,11 @@ struct Ctx {
   void* splitk;
   size_t splitk_cap;
   int attn_eng;         // 0 = FFMA streaming kernels, 1 = tcgen05 kernels
+  int fast;             // frn_refusion_infer(FRN_BF16): single-pass TF32 products on the tcgen05 engines
+  bool out_bf16;        // ... and the AdaIN affine writes the block output as bf16
   Ctx(cudaStream_t s, void* p, size_t bytes, bool dry_)
       : st(s), dry(dry_), ws(p, bytes, dry_), splitk_need(0), splitk(nullptr), splitk_cap(0),
-        attn_eng(attn_engine()) {}
+        attn_eng(attn_engine()), fast(0), out_bf16(false) {}
 };
 
 #define RUN(c, expr)              \
@@ -35,7 +37,9 @@ struct Ctx {
     if (!(c).dry) FRN_TRY(expr);  \
   } while (0)
 
-int run_gemm(Ctx& c, const GemmDesc& d) {
+int run_gemm(Ctx& c, const GemmDesc& d_in) {
+  GemmDesc d = d_in;
+  d.fast = c.fast;
   if (c.dry) {
     c.splitk_need = std::max(c.splitk_need, gemm_workspace_bytes(d));
     return FRN_OK;
@@ -130,11 +134,11 @@ int chunk_for_scores(int B, int N, int mats) {
 }
 
 // workspace planes of one packed split image (attention_tc.cu)
-SplitImage take_image(Ctx& c, int B, int N, int d, bool pos, bool chan) {
+SplitImage take_image(Ctx& c, int B, int N, int d, bool pos, bool chan, bool lo = true) {
   const size_t n = attn_tc_plane_floats(B, N, d);
   SplitImage im{nullptr, nullptr, nullptr, nullptr};
-  if (pos) { im.pos_hi = c.ws.take<float>(n); im.pos_lo = c.ws.take<float>(n); }
-  if (chan) { im.chan_hi = c.ws.take<float>(n); im.chan_lo = c.ws.take<float>(n); }
+  if (pos) { im.pos_hi = c.ws.take<float>(n); if (lo) im.pos_lo = c.ws.take<float>(n); }
+  if (chan) { im.chan_hi = c.ws.take<float>(n); if (lo) im.chan_lo = c.ws.take<float>(n); }
   return im;
 }
 
@@ -144,15 +148,16 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
     if (c.attn_eng == 1 || c.dry) {     // dry: count both engines' scratch, the arena keeps the peak
       const size_t m0 = c.ws.off;
       const long dn = (long)d * N;
-      SplitImage Q = take_image(c, B, N, d, true, false), K = take_image(c, B, N, d, true, false);
-      SplitImage V = take_image(c, B, N, d, false, true);
+      const bool lo = !c.fast;            // the single-pass variant reads the hi planes only
+      SplitImage Q = take_image(c, B, N, d, true, false, lo), K = take_image(c, B, N, d, true, false, lo);
+      SplitImage V = take_image(c, B, N, d, false, true, lo);
       float* kbar = c.ws.take<float>((size_t)B * d);
       float* ksd = c.ws.take<float>((size_t)B * d);
       RUN(c, row_mean_std(c.st, (long)B * d, N, s.Kc, kEps, kbar, ksd));
       RUN(c, attn_tc_pack(c.st, B, d, N, s.Qc, nullptr, dn, N, 1, Q));
       RUN(c, attn_tc_pack(c.st, B, d, N, s.Kc, kbar, dn, N, 1, K));
       RUN(c, attn_tc_pack(c.st, B, d, N, s.Vc, nullptr, dn, N, 1, V));
-      RUN(c, attn_forward_tc(c.st, B, N, d, Q, K, V, s.Y, s.lse));
+      RUN(c, attn_forward_tc(c.st, B, N, d, Q, K, V, s.Y, s.lse, c.fast));
       if (!c.dry) return FRN_OK;
       c.ws.release_to(m0);
     }
@@ -212,6 +217,7 @@ int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, c
     GemmDesc g = desc(p.W_w, Yc, nullptr, C, N, d, B);
     g.sAm = d; g.sAk = 1; g.sAb = 0;
     g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
+    g.fast = c.fast;
     RUN(c, gemm_rowsumsq(c.st, g, parts));
     RUN(c, finish_style_std(c.st, (long)B * C, nparts, N, parts, kEps, s.sd_t));
     GemmDesc m = desc(p.W_w, s.ybar, s.mu_t, C, B, d, 1);       // mu_t[b][c] = W[c] . ybar[b] + b_c
@@ -222,7 +228,10 @@ int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, c
     FRN_TRY(run_gemm(c, m));
   }
   if (!have_x_stats) RUN(c, row_mean_std(c.st, (long)B * C, N, x0, kEps, s.mu_x, s.sd_x));
-  RUN(c, adain_apply(c.st, B, C, N, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, out, ob));  // AdaIN.py:24-26
+  if (c.out_bf16)     // `out` is a bf16 buffer; ob is in elements either way
+    RUN(c, adain_apply_bf16(c.st, B, C, N, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, (uint16_t*)out, ob));
+  else
+    RUN(c, adain_apply(c.st, B, C, N, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, out, ob));  // AdaIN.py:24-26
   c.ws.release_to(mark);
   return FRN_OK;
 }
@@ -411,7 +420,8 @@ int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e
                     s.blkB.mu_x, s.blkB.sd_x));
   const long ob = 2L * C * N;
   FRN_TRY(cab_forward(c, B, C, N, s.R1, s.E1, p.rgb_ca, out, ob, s.blkA, true));                 // fusion.py:31
-  FRN_TRY(cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out + (long)C * N, ob, s.blkB, true));  // fusion.py:32,34
+  float* out_b = c.out_bf16 ? (float*)((uint16_t*)out + (long)C * N) : out + (long)C * N;
+  FRN_TRY(cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out_b, ob, s.blkB, true));  // fusion.py:32,34
   return FRN_OK;
 }
 
@@ -683,6 +693,43 @@ int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, con
   return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
     return refusion_backward(c, B, C, N, a, e, *p, s, dout, da, de, *grads);
   });
+}
+
+// ---- REFusion, inference only (no state kept), fp32 or bf16 activations --------------------------
+static int refusion_infer_body(Ctx& c, int dtype, int B, int C, int N, const void* a, const void* e,
+                               const frn_refusion_params& p, void* out) {
+  const size_t cn = (size_t)B * C * N;
+  const float *a32 = (const float*)a, *e32 = (const float*)e;
+  if (dtype == FRN_BF16) {
+    // bf16 activations in and out, fp32 parameters, fp32 statistics and accumulation; every tensor-core product
+    // single-pass TF32 (11 significant bits against bf16's 8)
+    c.fast = 1;
+    c.out_bf16 = true;
+    float* af = c.ws.take<float>(cn);
+    float* ef = c.ws.take<float>(cn);
+    RUN(c, cast_bf16_to_f32(c.st, cn, (const uint16_t*)a, af));
+    RUN(c, cast_bf16_to_f32(c.st, cn, (const uint16_t*)e, ef));
+    a32 = af; e32 = ef;
+  }
+  const size_t need_saved = fusion_saved_layout(nullptr, B, C, N).bytes;
+  void* sv = c.ws.take<char>(need_saved);
+  if (!c.dry && !sv) return (int)FRN_ERR_WORKSPACE;
+  FusionSaved s = fusion_saved_layout(c.dry ? nullptr : sv, B, C, N);
+  return refusion_forward(c, B, C, N, a32, e32, p, (float*)out, s);
+}
+size_t frn_refusion_infer_workspace_bytes(int dtype, int B, int C, int N) {
+  if (!shape_ok(B, C, N) || (dtype != FRN_F32 && dtype != FRN_BF16)) return 0;
+  frn_refusion_params p{};
+  return dry_bytes([&](Ctx& c) { return refusion_infer_body(c, dtype, B, C, N, nullptr, nullptr, p, nullptr); });
+}
+int frn_refusion_infer(void* stream, int dtype, int B, int C, int N, const void* a, const void* e,
+                       const frn_refusion_params* p, void* out, void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N)) return FRN_ERR_BAD_SHAPE;
+  if (dtype != FRN_F32 && dtype != FRN_BF16) return FRN_ERR_UNSUPPORTED;
+  if (!a || !e || !p || !out) return FRN_ERR_NULL_POINTER;
+  if (dtype == FRN_BF16 && (gemm_engine() != 1 || attn_engine() != 1)) return FRN_ERR_UNSUPPORTED;
+  return with_ctx(stream, ws, ws_bytes,
+                  [&](Ctx& c) { return refusion_infer_body(c, dtype, B, C, N, a, e, *p, out); });
 }
 
 // ---- 1x1 convolution (FPN laterals, model.py:28-40) ---------------------------------

@@ -169,6 +169,28 @@ __global__ void fill_zero_kernel(float* __restrict__ p, size_t count) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += stride) p[i] = 0.f;
 }
 
+// bf16 -> fp32 is a 16-bit shift; eight elements (one 16-byte load, two 16-byte stores) per thread and step
+__global__ void cast_bf16_to_f32_kernel(size_t count, const uint16_t* __restrict__ src, float* __restrict__ dst,
+                                        int vec) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t done = 0;
+  if (vec) {
+    const size_t n8 = count / 8;
+    for (size_t i = t0; i < n8; i += stride) {
+      const uint4 r = __ldg(reinterpret_cast<const uint4*>(src) + i);
+      float4 lo4, hi4;
+      lo4.x = __uint_as_float(r.x << 16); lo4.y = __uint_as_float(r.x & 0xffff0000u);
+      lo4.z = __uint_as_float(r.y << 16); lo4.w = __uint_as_float(r.y & 0xffff0000u);
+      hi4.x = __uint_as_float(r.z << 16); hi4.y = __uint_as_float(r.z & 0xffff0000u);
+      hi4.z = __uint_as_float(r.w << 16); hi4.w = __uint_as_float(r.w & 0xffff0000u);
+      reinterpret_cast<float4*>(dst)[2 * i] = lo4;
+      reinterpret_cast<float4*>(dst)[2 * i + 1] = hi4;
+    }
+    done = n8 * 8;
+  }
+  for (size_t i = done + t0; i < count; i += stride) dst[i] = __uint_as_float((uint32_t)src[i] << 16);
+}
+
 __global__ void scale_sum_batch_kernel(int B, int C, const float* __restrict__ alpha, float scale,
                                        float* __restrict__ out) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -393,6 +415,15 @@ int center_cols(cudaStream_t st, int B, int N, int d, float* x, float* part) {
 int fill_zero(cudaStream_t st, float* p, size_t count) {
   if (count == 0) return FRN_OK;
   fill_zero_kernel<<<grid_for((long)count), 256, 0, st>>>(p, count);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int cast_bf16_to_f32(cudaStream_t st, size_t count, const uint16_t* src, float* dst) {
+  if (count == 0) return FRN_OK;
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  const int vec = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+  cast_bf16_to_f32_kernel<<<grid_for((long)(count / 8 + 1)), 256, 0, st>>>(count, src, dst, vec);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }

@@ -133,7 +133,7 @@ __device__ __forceinline__ void issue_raw(uint32_t raw, const float* __restrict_
 // raw tile -> tf32 hi / lo split -> SWIZZLE_128B K-major tiles (all by 32-bit shared addresses)
 template <int ROWS, bool KFAST>
 __device__ __forceinline__ void convert_tile(uint32_t hi, uint32_t lo, uint32_t raw, const OperandPlan<ROWS>& pl,
-                                             int t) {
+                                             int t, bool with_lo) {
   constexpr int CH = OperandPlan<ROWS>::CH;
   float v[CH][4];
   uint32_t o[CH];
@@ -160,7 +160,7 @@ __device__ __forceinline__ void convert_tile(uint32_t hi, uint32_t lo, uint32_t 
 #pragma unroll
     for (int q = 0; q < 4; q++) split_tf32(v[i][q], h[q], l[q]);
     sts128(hi + o[i], h[0], h[1], h[2], h[3]);
-    sts128(lo + o[i], l[0], l[1], l[2], l[3]);
+    if (with_lo) sts128(lo + o[i], l[0], l[1], l[2], l[3]);
   }
 }
 
@@ -308,12 +308,12 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
       const uint32_t sB = sAl + Cfg::kABytes;
       const uint32_t sBl = sB + Cfg::kBBytes;
       { TRACE_T0();
-      if (planA.kfast) convert_tile<TBM, true>(sA, sAl, rA, planA, tid);
-      else convert_tile<TBM, false>(sA, sAl, rA, planA, tid);
+      if (planA.kfast) convert_tile<TBM, true>(sA, sAl, rA, planA, tid, !p.fast);
+      else convert_tile<TBM, false>(sA, sAl, rA, planA, tid, !p.fast);
       TRACE_ADD(9); }
       { TRACE_T0();
-      if (planB.kfast) convert_tile<BN, true>(sB, sBl, rB, planB, tid);
-      else convert_tile<BN, false>(sB, sBl, rB, planB, tid);
+      if (planB.kfast) convert_tile<BN, true>(sB, sBl, rB, planB, tid, !p.fast);
+      else convert_tile<BN, false>(sB, sBl, rB, planB, tid, !p.fast);
       TRACE_ADD(10); }
       { TRACE_T0();
       fence_proxy_async_smem();
@@ -356,9 +356,11 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
             // lo*lo (2^-22 of the product) is kept as well: when one operand is near-constant (|mean| >> sigma,
             // the blanked-RGB case of model.py:279-280) all of its variation lives in `lo`, and a product with a
             // zero-sum partner would otherwise be 2^-11 off.
-            umma_tf32_ss(d_small, a_lo + 2 * k, b_lo + 2 * k, idesc, acc);
-            umma_tf32_ss(d_small, a_lo + 2 * k, b_hi + 2 * k, idesc, true);
-            umma_tf32_ss(d_small, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
+            if (!p.fast) {     // p.fast: single-pass TF32 (bf16-tolerance inference): hi * hi only, no lo tiles staged
+              umma_tf32_ss(d_small, a_lo + 2 * k, b_lo + 2 * k, idesc, acc);
+              umma_tf32_ss(d_small, a_lo + 2 * k, b_hi + 2 * k, idesc, true);
+              umma_tf32_ss(d_small, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
+            }
             umma_tf32_ss(d_main, a_hi + 2 * k, b_hi + 2 * k, idesc, acc);
           }
           umma_commit(&empty[stage]);            // frees the stage once these MMAs have read it
@@ -394,7 +396,12 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
         for (int c0 = 0; c0 < HC; c0 += 16) {
           float v[16], w[16];
           tmem_ld16(taddr + c0, v);
-          tmem_ld16(taddr + BN + c0, w);
+          if (!p.fast) {
+            tmem_ld16(taddr + BN + c0, w);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; j++) w[j] = 0.f;
+          }
           tmem_wait_ld();
 #pragma unroll
           for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];

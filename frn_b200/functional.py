@@ -213,9 +213,40 @@ class _REFusionFn(torch.autograd.Function):
         return (da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
 
 
+def refusion_infer_bf16(rgb, evt, conv0, rgb_ca, event_ca):
+    """Inference with bf16 activations (BASELINE.json config 4; the reference under
+    torch.autocast(bfloat16) + no_grad, train_dsec_det_fast.py:241): bf16 in, bf16 out, fp32 parameters,
+    fp32 statistics / softmax / accumulation, single-pass TF32 products.  No autograd graph."""
+    params = (*conv0, *rgb_ca, *event_ca)
+    _check_cuda(rgb, evt, *params)
+    lib = _lib.load()
+    b, c, h, w = rgb.shape
+    n = h * w
+    a = rgb.detach().to(torch.bfloat16).contiguous()
+    e = evt.detach().to(torch.bfloat16).contiguous()
+    prm = [_f32c(p) for p in params]
+    out = torch.empty((b, 2 * c, h, w), dtype=torch.bfloat16, device=a.device)
+    with torch.cuda.device(a.device):
+        ws_bytes = lib.frn_refusion_infer_workspace_bytes(_lib.FRN_BF16, b, c, n)
+        ws = _bytes(ws_bytes, a.device)
+        st = _fusion_struct(prm[0:4], prm[4:12], prm[12:20])
+        _lib.check(lib.frn_refusion_infer(_stream(), _lib.FRN_BF16, b, c, n, _ptr(a), _ptr(e), C.byref(st),
+                                          _ptr(out), _ptr(ws), ws_bytes), "refusion_infer")
+    return out
+
+
 def refusion(rgb, evt, conv0, rgb_ca, event_ca):
-    """conv0: (rgb_w, rgb_b, evt_w, evt_b); rgb_ca / event_ca: 8 tensors in CAB_PARAM_ORDER."""
-    return _REFusionFn.apply(rgb, evt, *conv0, *rgb_ca, *event_ca)
+    """conv0: (rgb_w, rgb_b, evt_w, evt_b); rgb_ca / event_ca: 8 tensors in CAB_PARAM_ORDER.
+
+    bf16 activations (bf16 inputs, or fp32 inputs under torch.autocast(bfloat16)) with no gradient required
+    take the bf16 inference path; everything else runs the fp32-parity kernels."""
+    params = (*conv0, *rgb_ca, *event_ca)
+    wants_grad = torch.is_grad_enabled() and any(t.requires_grad for t in (rgb, evt, *params))
+    autocast_bf16 = (torch.is_autocast_enabled("cuda") and
+                     torch.get_autocast_dtype("cuda") == torch.bfloat16)
+    if not wants_grad and (autocast_bf16 or (rgb.dtype == torch.bfloat16 and evt.dtype == torch.bfloat16)):
+        return refusion_infer_bf16(rgb, evt, conv0, rgb_ca, event_ca)
+    return _REFusionFn.apply(rgb, evt, *params)
 
 
 # --------------------------------------------------------------------------- 1x1 conv (FPN laterals, row f1)

@@ -183,6 +183,16 @@ int frn_attn_backward(void* stream, int engine, int B, int N, int d, const float
                       const float* Vc, const float* Y, const float* lse, const float* dY, float* dQ,
                       float* dK, float* dV, void* ws, size_t ws_bytes);
 
+/* ---- REFusion, inference (retinanet/fusion.py:20-36 under torch.no_grad(); BASELINE.json config 4) -----
+ * Forward pass that keeps no state for a backward.  dtype = FRN_F32: a, e, out are float (identical results
+ * to frn_refusion_forward with saved == NULL).  dtype = FRN_BF16: a, e (B, C, N) and out (B, 2C, N) are
+ * bfloat16, parameters stay float; statistics, softmax and accumulation are fp32 and every tensor-core
+ * product is single-pass TF32 (11 significant bits), i.e. the result is at least as accurate as the
+ * reference under torch.autocast(bfloat16) (train_dsec_det_fast.py:241).  Needs the tcgen05 engines. */
+size_t frn_refusion_infer_workspace_bytes(int dtype, int B, int C, int N);
+int frn_refusion_infer(void* stream, int dtype, int B, int C, int N, const void* a, const void* e,
+                       const frn_refusion_params* p, void* out, void* ws, size_t ws_bytes);
+
 /* ---- 1x1 convolution (the FPN laterals that consume the fused map) -------------
  * y (B, Cout, N) = w (Cout, Cin) x (B, Cin, N) + bias  -- nn.Conv2d(Cin, Cout, kernel_size=1) of
  * retinanet/model.py:28,32,36,40 (P{5,4,3,2}_1) on NCHW fp32 tensors viewed as (B, C, N = H*W), run on the
