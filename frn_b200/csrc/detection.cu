@@ -1,0 +1,358 @@
+// the two host-bound hops between the heads and the optimiser step.
+//
+//   anchors    retinanet/anchors.py:25-45 (Anchors.forward), :47-82 (generate_anchors), :120-147 (shift):
+//              NumPy regenerates ~230 k boxes in float64 and copies them host -> device on EVERY step.
+//              Here: the (ratios x scales) base boxes are formed on the host in double (a few dozen
+//              numbers), one kernel per pyramid level adds the cell shifts in double and rounds once to
+//              fp32 -- bit-identical to the NumPy result, written straight into device memory.
+//   focal loss retinanet/losses.py:28-169 (FocalLoss.forward) with calc_iou (:5-24): a Python loop over
+//              the batch, ~60 ATen launches and three host synchronisations per sample (boolean-mask
+//              indexing, `if positive_indices.sum() > 0`).  Here: ONE forward kernel (IoU assignment,
+//              classification and box terms, per-CTA partial sums in double) + one finalising CTA, and
+//              ONE backward kernel; no host synchronisation, no atomics (bit-reproducible).
+//
+// Both are HBM-bound streaming passes: forward reads (K + 4) floats per (sample, anchor) and writes one
+// int32 of assignment state; backward reads the same and writes (K + 4) floats.
+#include <math.h>
+#include "common.cuh"
+
+namespace frn {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxAnn = 2048;          // annotations per sample staged in shared memory (5 floats each)
+constexpr int kMaxBase = 32;           // ratios x scales per cell
+
+struct BaseBoxes { double v[kMaxBase][4]; };
+
+// out[((y * fw + x) * nA + a) * 4 + j] = float(base[a][j] + shift_j),  shift = ((x|y) + 0.5) * stride
+// (anchors.py:120-147: cells row-major, the nA boxes of a cell adjacent).
+__global__ void __launch_bounds__(kThreads) anchors_level_kernel(int fh, int fw, int nA, int stride, BaseBoxes base,
+                                                                 float4* __restrict__ out) {
+  long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  long total = (long)fh * fw * nA;
+  if (i >= total) return;
+  int a = (int)(i % nA);
+  long cell = i / nA;
+  int x = (int)(cell % fw), y = (int)(cell / fw);
+  double sx = __dmul_rn((double)x + 0.5, (double)stride);
+  double sy = __dmul_rn((double)y + 0.5, (double)stride);
+  float4 o;
+  o.x = (float)__dadd_rn(base.v[a][0], sx);
+  o.y = (float)__dadd_rn(base.v[a][1], sy);
+  o.z = (float)__dadd_rn(base.v[a][2], sx);
+  o.w = (float)__dadd_rn(base.v[a][3], sy);
+  out[i] = o;
+}
+
+// ---- focal loss ------------------------------------------------------------------------------------
+// Assignment state of one (sample, anchor): >= 0 positive, matched to that annotation row (IoU >= 0.5);
+// kNegative: IoU_max < 0.4 (all targets 0); kIgnore: 0.4 <= IoU_max < 0.5 (no classification term).
+constexpr int kNegative = -1, kIgnore = -2;
+
+// calc_iou (losses.py:5-24) in the reference's own operation order, every step rounded to fp32 separately
+// (no FMA contraction) so that the 0.4 / 0.5 thresholds fall exactly where the reference's fp32 ATen ops
+// put them.
+__device__ __forceinline__ float iou_f32(float4 a, float area_a, float4 b) {
+  float area_b = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+  float iw = fmaxf(__fsub_rn(fminf(a.z, b.z), fmaxf(a.x, b.x)), 0.f);
+  float ih = fmaxf(__fsub_rn(fminf(a.w, b.w), fmaxf(a.y, b.y)), 0.f);
+  float inter = __fmul_rn(iw, ih);
+  float ua = fmaxf(__fsub_rn(__fadd_rn(area_a, area_b), inter), 1e-8f);
+  return __fdiv_rn(inter, ua);
+}
+
+__device__ __forceinline__ int assign_anchor(float4 a, const float* __restrict__ ann, int M) {
+  float area_a = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
+  float best = -1.f;
+  int arg = -1;
+  for (int j = 0; j < M; j++) {
+    if (ann[j * 5 + 4] == -1.f) continue;                          // padding rows (losses.py:45)
+    float4 g = make_float4(ann[j * 5], ann[j * 5 + 1], ann[j * 5 + 2], ann[j * 5 + 3]);
+    float v = iou_f32(a, area_a, g);
+    if (v > best) { best = v; arg = j; }                           // first maximum wins (torch.max on CPU)
+  }
+  if (arg < 0 || best < 0.4f) return kNegative;                    // no annotation at all: losses.py:48-79
+  return best >= 0.5f ? arg : kIgnore;
+}
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block sums of three doubles; valid in thread 0.
+__device__ __forceinline__ void block_sum3(double& a, double& b, double& c, double (*red)[3]) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  a = warp_sum_d(a); b = warp_sum_d(b); c = warp_sum_d(c);
+  if (lane == 0) { red[w][0] = a; red[w][1] = b; red[w][2] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a = b = c = 0.0;
+    for (int i = 0; i < nw; i++) { a += red[i][0]; b += red[i][1]; c += red[i][2]; }
+  }
+}
+
+// Box regression targets of a positive anchor (losses.py:123-146) minus the prediction.
+__device__ __forceinline__ float4 box_residual(float4 a, float4 g, float4 r) {
+  float aw = a.z - a.x, ah = a.w - a.y;
+  float acx = a.x + 0.5f * aw, acy = a.y + 0.5f * ah;
+  float gw = g.z - g.x, gh = g.w - g.y;
+  float gcx = g.x + 0.5f * gw, gcy = g.y + 0.5f * gh;
+  gw = fmaxf(gw, 1.f); gh = fmaxf(gh, 1.f);
+  float4 t;
+  t.x = (gcx - acx) / aw / 0.1f;
+  t.y = (gcy - acy) / ah / 0.1f;
+  t.z = logf(gw / aw) / 0.2f;
+  t.w = logf(gh / ah) / 0.2f;
+  return make_float4(t.x - r.x, t.y - r.y, t.z - r.z, t.w - r.w);
+}
+
+__device__ __forceinline__ float smooth_l1(float d) {          // losses.py:149-156, beta = 1/9
+  float v = fabsf(d);
+  return v <= 1.0f / 9.0f ? 4.5f * v * v : v - 0.5f / 9.0f;
+}
+__device__ __forceinline__ float smooth_l1_grad(float d) {     // d/dd
+  float v = fabsf(d);
+  float g = v <= 1.0f / 9.0f ? 9.0f * v : 1.0f;
+  return d > 0.f ? g : (d < 0.f ? -g : 0.f);
+}
+
+// grid (ceil(A / 256), B).  CTA = 256 consecutive anchors of one sample.
+__global__ void __launch_bounds__(kThreads) focal_forward_kernel(
+    int A, int K, int M, const float* __restrict__ cls, const float* __restrict__ reg,
+    const float4* __restrict__ anchors, const float* __restrict__ ann_all, float alpha,
+    int* __restrict__ assign_out, double* __restrict__ partials) {
+  extern __shared__ float s_ann[];                     // M x 5
+  __shared__ int s_state[kThreads];                    // assignment of the CTA's anchors
+  __shared__ int s_class[kThreads];                    // class of the matched annotation (positives)
+  __shared__ double s_red[kThreads / 32][3];
+  int b = blockIdx.y;
+  long a0 = (long)blockIdx.x * kThreads;
+  int na = (int)min((long)kThreads, A - a0);
+  const float* ann = ann_all + (long)b * M * 5;
+  for (int i = threadIdx.x; i < M * 5; i += kThreads) s_ann[i] = ann[i];
+  __syncthreads();
+
+  float cls_sum = 0.f, reg_sum = 0.f, npos = 0.f;
+  int t = threadIdx.x;
+  if (t < na) {
+    float4 a = anchors[a0 + t];
+    int st = assign_anchor(a, s_ann, M);
+    s_state[t] = st;
+    assign_out[(long)b * A + a0 + t] = st;
+    if (st >= 0) {
+      s_class[t] = (int)(long)s_ann[st * 5 + 4];
+      float4 g = make_float4(s_ann[st * 5], s_ann[st * 5 + 1], s_ann[st * 5 + 2], s_ann[st * 5 + 3]);
+      float4 r = reinterpret_cast<const float4*>(reg)[(long)b * A + a0 + t];
+      float4 d = box_residual(a, g, r);
+      reg_sum = smooth_l1(d.x) + smooth_l1(d.y) + smooth_l1(d.z) + smooth_l1(d.w);
+      npos = 1.f;
+    }
+  }
+  __syncthreads();
+
+  // classification terms: the CTA's na*K scores are contiguous in (B, A, K)
+  const float* c0 = cls + ((long)b * A + a0) * K;
+  int count = na * K;
+  for (int i = t; i < count; i += kThreads) {
+    int al = i / K, k = i - al * K;
+    int st = s_state[al];
+    if (st == kIgnore) continue;
+    float c = fminf(fmaxf(__ldg(c0 + i), 1e-4f), 1.0f - 1e-4f);            // losses.py:46
+    bool one = st >= 0 && s_class[al] == k;
+    // alpha (1-c)^2 (-log c)  |  (1-alpha) c^2 (-log(1-c))    (losses.py:98-106, gamma = 2)
+    cls_sum += one ? alpha * (1.f - c) * (1.f - c) * -logf(c) : (1.f - alpha) * c * c * -log1pf(-c);
+  }
+  double s0 = cls_sum, s1 = reg_sum, s2 = npos;
+  block_sum3(s0, s1, s2, s_red);
+  if (t == 0) {
+    double* p = partials + ((long)b * gridDim.x + blockIdx.x) * 3;
+    p[0] = s0; p[1] = s1; p[2] = s2;
+  }
+}
+
+// One CTA: per-sample sums in a fixed order, the normalisations of losses.py:113,157 and the batch mean (:169).
+// per_sample[b] = { classification loss of sample b, box loss of sample b, number of positive anchors }.
+__global__ void __launch_bounds__(1024) focal_finalize_kernel(int B, int nblk, const double* __restrict__ partials,
+                                                              double* __restrict__ per_sample,
+                                                              float* __restrict__ losses) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int b = w; b < B; b += nw) {
+    double s0 = 0, s1 = 0, s2 = 0;
+    for (int i = lane; i < nblk; i += 32) {
+      const double* p = partials + ((long)b * nblk + i) * 3;
+      s0 += p[0]; s1 += p[1]; s2 += p[2];
+    }
+    s0 = warp_sum_d(s0); s1 = warp_sum_d(s1); s2 = warp_sum_d(s2);
+    if (lane == 0) {
+      per_sample[b * 3 + 0] = s0 / fmax(s2, 1.0);
+      per_sample[b * 3 + 1] = s2 > 0 ? s1 / (4.0 * s2) : 0.0;
+      per_sample[b * 3 + 2] = s2;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double c = 0, r = 0;
+    for (int b = 0; b < B; b++) { c += per_sample[b * 3]; r += per_sample[b * 3 + 1]; }
+    losses[0] = (float)(c / B);
+    losses[1] = (float)(r / B);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) focal_backward_kernel(
+    int B, int A, int K, int M, const float* __restrict__ cls, const float* __restrict__ reg,
+    const float4* __restrict__ anchors, const float* __restrict__ ann_all, float alpha,
+    const int* __restrict__ assign, const double* __restrict__ per_sample, const float* __restrict__ dloss,
+    float* __restrict__ dcls, float* __restrict__ dreg) {
+  __shared__ int s_state[kThreads];
+  __shared__ int s_class[kThreads];
+  int b = blockIdx.y;
+  long a0 = (long)blockIdx.x * kThreads;
+  int na = (int)min((long)kThreads, A - a0);
+  const float* ann = ann_all + (long)b * M * 5;
+  double npos = per_sample[b * 3 + 2];
+  float scale_c = (float)((double)dloss[0] / B / fmax(npos, 1.0));
+  float scale_r = npos > 0 ? (float)((double)dloss[1] / B / (4.0 * npos)) : 0.f;
+  int t = threadIdx.x;
+  if (t < na) {
+    long ia = (long)b * A + a0 + t;
+    int st = assign[ia];
+    s_state[t] = st;
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (st >= 0) {
+      const float* g5 = ann + st * 5;
+      s_class[t] = (int)(long)g5[4];
+      float4 d = box_residual(anchors[a0 + t], make_float4(g5[0], g5[1], g5[2], g5[3]),
+                              reinterpret_cast<const float4*>(reg)[ia]);
+      // residual = target - prediction: d/d prediction = -smooth_l1'(residual)
+      o = make_float4(-smooth_l1_grad(d.x) * scale_r, -smooth_l1_grad(d.y) * scale_r,
+                      -smooth_l1_grad(d.z) * scale_r, -smooth_l1_grad(d.w) * scale_r);
+    }
+    reinterpret_cast<float4*>(dreg)[ia] = o;
+  }
+  __syncthreads();
+  const float* c0 = cls + ((long)b * A + a0) * K;
+  float* d0 = dcls + ((long)b * A + a0) * K;
+  int count = na * K;
+  for (int i = t; i < count; i += kThreads) {
+    int al = i / K, k = i - al * K;
+    int st = s_state[al];
+    float raw = __ldg(c0 + i), g = 0.f;
+    if (st != kIgnore && raw >= 1e-4f && raw <= 1.0f - 1e-4f) {            // clamp passes gradient inside only
+      float c = raw;
+      bool one = st >= 0 && s_class[al] == k;
+      g = one ? alpha * (2.f * (1.f - c) * logf(c) - (1.f - c) * (1.f - c) / c)
+              : (1.f - alpha) * (2.f * c * -log1pf(-c) + c * c / (1.f - c));
+      g *= scale_c;
+    }
+    d0[i] = g;
+  }
+}
+
+size_t focal_assign_bytes(int B, int A) { return align_up((size_t)B * A * sizeof(int)); }
+
+}  // namespace
+}  // namespace frn
+
+using namespace frn;
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+long frn_anchors_count(int H, int W, int n_levels, const int* pyramid_levels, int boxes_per_cell) {
+  if (H <= 0 || W <= 0 || n_levels <= 0 || !pyramid_levels || boxes_per_cell <= 0) return 0;
+  long total = 0;
+  for (int l = 0; l < n_levels; l++) {
+    long s = 1L << pyramid_levels[l];
+    total += ((H + s - 1) / s) * ((W + s - 1) / s) * boxes_per_cell;      // anchors.py:30
+  }
+  return total;
+}
+
+int frn_anchors_generate(void* stream, int H, int W, int n_levels, const int* pyramid_levels, const int* strides,
+                         const int* sizes, int n_ratios, const double* ratios, int n_scales, const double* scales,
+                         float* out) {
+  if (!pyramid_levels || !strides || !sizes || !ratios || !scales || !out) return FRN_ERR_NULL_POINTER;
+  int nA = n_ratios * n_scales;
+  if (H <= 0 || W <= 0 || n_levels <= 0 || n_ratios <= 0 || n_scales <= 0) return FRN_ERR_BAD_SHAPE;
+  if (nA > kMaxBase) return FRN_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  long offset = 0;
+  for (int l = 0; l < n_levels; l++) {
+    if (pyramid_levels[l] < 0 || pyramid_levels[l] > 30) return FRN_ERR_BAD_SHAPE;
+    BaseBoxes base;
+    // generate_anchors (anchors.py:47-82) in double: box i pairs ratio i / n_scales with scale i % n_scales
+    for (int i = 0; i < nA; i++) {
+      double ratio = ratios[i / n_scales], side = (double)sizes[l] * scales[i % n_scales];
+      double area = side * side;
+      double w = sqrt(area / ratio);
+      double h = w * ratio;
+      base.v[i][0] = 0.0 - w * 0.5; base.v[i][1] = 0.0 - h * 0.5;
+      base.v[i][2] = w - w * 0.5;   base.v[i][3] = h - h * 0.5;
+    }
+    long s = 1L << pyramid_levels[l];
+    int fh = (int)((H + s - 1) / s), fw = (int)((W + s - 1) / s);
+    long total = (long)fh * fw * nA;
+    anchors_level_kernel<<<cdiv(total, kThreads), kThreads, 0, st>>>(fh, fw, nA, strides[l], base,
+                                                                     reinterpret_cast<float4*>(out) + offset);
+    FRN_LAUNCH_CHECK();
+    offset += total;
+  }
+  return FRN_OK;
+}
+
+size_t frn_focal_loss_saved_bytes(int B, int A) {
+  if (B <= 0 || A <= 0) return 0;
+  return focal_assign_bytes(B, A) + align_up((size_t)B * 3 * sizeof(double));
+}
+size_t frn_focal_loss_workspace_bytes(int B, int A) {
+  if (B <= 0 || A <= 0) return 0;
+  return align_up((size_t)B * cdiv(A, kThreads) * 3 * sizeof(double));
+}
+
+int frn_focal_loss_forward(void* stream, int B, int A, int K, int M, const float* classifications,
+                           const float* regressions, const float* anchors, const float* annotations, float alpha,
+                           float* losses, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes) {
+  if (B <= 0 || A <= 0 || K <= 0 || M < 0) return FRN_ERR_BAD_SHAPE;
+  if (M > kMaxAnn) return FRN_ERR_UNSUPPORTED;
+  if (!classifications || !regressions || !anchors || !losses || !saved || !ws || (M > 0 && !annotations))
+    return FRN_ERR_NULL_POINTER;
+  if (saved_bytes < frn_focal_loss_saved_bytes(B, A) || ws_bytes < frn_focal_loss_workspace_bytes(B, A))
+    return FRN_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  int* assign = (int*)saved;
+  double* per_sample = (double*)((char*)saved + focal_assign_bytes(B, A));
+  int nblk = cdiv(A, kThreads);
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  focal_forward_kernel<<<dim3(nblk, B), kThreads, (size_t)M * 5 * sizeof(float), st>>>(
+      A, K, M, classifications, regressions, reinterpret_cast<const float4*>(anchors), annotations, alpha, assign,
+      (double*)ws);
+  FRN_LAUNCH_CHECK();
+  focal_finalize_kernel<<<1, 1024, 0, st>>>(B, nblk, (const double*)ws, per_sample, losses);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+int frn_focal_loss_backward(void* stream, int B, int A, int K, int M, const float* classifications,
+                            const float* regressions, const float* anchors, const float* annotations, float alpha,
+                            const void* saved, const float* dlosses, float* dclassifications, float* dregressions) {
+  if (B <= 0 || A <= 0 || K <= 0 || M < 0) return FRN_ERR_BAD_SHAPE;
+  if (M > kMaxAnn) return FRN_ERR_UNSUPPORTED;
+  if (!classifications || !regressions || !anchors || !saved || !dlosses || !dclassifications || !dregressions ||
+      (M > 0 && !annotations))
+    return FRN_ERR_NULL_POINTER;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int* assign = (const int*)saved;
+  const double* per_sample = (const double*)((const char*)saved + focal_assign_bytes(B, A));
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  focal_backward_kernel<<<dim3(cdiv(A, kThreads), B), kThreads, 0, st>>>(
+      B, A, K, M, classifications, regressions, reinterpret_cast<const float4*>(anchors), annotations, alpha, assign,
+      per_sample, dlosses, dclassifications, dregressions);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+}  // extern "C"
+#pragma GCC visibility pop
