@@ -75,6 +75,16 @@ _SIGNATURES = {
     "frn_conv1x1_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
     "frn_conv1x1_forward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 5 + [C.c_size_t]),
     "frn_conv1x1_backward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 7 + [C.c_size_t]),
+    "frn_anchors_count": (C.c_long, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int]),
+    "frn_anchors_generate": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                       C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_double), C.c_int,
+                                       C.POINTER(C.c_double), C.c_void_p]),
+    "frn_focal_loss_saved_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "frn_focal_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "frn_focal_loss_forward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 4 + [C.c_float, C.c_void_p,
+                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "frn_focal_loss_backward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 4 + [C.c_float] +
+                                [C.c_void_p] * 4),
     "frn_set_gemm_engine": (None, [C.c_int]),
     "frn_get_gemm_engine": (C.c_int, []),
     "frn_set_attn_engine": (None, [C.c_int]),

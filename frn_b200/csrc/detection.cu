@@ -20,6 +20,7 @@ namespace frn {
 namespace {
 
 constexpr int kThreads = 256;
+constexpr int kAnch = 1024;            // anchors per CTA of the focal-loss kernels (4 per thread)
 constexpr int kMaxAnn = 2048;          // annotations per sample staged in shared memory (5 floats each)
 constexpr int kMaxBase = 32;           // ratios x scales per cell
 
@@ -119,36 +120,49 @@ __device__ __forceinline__ float smooth_l1_grad(float d) {     // d/dd
   return d > 0.f ? g : (d < 0.f ? -g : 0.f);
 }
 
-// grid (ceil(A / 256), B).  CTA = 256 consecutive anchors of one sample.
+// -log(1 - c) and (1 - c) of a clamped score.  A score clamped to the upper bound is 1 - 1e-4 in exact
+// arithmetic; fp32 cannot hold that bound (0.9999f = 1 - 1.00017e-4), so the two quantities that depend on
+// 1 - c take their exact values there (the reference's fp32 result is off by 1.7e-4 relative on those terms).
+__device__ __forceinline__ void one_minus(float raw, float c, float& omc, float& neg_log_omc) {
+  bool top = raw > 1.0f - 1e-4f;
+  omc = top ? 1e-4f : 1.f - c;
+  neg_log_omc = top ? 9.210340371976182f : -log1pf(-c);
+}
+
+// grid (ceil(A / kAnch), B).  CTA = kAnch consecutive anchors of one sample, 4 per thread.
 __global__ void __launch_bounds__(kThreads) focal_forward_kernel(
     int A, int K, int M, const float* __restrict__ cls, const float* __restrict__ reg,
     const float4* __restrict__ anchors, const float* __restrict__ ann_all, float alpha,
     int* __restrict__ assign_out, double* __restrict__ partials) {
   extern __shared__ float s_ann[];                     // M x 5
-  __shared__ int s_state[kThreads];                    // assignment of the CTA's anchors
-  __shared__ int s_class[kThreads];                    // class of the matched annotation (positives)
+  __shared__ short s_class[kAnch];                     // kIgnore / kNegative / class of the matched annotation
   __shared__ double s_red[kThreads / 32][3];
   int b = blockIdx.y;
-  long a0 = (long)blockIdx.x * kThreads;
-  int na = (int)min((long)kThreads, A - a0);
+  long a0 = (long)blockIdx.x * kAnch;
+  int na = (int)min((long)kAnch, A - a0);
   const float* ann = ann_all + (long)b * M * 5;
   for (int i = threadIdx.x; i < M * 5; i += kThreads) s_ann[i] = ann[i];
   __syncthreads();
 
   float cls_sum = 0.f, reg_sum = 0.f, npos = 0.f;
-  int t = threadIdx.x;
-  if (t < na) {
-    float4 a = anchors[a0 + t];
-    int st = assign_anchor(a, s_ann, M);
-    s_state[t] = st;
-    assign_out[(long)b * A + a0 + t] = st;
-    if (st >= 0) {
-      s_class[t] = (int)(long)s_ann[st * 5 + 4];
-      float4 g = make_float4(s_ann[st * 5], s_ann[st * 5 + 1], s_ann[st * 5 + 2], s_ann[st * 5 + 3]);
-      float4 r = reinterpret_cast<const float4*>(reg)[(long)b * A + a0 + t];
-      float4 d = box_residual(a, g, r);
-      reg_sum = smooth_l1(d.x) + smooth_l1(d.y) + smooth_l1(d.z) + smooth_l1(d.w);
-      npos = 1.f;
+#pragma unroll
+  for (int u = 0; u < kAnch / kThreads; u++) {
+    int t = threadIdx.x + u * kThreads;
+    if (t < na) {
+      float4 a = anchors[a0 + t];
+      int st = assign_anchor(a, s_ann, M);
+      assign_out[(long)b * A + a0 + t] = st;
+      int code = st;
+      if (st >= 0) {
+        code = (int)(long)s_ann[st * 5 + 4];
+        float4 g = make_float4(s_ann[st * 5], s_ann[st * 5 + 1], s_ann[st * 5 + 2], s_ann[st * 5 + 3]);
+        float4 r = reinterpret_cast<const float4*>(reg)[(long)b * A + a0 + t];
+        float4 d = box_residual(a, g, r);
+        reg_sum += smooth_l1(d.x) + smooth_l1(d.y) + smooth_l1(d.z) + smooth_l1(d.w);
+        npos += 1.f;
+        if (code < 0 || code > 32767) code = 32767;              // never equals a class index below
+      }
+      s_class[t] = (short)code;
     }
   }
   __syncthreads();
@@ -156,18 +170,21 @@ __global__ void __launch_bounds__(kThreads) focal_forward_kernel(
   // classification terms: the CTA's na*K scores are contiguous in (B, A, K)
   const float* c0 = cls + ((long)b * A + a0) * K;
   int count = na * K;
-  for (int i = t; i < count; i += kThreads) {
+#pragma unroll 4
+  for (int i = threadIdx.x; i < count; i += kThreads) {
     int al = i / K, k = i - al * K;
-    int st = s_state[al];
-    if (st == kIgnore) continue;
-    float c = fminf(fmaxf(__ldg(c0 + i), 1e-4f), 1.0f - 1e-4f);            // losses.py:46
-    bool one = st >= 0 && s_class[al] == k;
+    int code = s_class[al];
+    float raw = __ldg(c0 + i);
+    if (code == kIgnore) continue;
+    float c = fminf(fmaxf(raw, 1e-4f), 1.0f - 1e-4f);                       // losses.py:46
+    float omc, nl;
+    one_minus(raw, c, omc, nl);
     // alpha (1-c)^2 (-log c)  |  (1-alpha) c^2 (-log(1-c))    (losses.py:98-106, gamma = 2)
-    cls_sum += one ? alpha * (1.f - c) * (1.f - c) * -logf(c) : (1.f - alpha) * c * c * -log1pf(-c);
+    cls_sum += code == k ? alpha * omc * omc * -logf(c) : (1.f - alpha) * c * c * nl;
   }
   double s0 = cls_sum, s1 = reg_sum, s2 = npos;
   block_sum3(s0, s1, s2, s_red);
-  if (t == 0) {
+  if (threadIdx.x == 0) {
     double* p = partials + ((long)b * gridDim.x + blockIdx.x) * 3;
     p[0] = s0; p[1] = s1; p[2] = s2;
   }
@@ -206,45 +223,49 @@ __global__ void __launch_bounds__(kThreads) focal_backward_kernel(
     const float4* __restrict__ anchors, const float* __restrict__ ann_all, float alpha,
     const int* __restrict__ assign, const double* __restrict__ per_sample, const float* __restrict__ dloss,
     float* __restrict__ dcls, float* __restrict__ dreg) {
-  __shared__ int s_state[kThreads];
-  __shared__ int s_class[kThreads];
+  __shared__ short s_class[kAnch];
   int b = blockIdx.y;
-  long a0 = (long)blockIdx.x * kThreads;
-  int na = (int)min((long)kThreads, A - a0);
+  long a0 = (long)blockIdx.x * kAnch;
+  int na = (int)min((long)kAnch, A - a0);
   const float* ann = ann_all + (long)b * M * 5;
   double npos = per_sample[b * 3 + 2];
   float scale_c = (float)((double)dloss[0] / B / fmax(npos, 1.0));
   float scale_r = npos > 0 ? (float)((double)dloss[1] / B / (4.0 * npos)) : 0.f;
-  int t = threadIdx.x;
-  if (t < na) {
-    long ia = (long)b * A + a0 + t;
-    int st = assign[ia];
-    s_state[t] = st;
-    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (st >= 0) {
-      const float* g5 = ann + st * 5;
-      s_class[t] = (int)(long)g5[4];
-      float4 d = box_residual(anchors[a0 + t], make_float4(g5[0], g5[1], g5[2], g5[3]),
-                              reinterpret_cast<const float4*>(reg)[ia]);
-      // residual = target - prediction: d/d prediction = -smooth_l1'(residual)
-      o = make_float4(-smooth_l1_grad(d.x) * scale_r, -smooth_l1_grad(d.y) * scale_r,
-                      -smooth_l1_grad(d.z) * scale_r, -smooth_l1_grad(d.w) * scale_r);
+#pragma unroll
+  for (int u = 0; u < kAnch / kThreads; u++) {
+    int t = threadIdx.x + u * kThreads;
+    if (t < na) {
+      long ia = (long)b * A + a0 + t;
+      int st = assign[ia];
+      int code = st;
+      float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (st >= 0) {
+        const float* g5 = ann + st * 5;
+        code = (int)(long)g5[4];
+        if (code < 0 || code > 32767) code = 32767;
+        float4 d = box_residual(anchors[a0 + t], make_float4(g5[0], g5[1], g5[2], g5[3]),
+                                reinterpret_cast<const float4*>(reg)[ia]);
+        // residual = target - prediction: d/d prediction = -smooth_l1'(residual)
+        o = make_float4(-smooth_l1_grad(d.x) * scale_r, -smooth_l1_grad(d.y) * scale_r,
+                        -smooth_l1_grad(d.z) * scale_r, -smooth_l1_grad(d.w) * scale_r);
+      }
+      s_class[t] = (short)code;
+      reinterpret_cast<float4*>(dreg)[ia] = o;
     }
-    reinterpret_cast<float4*>(dreg)[ia] = o;
   }
   __syncthreads();
   const float* c0 = cls + ((long)b * A + a0) * K;
   float* d0 = dcls + ((long)b * A + a0) * K;
   int count = na * K;
-  for (int i = t; i < count; i += kThreads) {
+#pragma unroll 4
+  for (int i = threadIdx.x; i < count; i += kThreads) {
     int al = i / K, k = i - al * K;
-    int st = s_state[al];
-    float raw = __ldg(c0 + i), g = 0.f;
-    if (st != kIgnore && raw >= 1e-4f && raw <= 1.0f - 1e-4f) {            // clamp passes gradient inside only
-      float c = raw;
-      bool one = st >= 0 && s_class[al] == k;
-      g = one ? alpha * (2.f * (1.f - c) * logf(c) - (1.f - c) * (1.f - c) / c)
-              : (1.f - alpha) * (2.f * c * -log1pf(-c) + c * c / (1.f - c));
+    int code = s_class[al];
+    float c = __ldg(c0 + i), g = 0.f;
+    if (code != kIgnore && c >= 1e-4f && c <= 1.0f - 1e-4f) {              // clamp passes gradient inside only
+      float omc = 1.f - c;
+      g = code == k ? alpha * (2.f * omc * logf(c) - omc * omc / c)
+                    : (1.f - alpha) * (2.f * c * -log1pf(-c) + c * c / omc);
       g *= scale_c;
     }
     d0[i] = g;
@@ -309,7 +330,7 @@ size_t frn_focal_loss_saved_bytes(int B, int A) {
 }
 size_t frn_focal_loss_workspace_bytes(int B, int A) {
   if (B <= 0 || A <= 0) return 0;
-  return align_up((size_t)B * cdiv(A, kThreads) * 3 * sizeof(double));
+  return align_up((size_t)B * cdiv(A, kAnch) * 3 * sizeof(double));
 }
 
 int frn_focal_loss_forward(void* stream, int B, int A, int K, int M, const float* classifications,
@@ -324,7 +345,7 @@ int frn_focal_loss_forward(void* stream, int B, int A, int K, int M, const float
   cudaStream_t st = (cudaStream_t)stream;
   int* assign = (int*)saved;
   double* per_sample = (double*)((char*)saved + focal_assign_bytes(B, A));
-  int nblk = cdiv(A, kThreads);
+  int nblk = cdiv(A, kAnch);
   ScopedTimer tm(st, FRN_TIME_ROWS);
   focal_forward_kernel<<<dim3(nblk, B), kThreads, (size_t)M * 5 * sizeof(float), st>>>(
       A, K, M, classifications, regressions, reinterpret_cast<const float4*>(anchors), annotations, alpha, assign,
@@ -347,7 +368,7 @@ int frn_focal_loss_backward(void* stream, int B, int A, int K, int M, const floa
   const int* assign = (const int*)saved;
   const double* per_sample = (const double*)((const char*)saved + focal_assign_bytes(B, A));
   ScopedTimer tm(st, FRN_TIME_ROWS);
-  focal_backward_kernel<<<dim3(cdiv(A, kThreads), B), kThreads, 0, st>>>(
+  focal_backward_kernel<<<dim3(cdiv(A, kAnch), B), kThreads, 0, st>>>(
       B, A, K, M, classifications, regressions, reinterpret_cast<const float4*>(anchors), annotations, alpha, assign,
       per_sample, dlosses, dclassifications, dregressions);
   FRN_LAUNCH_CHECK();

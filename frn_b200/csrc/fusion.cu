@@ -501,7 +501,8 @@ const char* frn_kernel_inventory(void) {
          "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
          "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
-         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel";
+         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,"
+         "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel";
 }
 
 // ---- GEMM ----------------------------------------------------------------------

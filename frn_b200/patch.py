@@ -12,16 +12,18 @@ import sys
 
 
 def patch_reference(package: str = "retinanet"):
-    """Rebind REFusion / CrossAttentionBlock / AdaIN_block inside `package`.  Returns the
+    """Rebind REFusion / CrossAttentionBlock / AdaIN_block (and Anchors / FocalLoss, row f2) inside `package`.  Returns the
     list of (module, attribute) pairs that were rebound."""
-    from . import modules
+    from . import detection, modules
 
     done = []
     targets = {
         f"{package}.AdaIN": ("AdaIN_block",),
         f"{package}.Attention": ("CrossAttentionBlock", "AdaIN_block"),
         f"{package}.fusion": ("REFusion", "CrossAttentionBlock", "AdaIN_block"),
-        f"{package}.model": ("REFusion",),
+        f"{package}.model": ("REFusion", "Anchors"),          # model.py:7,221: `self.anchors = Anchors()`
+        f"{package}.anchors": ("Anchors",),
+        f"{package}.losses": ("FocalLoss",),                  # model.py:227: `losses.FocalLoss()`
     }
     for mod_name, attrs in targets.items():
         mod = sys.modules.get(mod_name)
@@ -32,6 +34,6 @@ def patch_reference(package: str = "retinanet"):
                 continue
         for attr in attrs:
             if hasattr(mod, attr):
-                setattr(mod, attr, getattr(modules, attr))
+                setattr(mod, attr, getattr(modules, attr, None) or getattr(detection, attr))
                 done.append((mod_name, attr))
     return done

@@ -205,6 +205,35 @@ int frn_conv1x1_forward(void* stream, int B, int Cin, int Cout, int N, const flo
 int frn_conv1x1_backward(void* stream, int B, int Cin, int Cout, int N, const float* x, const float* w,
                          const float* dy, float* dx, float* dw, float* db, void* ws, size_t ws_bytes);
 
+/* ---- anchors + focal loss ----------------------------------------------------
+ * frn_anchors_generate replaces Anchors.forward (retinanet/anchors.py:25-45, generate_anchors :47-82, shift
+ * :120-147): all boxes of an H x W image over the pyramid levels, (1, A, 4) fp32 (x1, y1, x2, y2), cells
+ * row-major and the n_ratios * n_scales boxes of a cell adjacent, computed in double and rounded once --
+ * bit-identical to the NumPy result.  pyramid_levels, strides, sizes (n_levels ints), ratios and scales are
+ * HOST arrays; out is a device pointer to frn_anchors_count(...) * 4 floats.
+ *
+ * frn_focal_loss_forward replaces FocalLoss.forward (retinanet/losses.py:28-169, calc_iou :5-24):
+ * classifications (B, A, K) in (0, 1), regressions (B, A, 4), anchors (A, 4), annotations (B, M, 5) =
+ * (x1, y1, x2, y2, class) padded with class == -1 rows (M may be 0); gamma = 2.  losses[0] = mean over the batch
+ * of the classification loss, losses[1] = of the box loss (the two (1,) tensors the reference returns).
+ * `saved` keeps the per-(sample, anchor) assignment as int32 (>= 0: matched annotation row, -1: background,
+ * -2: ignored) followed (at the next 256-byte boundary) by B x 3 doubles {classification loss, box loss,
+ * positives} per sample.  The IoU thresholds are evaluated with the reference's fp32 operation order, so the
+ * assignment is bit-identical to the reference's.  backward: dlosses = 2 device floats (upstream gradients of
+ * the two outputs); dclassifications and dregressions are overwritten.  No host synchronisation. */
+long frn_anchors_count(int H, int W, int n_levels, const int* pyramid_levels, int boxes_per_cell);
+int frn_anchors_generate(void* stream, int H, int W, int n_levels, const int* pyramid_levels, const int* strides,
+                         const int* sizes, int n_ratios, const double* ratios, int n_scales, const double* scales,
+                         float* out);
+size_t frn_focal_loss_saved_bytes(int B, int A);
+size_t frn_focal_loss_workspace_bytes(int B, int A);
+int frn_focal_loss_forward(void* stream, int B, int A, int K, int M, const float* classifications,
+                           const float* regressions, const float* anchors, const float* annotations, float alpha,
+                           float* losses, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes);
+int frn_focal_loss_backward(void* stream, int B, int A, int K, int M, const float* classifications,
+                            const float* regressions, const float* anchors, const float* annotations, float alpha,
+                            const void* saved, const float* dlosses, float* dclassifications, float* dregressions);
+
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
  * launching stream.  Classes: 0 = streaming attention forward, 1 = streaming

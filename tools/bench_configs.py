@@ -109,16 +109,19 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--only", type=int, default=-1, help="run only the i-th config (0-based)")
     args = ap.parse_args()
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
         peaks = {"hbm_gbs": 6650.0, "bf16_tflops_sustained": 1400.0}
-    run("config 4: DDD17 346x260 inference, batch=32, bf16", DDD17, 32, torch.bfloat16, False, args.steps, args.warmup, peaks)
-    run("DDD17 346x260 fp32 inference, batch=32", DDD17, 32, torch.float32, False, args.steps, args.warmup, peaks)
-    run("DDD17 346x260 fp32 fwd+bwd, batch=8", DDD17, 8, torch.float32, True, args.steps, args.warmup, peaks)
-    run("config 1 on the GPU: REFusion(256) fwd+bwd, batch=1, DSEC level 1", DSEC[:1], 1, torch.float32, True,
-        args.steps, args.warmup, peaks)
+    configs = [("config 4: DDD17 346x260 inference, batch=32, bf16", DDD17, 32, torch.bfloat16, False),
+               ("DDD17 346x260 fp32 inference, batch=32", DDD17, 32, torch.float32, False),
+               ("DDD17 346x260 fp32 fwd+bwd, batch=8", DDD17, 8, torch.float32, True),
+               ("config 1 on the GPU: REFusion(256) fwd+bwd, batch=1, DSEC level 1", DSEC[:1], 1, torch.float32, True)]
+    for i, (name, levels, batch, dtype, train) in enumerate(configs):
+        if args.only < 0 or args.only == i:
+            run(name, levels, batch, dtype, train, args.steps, args.warmup, peaks)
 
 
 if __name__ == "__main__":
