@@ -21,7 +21,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kAnch = 1024;            // anchors per CTA of the focal-loss kernels (4 per thread)
-constexpr int kMaxAnn = 2048;          // annotations per sample staged in shared memory (5 floats each)
+constexpr int kMaxAnn = 1024;          // annotation rows per sample staged in shared memory (6 floats each)
 constexpr int kMaxBase = 32;           // ratios x scales per cell
 
 struct BaseBoxes { double v[kMaxBase][4]; };
@@ -53,28 +53,36 @@ constexpr int kNegative = -1, kIgnore = -2;
 
 // calc_iou (losses.py:5-24) in the reference's own operation order, every step rounded to fp32 separately
 // (no FMA contraction) so that the 0.4 / 0.5 thresholds fall exactly where the reference's fp32 ATen ops
-// put them.
-__device__ __forceinline__ float iou_f32(float4 a, float area_a, float4 b) {
-  float area_b = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
-  float iw = fmaxf(__fsub_rn(fminf(a.z, b.z), fmaxf(a.x, b.x)), 0.f);
-  float ih = fmaxf(__fsub_rn(fminf(a.w, b.w), fmaxf(a.y, b.y)), 0.f);
-  float inter = __fmul_rn(iw, ih);
-  float ua = fmaxf(__fsub_rn(__fadd_rn(area_a, area_b), inter), 1e-8f);
-  return __fdiv_rn(inter, ua);
-}
-
-__device__ __forceinline__ int assign_anchor(float4 a, const float* __restrict__ ann, int M) {
-  float area_a = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
-  float best = -1.f;
-  int arg = -1;
-  for (int j = 0; j < M; j++) {
-    if (ann[j * 5 + 4] == -1.f) continue;                          // padding rows (losses.py:45)
-    float4 g = make_float4(ann[j * 5], ann[j * 5 + 1], ann[j * 5 + 2], ann[j * 5 + 3]);
-    float v = iou_f32(a, area_a, g);
-    if (v > best) { best = v; arg = j; }                           // first maximum wins (torch.max on CPU)
+// put them (assign_anchors below).
+// Assignment of kAnch / kThreads anchors at once against the sample's annotations in shared memory
+// (ann: M x 5, area: M precomputed box areas).  Pairs that do not overlap have IoU = 0 / ua = 0 exactly and
+// skip the division.
+template <int U>
+__device__ __forceinline__ void assign_anchors(const float4 (&a)[U], const float* __restrict__ ann,
+                                               const float* __restrict__ area, int M, int (&state)[U]) {
+  float area_a[U], best[U];
+  int arg[U];
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    area_a[u] = __fmul_rn(__fsub_rn(a[u].z, a[u].x), __fsub_rn(a[u].w, a[u].y));
+    best[u] = -1.f; arg[u] = -1;
   }
-  if (arg < 0 || best < 0.4f) return kNegative;                    // no annotation at all: losses.py:48-79
-  return best >= 0.5f ? arg : kIgnore;
+  for (int j = 0; j < M; j++) {
+    if (ann[j * 5 + 4] == -1.f) continue;                          // padding rows (losses.py:45); CTA-uniform
+    float4 g = make_float4(ann[j * 5], ann[j * 5 + 1], ann[j * 5 + 2], ann[j * 5 + 3]);
+    float area_b = area[j];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      float iw = fmaxf(__fsub_rn(fminf(a[u].z, g.z), fmaxf(a[u].x, g.x)), 0.f);
+      float ih = fmaxf(__fsub_rn(fminf(a[u].w, g.w), fmaxf(a[u].y, g.y)), 0.f);
+      float inter = __fmul_rn(iw, ih), v = 0.f;
+      if (inter > 0.f) v = __fdiv_rn(inter, fmaxf(__fsub_rn(__fadd_rn(area_a[u], area_b), inter), 1e-8f));
+      if (v > best[u]) { best[u] = v; arg[u] = j; }                // first maximum wins (torch.max on CPU)
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; u++)                                      // no annotation at all: losses.py:48-79
+    state[u] = (arg[u] < 0 || best[u] < 0.4f) ? kNegative : (best[u] >= 0.5f ? arg[u] : kIgnore);
 }
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -134,7 +142,7 @@ __global__ void __launch_bounds__(kThreads) focal_forward_kernel(
     int A, int K, int M, const float* __restrict__ cls, const float* __restrict__ reg,
     const float4* __restrict__ anchors, const float* __restrict__ ann_all, float alpha,
     int* __restrict__ assign_out, double* __restrict__ partials) {
-  extern __shared__ float s_ann[];                     // M x 5
+  extern __shared__ float s_ann[];                     // M x 5, then M box areas
   __shared__ short s_class[kAnch];                     // kIgnore / kNegative / class of the matched annotation
   __shared__ double s_red[kThreads / 32][3];
   int b = blockIdx.y;
@@ -142,22 +150,33 @@ __global__ void __launch_bounds__(kThreads) focal_forward_kernel(
   int na = (int)min((long)kAnch, A - a0);
   const float* ann = ann_all + (long)b * M * 5;
   for (int i = threadIdx.x; i < M * 5; i += kThreads) s_ann[i] = ann[i];
+  float* s_area = s_ann + M * 5;
+  for (int j = threadIdx.x; j < M; j += kThreads)
+    s_area[j] = __fmul_rn(__fsub_rn(ann[j * 5 + 2], ann[j * 5]), __fsub_rn(ann[j * 5 + 3], ann[j * 5 + 1]));
   __syncthreads();
 
   float cls_sum = 0.f, reg_sum = 0.f, npos = 0.f;
+  constexpr int U = kAnch / kThreads;
+  float4 a[U];
+  int state[U];
 #pragma unroll
-  for (int u = 0; u < kAnch / kThreads; u++) {
+  for (int u = 0; u < U; u++) {
+    int t = threadIdx.x + u * kThreads;
+    a[u] = t < na ? anchors[a0 + t] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  assign_anchors<U>(a, s_ann, s_area, M, state);
+#pragma unroll
+  for (int u = 0; u < U; u++) {
     int t = threadIdx.x + u * kThreads;
     if (t < na) {
-      float4 a = anchors[a0 + t];
-      int st = assign_anchor(a, s_ann, M);
+      int st = state[u];
       assign_out[(long)b * A + a0 + t] = st;
       int code = st;
       if (st >= 0) {
         code = (int)(long)s_ann[st * 5 + 4];
         float4 g = make_float4(s_ann[st * 5], s_ann[st * 5 + 1], s_ann[st * 5 + 2], s_ann[st * 5 + 3]);
         float4 r = reinterpret_cast<const float4*>(reg)[(long)b * A + a0 + t];
-        float4 d = box_residual(a, g, r);
+        float4 d = box_residual(a[u], g, r);
         reg_sum += smooth_l1(d.x) + smooth_l1(d.y) + smooth_l1(d.z) + smooth_l1(d.w);
         npos += 1.f;
         if (code < 0 || code > 32767) code = 32767;              // never equals a class index below
@@ -347,7 +366,7 @@ int frn_focal_loss_forward(void* stream, int B, int A, int K, int M, const float
   double* per_sample = (double*)((char*)saved + focal_assign_bytes(B, A));
   int nblk = cdiv(A, kAnch);
   ScopedTimer tm(st, FRN_TIME_ROWS);
-  focal_forward_kernel<<<dim3(nblk, B), kThreads, (size_t)M * 5 * sizeof(float), st>>>(
+  focal_forward_kernel<<<dim3(nblk, B), kThreads, (size_t)M * 6 * sizeof(float), st>>>(
       A, K, M, classifications, regressions, reinterpret_cast<const float4*>(anchors), annotations, alpha, assign,
       (double*)ws);
   FRN_LAUNCH_CHECK();

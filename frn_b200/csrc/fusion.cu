@@ -502,7 +502,8 @@ const char* frn_kernel_inventory(void) {
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
          "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
          "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,"
-         "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel";
+         "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel,"
+         "event_bounds_kernel,event_scatter_kernel,voxel_normalize_kernel";
 }
 
 // ---- GEMM ----------------------------------------------------------------------

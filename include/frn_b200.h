@@ -214,7 +214,7 @@ int frn_conv1x1_backward(void* stream, int B, int Cin, int Cout, int N, const fl
  *
  * frn_focal_loss_forward replaces FocalLoss.forward (retinanet/losses.py:28-169, calc_iou :5-24):
  * classifications (B, A, K) in (0, 1), regressions (B, A, 4), anchors (A, 4), annotations (B, M, 5) =
- * (x1, y1, x2, y2, class) padded with class == -1 rows (M may be 0); gamma = 2.  losses[0] = mean over the batch
+ * (x1, y1, x2, y2, class) padded with class == -1 rows (0 <= M <= 1024); gamma = 2.  losses[0] = mean over the batch
  * of the classification loss, losses[1] = of the box loss (the two (1,) tensors the reference returns).
  * `saved` keeps the per-(sample, anchor) assignment as int32 (>= 0: matched annotation row, -1: background,
  * -2: ignored) followed (at the next 256-byte boundary) by B x 3 doubles {classification loss, box loss,
@@ -233,6 +233,21 @@ int frn_focal_loss_forward(void* stream, int B, int A, int K, int M, const float
 int frn_focal_loss_backward(void* stream, int B, int A, int K, int M, const float* classifications,
                             const float* regressions, const float* anchors, const float* annotations, float alpha,
                             const void* saved, const float* dlosses, float* dclassifications, float* dregressions);
+
+/* ---- event voxelisation ---------------------------------------------------------
+ * Replaces DSECDet.preprocess_events (retinanet/data/dsec_data.py:347-387) and normalize_event_data (:78-93).
+ * x, y: n_events coordinates (xy_bytes = 2: uint16 as stored in the DSEC h5 files, 4: int32); t: int64
+ * timestamps; p: uint8 polarity (> 0 -> +1, else -1).  Events with y >= H or x >= W are dropped; the first and
+ * last remaining event define the time window, bin = trunc((t - t_first) / (t_last - t_first + 1e-6) * (C - 1))
+ * clipped to [0, C-1], evaluated in double like NumPy.  voxel (C, H, W) fp32 is overwritten (zero when no event
+ * is in range).  normalize: 0 none, 1 tanh(v / 5), 2 clamp to [-2, 2].  The counts are bit-identical to the
+ * reference's sequential loop (sums of +-1 are exact in fp32).  ws: frn_voxelize_workspace_bytes() bytes. */
+size_t frn_voxelize_workspace_bytes(void);
+int frn_voxelize_events(void* stream, long n_events, int xy_bytes, const void* x, const void* y, const int64_t* t,
+                        const uint8_t* p, int C, int H, int W, int normalize, float* voxel, void* ws,
+                        size_t ws_bytes);
+/* normalize_event_data (dsec_data.py:78-93) in place on `count` floats: mode 1 tanh(v / 5), 2 clamp to [-2, 2]. */
+int frn_voxel_normalize(void* stream, long count, int mode, float* voxel);
 
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
