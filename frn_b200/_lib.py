@@ -89,6 +89,10 @@ _SIGNATURES = {
     "frn_voxelize_events": (C.c_int, [C.c_void_p, C.c_long, C.c_int] + [C.c_void_p] * 4 + [C.c_int] * 4 +
                             [C.c_void_p, C.c_void_p, C.c_size_t]),
     "frn_voxel_normalize": (C.c_int, [C.c_void_p, C.c_long, C.c_int, C.c_void_p]),
+    "frn_detect_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "frn_decode_boxes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "frn_detect_postprocess": (C.c_int, [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_int,
+                                         C.c_float, C.c_float, C.c_int] + [C.c_void_p] * 6 + [C.c_size_t]),
     "frn_set_gemm_engine": (None, [C.c_int]),
     "frn_get_gemm_engine": (C.c_int, []),
     "frn_set_attn_engine": (None, [C.c_int]),

@@ -134,3 +134,65 @@ class FocalLoss(nn.Module):
         assert classifications.dim() == 3 and regressions.dim() == 3 and regressions.shape[2] == 4
         assert anchors.dim() == 3 and annotations.dim() == 3 and annotations.shape[2] == 5
         return focal_loss(classifications, regressions, anchors, annotations, alpha=0.25)
+
+
+# --------------------------------------------------------------------------- row f3: inference post-processing
+def _postprocess(classification, boxes_or_none, regression, anchors, img_hw, score_threshold, iou_threshold):
+    lib = _lib.load()
+    cls = _f32c(classification)
+    a, k = cls.shape
+    dev = cls.device
+    cap = a * k
+    scores = torch.empty(cap, dtype=torch.float32, device=dev)
+    classes = torch.empty(cap, dtype=torch.int32, device=dev)
+    boxes = torch.empty((cap, 4), dtype=torch.float32, device=dev)
+    index = torch.empty(cap, dtype=torch.int32, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        ws_bytes = lib.frn_detect_workspace_bytes(a, k)
+        ws = _bytes(ws_bytes, dev)
+        if boxes_or_none is not None:
+            bx = _f32c(boxes_or_none)
+            rc = lib.frn_detect_postprocess(_stream(), a, k, _ptr(cls), None, None, _ptr(bx), 0, 0, score_threshold,
+                                            iou_threshold, cap, _ptr(scores), _ptr(classes), _ptr(boxes), _ptr(index),
+                                            _ptr(count), _ptr(ws), ws_bytes)
+        else:
+            reg, anc = _f32c(regression), _f32c(anchors)
+            rc = lib.frn_detect_postprocess(_stream(), a, k, _ptr(cls), _ptr(reg), _ptr(anc), None, int(img_hw[0]),
+                                            int(img_hw[1]), score_threshold, iou_threshold, cap, _ptr(scores),
+                                            _ptr(classes), _ptr(boxes), _ptr(index), _ptr(count), _ptr(ws), ws_bytes)
+        _lib.check(rc, "detect_postprocess")
+    n = int(count.item())                      # the one D2H read: the result tensors are sized by the data
+    return scores[:n], classes[:n], boxes[:n], index[:n]
+
+
+def detect_postprocess(classification, regression, anchors, img_batch, score_threshold=0.05, iou_threshold=0.5):
+    """model.py:326-364 (eval branch of ResNet.forward) for the reference's batch of 1: classification (1, A, K),
+    regression (1, A, 4), anchors (1, A, 4), img_batch (1, C, H, W) -> [scores, class indexes (int64), boxes]."""
+    _check_cuda(classification, regression, anchors)
+    assert classification.dim() == 3 and classification.shape[0] == 1, "batch of 1 (model.py:340 squeezes it)"
+    h, w = int(img_batch.shape[2]), int(img_batch.shape[3])
+    s, c, b, _ = _postprocess(classification[0], None, regression[0], anchors[0], (h, w), float(score_threshold),
+                              float(iou_threshold))
+    return [s, c.long(), b]
+
+
+def decode_boxes(anchors, regression, img_batch):
+    """regressBoxes + clipBoxes (model.py:326-327; utils.py:103-126, 135-145): (1, A, 4) -> (1, A, 4)."""
+    _check_cuda(anchors, regression)
+    lib = _lib.load()
+    anc, reg = _f32c(anchors[0]), _f32c(regression[0])
+    out = torch.empty_like(anc)
+    with torch.cuda.device(anc.device):
+        _lib.check(lib.frn_decode_boxes(_stream(), anc.shape[0], _ptr(anc), _ptr(reg), int(img_batch.shape[2]),
+                                        int(img_batch.shape[3]), _ptr(out)), "decode_boxes")
+    return out[None]
+
+
+def nms(boxes, scores, iou_threshold):
+    """torchvision.ops.nms(boxes (N, 4), scores (N), iou_threshold) -> int64 indices kept, by decreasing score."""
+    _check_cuda(boxes, scores)
+    if boxes.shape[0] == 0:
+        return torch.empty(0, dtype=torch.int64, device=boxes.device)
+    _, _, _, idx = _postprocess(scores.reshape(-1, 1), boxes, None, None, None, -3.0e38, float(iou_threshold))
+    return idx.long()

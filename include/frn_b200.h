@@ -249,6 +249,24 @@ int frn_voxelize_events(void* stream, long n_events, int xy_bytes, const void* x
 /* normalize_event_data (dsec_data.py:78-93) in place on `count` floats: mode 1 tanh(v / 5), 2 clamp to [-2, 2]. */
 int frn_voxel_normalize(void* stream, long count, int mode, float* voxel);
 
+/* ---- inference post-processing ---------------------------------------------------
+ * Replaces retinanet/model.py:326-364: BBoxTransform (retinanet/utils.py:103-126, std 0.1/0.1/0.2/0.2) +
+ * ClipBoxes (utils.py:135-145), then per class `scores > score_thresh`, torchvision.ops.nms(iou_thresh) and the
+ * concatenation of the classes.  Batch 1 like the reference: classification (A, K), regression (A, 4),
+ * anchors (A, 4).  If boxes_in is not NULL it is used instead of decoding (then regression / anchors may be NULL:
+ * a drop-in for torchvision.ops.nms with K = 1).  Outputs hold up to `capacity` detections, class-major and by
+ * decreasing score inside a class (score ties: lower anchor index first): out_scores, out_classes (int32),
+ * out_boxes (x1, y1, x2, y2), out_index (anchor index; may be NULL); *out_count (device int) = number of
+ * detections (may exceed capacity: the excess is not written).  The overlap test is torchvision's CPU kernel
+ * arithmetic in the same order, so the kept set is identical for identical boxes.  No host synchronisation. */
+size_t frn_detect_workspace_bytes(int A, int K);
+int frn_decode_boxes(void* stream, int A, const float* anchors, const float* regression, int img_h, int img_w,
+                     float* boxes);
+int frn_detect_postprocess(void* stream, int A, int K, const float* classification, const float* regression,
+                           const float* anchors, const float* boxes_in, int img_h, int img_w, float score_thresh,
+                           float iou_thresh, int capacity, float* out_scores, int* out_classes, float* out_boxes,
+                           int* out_index, int* out_count, void* ws, size_t ws_bytes);
+
 /* ---- measurement hooks (bench.py / profiling only) --------------------------
  * When enabled, the library brackets its hot kernels with cudaEvents on the
  * launching stream.  Classes: 0 = streaming attention forward, 1 = streaming
