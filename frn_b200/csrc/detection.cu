@@ -128,15 +128,9 @@ __device__ __forceinline__ float smooth_l1_grad(float d) {     // d/dd
   return d > 0.f ? g : (d < 0.f ? -g : 0.f);
 }
 
-// -log(1 - c) and (1 - c) of a clamped score.  A score clamped to the upper bound is 1 - 1e-4 in exact
-// arithmetic; fp32 cannot hold that bound (0.9999f = 1 - 1.00017e-4), so the two quantities that depend on
-// 1 - c take their exact values there (the reference's fp32 result is off by 1.7e-4 relative on those terms).
-__device__ __forceinline__ void one_minus(float raw, float c, float& omc, float& neg_log_omc) {
-  bool top = raw > 1.0f - 1e-4f;
-  omc = top ? 1e-4f : 1.f - c;
-  neg_log_omc = top ? 9.210340371976182f : -log1pf(-c);
-}
-
+// A score clamped to the upper bound is 1 - 1e-4 in exact arithmetic; fp32 cannot hold that bound (0.9999f =
+// 1 - 1.00017e-4), so the two quantities that depend on 1 - c take their exact values there, 1e-4 and
+// -log(1e-4) (the reference's own fp32 result is off by 1.7e-4 relative on those terms).
 // grid (ceil(A / kAnch), B).  CTA = kAnch consecutive anchors of one sample, 4 per thread.
 __global__ void __launch_bounds__(kThreads) focal_forward_kernel(
     int A, int K, int M, const float* __restrict__ cls, const float* __restrict__ reg,
@@ -196,10 +190,15 @@ __global__ void __launch_bounds__(kThreads) focal_forward_kernel(
     float raw = __ldg(c0 + i);
     if (code == kIgnore) continue;
     float c = fminf(fmaxf(raw, 1e-4f), 1.0f - 1e-4f);                       // losses.py:46
-    float omc, nl;
-    one_minus(raw, c, omc, nl);
-    // alpha (1-c)^2 (-log c)  |  (1-alpha) c^2 (-log(1-c))    (losses.py:98-106, gamma = 2)
-    cls_sum += code == k ? alpha * omc * omc * -logf(c) : (1.f - alpha) * c * c * nl;
+    // alpha (1-c)^2 (-log c)  |  (1-alpha) c^2 (-log(1-c))    (losses.py:98-106, gamma = 2); one logarithm
+    // per element: the target-1 branch is taken by one class of the few positive anchors only
+    const bool top = raw > 1.0f - 1e-4f;
+    if (code == k) {
+      const float omc = top ? 1e-4f : 1.f - c;
+      cls_sum += alpha * omc * omc * -logf(c);
+    } else {
+      cls_sum += (1.f - alpha) * c * c * (top ? 9.210340371976182f : -log1pf(-c));
+    }
   }
   double s0 = cls_sum, s1 = reg_sum, s2 = npos;
   block_sum3(s0, s1, s2, s_red);
@@ -282,9 +281,9 @@ __global__ void __launch_bounds__(kThreads) focal_backward_kernel(
     int code = s_class[al];
     float c = __ldg(c0 + i), g = 0.f;
     if (code != kIgnore && c >= 1e-4f && c <= 1.0f - 1e-4f) {              // clamp passes gradient inside only
-      float omc = 1.f - c;
-      g = code == k ? alpha * (2.f * omc * logf(c) - omc * omc / c)
-                    : (1.f - alpha) * (2.f * c * -log1pf(-c) + c * c / omc);
+      const float omc = 1.f - c;
+      if (code == k) g = alpha * (2.f * omc * logf(c) - omc * omc / c);
+      else g = (1.f - alpha) * (2.f * c * -log1pf(-c) + c * c / omc);
       g *= scale_c;
     }
     d0[i] = g;
