@@ -504,7 +504,7 @@ const char* frn_kernel_inventory(void) {
          "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,"
          "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel,"
          "event_bounds_kernel,event_scatter_kernel,voxel_normalize_kernel,"
-         "decode_clip_kernel,nms_keys_kernel,nms_class_kernel,nms_gather_kernel";
+         "decode_clip_kernel,nms_keys_kernel,nms_class_kernel,nms_gather_kernel,row_sum_kernel,sum_parts_kernel";
 }
 
 // ---- GEMM ----------------------------------------------------------------------
