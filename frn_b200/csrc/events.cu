@@ -78,8 +78,9 @@ int voxelize(cudaStream_t st, long n, const void* x, const void* y, const long l
   cudaError_t e = cudaMemsetAsync(voxel, 0, total * sizeof(float), st);
   if (e != cudaSuccess) return (int)e;
   if (n > 0) {
-    cudaMemsetAsync(bounds, 0x7f, sizeof(int), st);
-    cudaMemsetAsync(bounds + 1, 0xff, sizeof(int), st);
+    e = cudaMemsetAsync(bounds, 0x7f, sizeof(int), st);               // first = 0x7f7f7f7f (> any index)
+    if (e == cudaSuccess) e = cudaMemsetAsync(bounds + 1, 0xff, sizeof(int), st);      // last = -1
+    if (e != cudaSuccess) return (int)e;
     int grid = (int)min((long)148 * 8, (n + kThreads - 1) / kThreads);
     event_bounds_kernel<XY><<<grid, kThreads, 0, st>>>(n, (const XY*)x, (const XY*)y, H, W, bounds);
     FRN_LAUNCH_CHECK();
