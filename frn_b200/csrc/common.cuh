@@ -108,8 +108,13 @@ struct GemmDesc {
   int accumulate;        // C += result
   int reduce_batch;
   int fast;              // tcgen05 engine only: single-pass TF32 (hi * hi), ~2^-11 relative; bf16-tolerance inference
+  // tcgen05 engine only, plain stores (no reduce_batch / accumulate): rows [g * group_m, (g + 1) * group_m) of the
+  // product go to the g-th of up to three output matrices (C, C1, C2; same strides) -- one GEMM for the three 1x1
+  // projections that read the same feature map.  group_m == 0: a single output.
+  float* C1; float* C2;
+  int group_m;
 };
-enum { GEMM_EPI_STORE = 0, GEMM_EPI_ROWSUMSQ = 1 };
+enum { GEMM_EPI_STORE = 0, GEMM_EPI_ROWSUMSQ = 1, GEMM_EPI_GROUPS = 2 /* store with row-grouped outputs */ };
 
 // Engine: 0 = FFMA (gemm.cu), 1 = tcgen05 3xTF32 (tc_gemm.cu).  Default from FRN_GEMM_ENGINE
 // ("ffma" / "tc"), see gemm_engine().
@@ -211,6 +216,7 @@ int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb,
                   float* out, float* scratch = nullptr);
 size_t batch_row_sum_scratch(int B, int M, int N);
 // gate backward: dr0 = dr1*(1+e0) + de1*e0 ; de0 = de1*(1+r0) + dr1*r0 (in place allowed)
+int stack3(cudaStream_t st, long n, const float* a, const float* b, const float* c, float* out);
 int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
                   const float* de1, float* dr0, float* de0);
 // dst (B, cols, rows) = transpose of src (B, rows, cols)

@@ -68,6 +68,26 @@ int conv1x1(Ctx& c, const float* W, const float* bias, const float* x, float* ou
   d.bias_m = bias;
   return run_gemm(c, d);
 }
+// The three 1x1 projections that read the same map x (g of one attention block, theta and phi of the other:
+// Attention.py:24-27 with fusion.py:31-32) as ONE GEMM with the weights stacked to (3 d, C) and row-grouped
+// outputs: x is read once instead of three times (these GEMMs are bound by reading x, not by the tensor pipe).
+int proj3(Ctx& c, const float* w0, const float* b0, const float* w1, const float* b1, const float* w2,
+          const float* b2, const float* x, float* o0, float* o1, float* o2, int batch, int d, int K, int N) {
+  size_t mark = c.ws.off;
+  float* W = c.ws.take<float>((size_t)3 * d * K);
+  float* bias = c.ws.take<float>((size_t)3 * d);
+  RUN(c, stack3(c.st, (long)d * K, w0, w1, w2, W));
+  RUN(c, stack3(c.st, d, b0, b1, b2, bias));
+  GemmDesc g = desc(W, x, o0, 3 * d, N, K, batch);
+  g.sAm = K; g.sAk = 1; g.sAb = 0;
+  g.sBk = N; g.sBn = 1; g.sBb = (long)K * N;
+  g.sCm = N; g.sCn = 1; g.sCb = (long)d * N;
+  g.bias_m = bias;
+  g.C1 = o1; g.C2 = o2; g.group_m = d;
+  int rc = run_gemm(c, g);
+  c.ws.release_to(mark);
+  return rc;
+}
 // dx (batch, K, N) (+)= W^T (K, M) @ dy (batch, M, N), dy element (m, n) at dy[m*sm + n*sn]
 int conv1x1_dgrad(Ctx& c, const float* W, const float* dy, long sm, long sn, long sb, float* dx,
                   int batch, int M, int K, int N, int accumulate) {
@@ -195,11 +215,13 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
 // CrossAttentionBlock.forward([x0, x1]).  have_x_stats: s.mu_x / s.sd_x already hold the
 // statistics of x0 (REFusion computes them inside the gate kernel).
 int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, const frn_cab_params& p,
-                float* out, long ob, const CabSaved& s, bool have_x_stats) {
+                float* out, long ob, const CabSaved& s, bool have_x_stats, bool have_qkv = false) {
   const int d = C / 8;
-  FRN_TRY(conv1x1(c, p.g_w, p.g_b, x0, s.Vc, B, d, C, N));        // Attention.py:24
-  FRN_TRY(conv1x1(c, p.theta_w, p.theta_b, x1, s.Kc, B, d, C, N));  // Attention.py:26
-  FRN_TRY(conv1x1(c, p.phi_w, p.phi_b, x1, s.Qc, B, d, C, N));      // Attention.py:27
+  if (!have_qkv) {                                                  // REFusion projects both blocks at once (proj3)
+    FRN_TRY(conv1x1(c, p.g_w, p.g_b, x0, s.Vc, B, d, C, N));        // Attention.py:24
+    FRN_TRY(conv1x1(c, p.theta_w, p.theta_b, x1, s.Kc, B, d, C, N));  // Attention.py:26
+    FRN_TRY(conv1x1(c, p.phi_w, p.phi_b, x1, s.Qc, B, d, C, N));      // Attention.py:27
+  }
   size_t mark = c.ws.off;
   FRN_TRY(attention_fwd(c, B, N, d, s));                          // Attention.py:29-32
   c.ws.release_to(mark);
@@ -419,9 +441,20 @@ int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e
   RUN(c, gate_stats(c.st, (long)B * C, N, s.R0, s.E0, s.R1, s.E1, kEps, s.blkA.mu_x, s.blkA.sd_x,
                     s.blkB.mu_x, s.blkB.sd_x));
   const long ob = 2L * C * N;
-  FRN_TRY(cab_forward(c, B, C, N, s.R1, s.E1, p.rgb_ca, out, ob, s.blkA, true));                 // fusion.py:31
+  // block A = CAB(x0 = R1, x1 = E1), block B = CAB(x0 = E1, x1 = R1): R1 feeds g_A, theta_B, phi_B and E1 feeds
+  // g_B, theta_A, phi_A -- one GEMM per map on the tcgen05 engine (the FFMA engine keeps the six separate ones)
+  const bool fuse = gemm_engine() == 1 && std::getenv("FRN_NO_PROJ3") == nullptr;
+  if (fuse) {
+    const int d = C / 8;
+    const frn_cab_params &pa = p.rgb_ca, &pb = p.event_ca;
+    FRN_TRY(proj3(c, pa.g_w, pa.g_b, pb.theta_w, pb.theta_b, pb.phi_w, pb.phi_b, s.R1, s.blkA.Vc, s.blkB.Kc,
+                  s.blkB.Qc, B, d, C, N));
+    FRN_TRY(proj3(c, pb.g_w, pb.g_b, pa.theta_w, pa.theta_b, pa.phi_w, pa.phi_b, s.E1, s.blkB.Vc, s.blkA.Kc,
+                  s.blkA.Qc, B, d, C, N));
+  }
+  FRN_TRY(cab_forward(c, B, C, N, s.R1, s.E1, p.rgb_ca, out, ob, s.blkA, true, fuse));           // fusion.py:31
   float* out_b = c.out_bf16 ? (float*)((uint16_t*)out + (long)C * N) : out + (long)C * N;
-  FRN_TRY(cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out_b, ob, s.blkB, true));  // fusion.py:32,34
+  FRN_TRY(cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out_b, ob, s.blkB, true, fuse));  // fusion.py:32,34
   return FRN_OK;
 }
 
@@ -501,7 +534,7 @@ const char* frn_kernel_inventory(void) {
          "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
          "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
-         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,"
+         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,stack3_kernel,"
          "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel,"
          "event_bounds_kernel,event_scatter_kernel,voxel_normalize_kernel,"
          "decode_clip_kernel,nms_keys_kernel,nms_class_kernel,nms_gather_kernel,row_sum_kernel,sum_parts_kernel";

@@ -402,6 +402,19 @@ int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb,
   return FRN_OK;
 }
 
+__global__ void stack3_kernel(long n, const float* __restrict__ a, const float* __restrict__ b,
+                              const float* __restrict__ c, float* __restrict__ out) {
+  long stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < 3 * n; i += stride)
+    out[i] = i < n ? a[i] : (i < 2 * n ? b[i - n] : c[i - 2 * n]);
+}
+// out = [a; b; c], n floats each (stacked weights / biases of the fused projection GEMM)
+int stack3(cudaStream_t st, long n, const float* a, const float* b, const float* c, float* out) {
+  stack3_kernel<<<grid_for(3 * n), 256, 0, st>>>(n, a, b, c, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
 int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
                   const float* de1, float* dr0, float* de0) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };

@@ -430,7 +430,9 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
         const bool acc_out = ACC && !partial;
         const long boff = p.reduce_batch ? 0 : (long)z * p.bias_bs;
         const float bm = (!partial && p.bias_m) ? __ldg(p.bias_m + boff + gm) : 0.f;
-        const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+        const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0) &&
+                         (EPI != GEMM_EPI_GROUPS || (((reinterpret_cast<uintptr_t>(p.C1) | reinterpret_cast<uintptr_t>(p.C2) |
+                                               (uintptr_t)(p.sCb * 4)) & 15) == 0));
         if (!vec) {                             // n-contiguous aligned outputs take the coalesced path below
 #pragma unroll
         for (int c0 = 0; c0 < HC; c0 += 4) {
@@ -442,6 +444,11 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
             o[j] = fmaf(p.alpha, acc[c0 + j], bm + bn);
           }
           float* dst = Cb + (long)gm * sCm + (long)(nb + c0) * sCn;
+          if (EPI == GEMM_EPI_GROUPS) {          // row-grouped outputs (never partial / accumulated)
+            const int g = gm / p.group_m;
+            dst = (g == 0 ? p.C : (g == 1 ? p.C1 : p.C2)) + (long)z * p.sCb + (long)(gm - g * p.group_m) * sCm +
+                  (long)(nb + c0) * sCn;
+          }
           if (vec && nb + c0 + 3 < p.N) {
             float4 q = make_float4(o[0], o[1], o[2], o[3]);
             float4* d4 = reinterpret_cast<float4*>(dst);
@@ -458,7 +465,7 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
         }
         }
       }
-      if (EPI == GEMM_EPI_STORE) {
+      if (EPI != GEMM_EPI_ROWSUMSQ) {
         // Coalesced path for n-contiguous outputs: thread = row is the TMEM read layout, but a warp-wide store
         // of 16 bytes per ROW touches 32 different lines (measured: the epilogue, not the MMAs, bounded every
         // K = 32 GEMM of the backward pass).  Each warp transposes 32 x 32 blocks through a swizzled shared
@@ -466,7 +473,9 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
         float* Cb; long sCm, sCn;
         if (partial) { Cb = aux + (long)z * p.M * p.N; sCm = p.N; sCn = 1; }
         else { Cb = p.C + (p.reduce_batch ? 0 : (long)z * p.sCb); sCm = p.sCm; sCn = p.sCn; }
-        const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+        const bool vec = (sCn == 1) && ((sCm & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0) &&
+                         (EPI != GEMM_EPI_GROUPS || (((reinterpret_cast<uintptr_t>(p.C1) | reinterpret_cast<uintptr_t>(p.C2) |
+                                               (uintptr_t)(p.sCb * 4)) & 15) == 0));
         if (vec) {
           constexpr int W = HC < 32 ? HC : 32;      // block width (columns)
           constexpr int CPR = W / 4;                // 16-byte chunks per row
@@ -500,6 +509,10 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
               float4 q = lds128(tile + (uint32_t)(rr * 32 + ((csub ^ (rr & 7)) << 2)) * 4u);
               if (grow < p.M && gn < p.N) {
                 float* dst = Cb + (long)grow * sCm + gn;
+                if (EPI == GEMM_EPI_GROUPS) {
+                  const int g = grow / p.group_m;
+                  dst = (g == 0 ? p.C : (g == 1 ? p.C1 : p.C2)) + (long)z * p.sCb + (long)(grow - g * p.group_m) * sCm + gn;
+                }
                 if (gn + 3 < p.N) {
                   q.x += bn4.x; q.y += bn4.y; q.z += bn4.z; q.w += bn4.w;
                   if (acc_out) {
@@ -538,7 +551,7 @@ TcPlan tc_plan(const GemmDesc& in, bool allow_swap) {
   TcPlan pl;
   pl.d = in;
   pl.swapped = false;
-  if (allow_swap && in.M <= 64 && in.N > in.M) {
+  if (allow_swap && in.M <= 64 && in.N > in.M && in.group_m == 0) {
     GemmDesc& d = pl.d;
     d.A = in.B; d.sAm = in.sBn; d.sAk = in.sBk; d.sAb = in.sBb;
     d.B = in.A; d.sBn = in.sAm; d.sBk = in.sAk; d.sBb = in.sAb;
@@ -671,7 +684,15 @@ size_t tc_gemm_workspace_bytes(const GemmDesc& d) {
 int tc_gemm(cudaStream_t st, const GemmDesc& in, void* ws, size_t ws_bytes) {
   if (in.M <= 0 || in.N <= 0 || in.K <= 0 || in.batch <= 0) return FRN_ERR_BAD_SHAPE;
   if ((in.sAm != 1 && in.sAk != 1) || (in.sBn != 1 && in.sBk != 1)) return FRN_ERR_UNSUPPORTED;
+  if (in.group_m > 0 && (in.reduce_batch || in.accumulate || !in.C1 || !in.C2 || in.M > 3 * in.group_m || in.bias_n))
+    return FRN_ERR_UNSUPPORTED;
   TcPlan pl = tc_plan(in, true);
+  if (in.group_m > 0) {
+    ScopedTimer tm(st, FRN_TIME_GEMM);
+    ShapeTimer sh(st, "tc-groups", in.M, in.N, in.K, in.batch, 0);
+    pl.bn = 128;
+    return tc_launch_acc<128, GEMM_EPI_GROUPS, false>(st, pl, nullptr);
+  }
   ScopedTimer tm(st, FRN_TIME_GEMM);
   ShapeTimer sh(st, "tc", in.M, in.N, in.K, in.batch,
                 (in.reduce_batch ? 1 : 0) | (in.accumulate ? 2 : 0) | (in.sAk == 1 ? 4 : 0) | (in.sBn == 1 ? 8 : 0));
