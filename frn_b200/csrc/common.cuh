@@ -217,6 +217,8 @@ int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb,
 size_t batch_row_sum_scratch(int B, int M, int N);
 // gate backward: dr0 = dr1*(1+e0) + de1*e0 ; de0 = de1*(1+r0) + dr1*r0 (in place allowed)
 int stack3(cudaStream_t st, long n, const float* a, const float* b, const float* c, float* out);
+int unstack3(cudaStream_t st, long n, const float* in, float* a, float* b, float* c);
+int stack_cols3(cudaStream_t st, long rows, int d, const float* a, const float* b, const float* c, float* out);
 int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
                   const float* de1, float* dr0, float* de0);
 // dst (B, cols, rows) = transpose of src (B, rows, cols)

@@ -337,11 +337,21 @@ int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* d
   return FRN_OK;
 }
 
-// Backward of CrossAttentionBlock.forward.  dx0 / dx1: overwritten unless
-// acc0 / acc1.  Parameter gradients are overwritten.
-int cab_backward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, const frn_cab_params& p,
-                 const CabSaved& s, const float* g, long gb, float* dx0, int acc0, float* dx1, int acc1,
-                 const frn_cab_grads& gr) {
+// Position-major (B, N, d) gradients of the three projections of one block, and scratch for the column centring.
+struct QkvGrads { float *dQp, *dKp, *dVp, *part; };
+QkvGrads take_qkv_grads(Ctx& c, int B, int N, int d) {
+  QkvGrads q;
+  q.dQp = c.ws.take<float>((size_t)B * N * d);
+  q.dKp = c.ws.take<float>((size_t)B * N * d);
+  q.dVp = c.ws.take<float>((size_t)B * N * d);
+  q.part = c.ws.take<float>((size_t)B * center_cols_parts(N) * d);
+  return q;
+}
+
+// First half of the backward of CrossAttentionBlock.forward: AdaIN and style path, W conv, attention core.
+// Writes the content-path gradient into dx0 and leaves dQ / dK / dV in `q`.
+int cab_backward_core(Ctx& c, int B, int C, int N, const float* x0, const frn_cab_params& p, const CabSaved& s,
+                      const float* g, long gb, float* dx0, int acc0, const frn_cab_grads& gr, const QkvGrads& q) {
   const int d = C / 8;
   const long rows = (long)B * C;
   size_t mark = c.ws.off;
@@ -380,29 +390,67 @@ int cab_backward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, 
     FRN_TRY(conv1x1_dgrad(c, p.W_w, dT, N, 1, (long)C * N, dYp, B, C, d, N, 0));
     c.ws.release_to(m2);
   }
-  float* dQp = c.ws.take<float>((size_t)B * N * d);
-  float* dKp = c.ws.take<float>((size_t)B * N * d);
-  float* dVp = c.ws.take<float>((size_t)B * N * d);
-  float* part = c.ws.take<float>((size_t)B * center_cols_parts(N) * d);
   {
     size_t m2 = c.ws.off;
-    FRN_TRY(attention_bwd(c, B, N, d, s, dYp, dQp, dKp, dVp));
+    FRN_TRY(attention_bwd(c, B, N, d, s, dYp, q.dQp, q.dKp, q.dVp));
     // sum_j dK_j = sum_i q_i sum_j dS_ij = 0 exactly (rows of dS sum to zero; it is why the reference's
     // theta.bias gradient is pure rounding noise).  The computed dK misses that by a few 1e-7 of its
     // scale, and the theta weight gradient sum_j dK_j x1_j^T multiplies the miss by the large common
     // component of x1 (measured: 9.8e-6 -> 1.0e-6 at DSEC level 1, tools/attn_err_probe.py), so the
     // identity is enforced here.
     c.ws.release_to(m2);
-    RUN(c, center_cols(c.st, B, N, d, dKp, part));
+    RUN(c, center_cols(c.st, B, N, d, q.dKp, q.part));
   }
+  c.ws.release_to(mark);
+  return FRN_OK;
+}
+
+// Backward of CrossAttentionBlock.forward, stand-alone block.  dx0 / dx1: overwritten unless
+// acc0 / acc1.  Parameter gradients are overwritten.
+int cab_backward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, const frn_cab_params& p,
+                 const CabSaved& s, const float* g, long gb, float* dx0, int acc0, float* dx1, int acc1,
+                 const frn_cab_grads& gr) {
+  const int d = C / 8;
+  size_t mark = c.ws.off;
+  QkvGrads q = take_qkv_grads(c, B, N, d);
+  FRN_TRY(cab_backward_core(c, B, C, N, x0, p, s, g, gb, dx0, acc0, gr, q));
   // projections (Attention.py:24-27); position-major gradients: element (k, n) at [n*d + k]
   const long nd = (long)N * d;
-  FRN_TRY(conv1x1_dgrad(c, p.g_w, dVp, 1, d, nd, dx0, B, d, C, N, 1));
-  FRN_TRY(conv1x1_dgrad(c, p.theta_w, dKp, 1, d, nd, dx1, B, d, C, N, acc1));
-  FRN_TRY(conv1x1_dgrad(c, p.phi_w, dQp, 1, d, nd, dx1, B, d, C, N, 1));
-  FRN_TRY(conv1x1_wgrad(c, dVp, 1, d, nd, x0, gr.g_w, gr.g_b, B, d, C, N));
-  FRN_TRY(conv1x1_wgrad(c, dKp, 1, d, nd, x1, gr.theta_w, gr.theta_b, B, d, C, N));
-  FRN_TRY(conv1x1_wgrad(c, dQp, 1, d, nd, x1, gr.phi_w, gr.phi_b, B, d, C, N));
+  FRN_TRY(conv1x1_dgrad(c, p.g_w, q.dVp, 1, d, nd, dx0, B, d, C, N, 1));
+  FRN_TRY(conv1x1_dgrad(c, p.theta_w, q.dKp, 1, d, nd, dx1, B, d, C, N, acc1));
+  FRN_TRY(conv1x1_dgrad(c, p.phi_w, q.dQp, 1, d, nd, dx1, B, d, C, N, 1));
+  FRN_TRY(conv1x1_wgrad(c, q.dVp, 1, d, nd, x0, gr.g_w, gr.g_b, B, d, C, N));
+  FRN_TRY(conv1x1_wgrad(c, q.dKp, 1, d, nd, x1, gr.theta_w, gr.theta_b, B, d, C, N));
+  FRN_TRY(conv1x1_wgrad(c, q.dQp, 1, d, nd, x1, gr.phi_w, gr.phi_b, B, d, C, N));
+  c.ws.release_to(mark);
+  return FRN_OK;
+}
+
+// Gradients through the three projections that read the map x (g of block `own`, theta and phi of block `oth`):
+// dx += [Wg; Wtheta; Wphi]^T [dV | dK | dQ] as one GEMM with K = 3 d (one read-modify-write of dx instead of
+// three), the three weight gradients as one GEMM with M = 3 d (x read once), bias gradients per projection.
+int proj3_backward(Ctx& c, int B, int C, int N, const float* x, const frn_cab_params& own, const frn_cab_params& oth,
+                   const QkvGrads& qown, const QkvGrads& qoth, float* dx, const frn_cab_grads& gown,
+                   const frn_cab_grads& goth) {
+  const int d = C / 8;
+  size_t mark = c.ws.off;
+  float* W = c.ws.take<float>((size_t)3 * d * C);
+  float* dW = c.ws.take<float>((size_t)3 * d * C);
+  float* S = c.ws.take<float>((size_t)B * N * 3 * d);
+  RUN(c, stack3(c.st, (long)d * C, own.g_w, oth.theta_w, oth.phi_w, W));
+  RUN(c, stack_cols3(c.st, (long)B * N, d, qown.dVp, qoth.dKp, qoth.dQp, S));
+  const long n3d = (long)N * 3 * d, nd = (long)N * d;
+  FRN_TRY(conv1x1_dgrad(c, W, S, 1, 3 * d, n3d, dx, B, 3 * d, C, N, 1));
+  FRN_TRY(conv1x1_wgrad(c, S, 1, 3 * d, n3d, x, dW, nullptr, B, 3 * d, C, N));
+  RUN(c, unstack3(c.st, (long)d * C, dW, gown.g_w, goth.theta_w, goth.phi_w));
+  const float* dys[3] = {qown.dVp, qoth.dKp, qoth.dQp};
+  float* dbs[3] = {gown.g_b, goth.theta_b, goth.phi_b};
+  for (int i = 0; i < 3; i++) {
+    size_t m2 = c.ws.off;
+    float* scratch = c.ws.take<float>(batch_row_sum_scratch(B, d, N));
+    RUN(c, batch_row_sum(c.st, B, d, N, dys[i], nd, 1, d, dbs[i], scratch));
+    c.ws.release_to(m2);
+  }
   c.ws.release_to(mark);
   return FRN_OK;
 }
@@ -465,8 +513,21 @@ int refusion_backward(Ctx& c, int B, int C, int N, const float* a, const float* 
   const long ob = 2L * C * N, cnl = (long)C * N;
   float* dR1 = c.ws.take<float>(cn);
   float* dE1 = c.ws.take<float>(cn);
-  FRN_TRY(cab_backward(c, B, C, N, s.R1, s.E1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, dE1, 0, g.rgb_ca));
-  FRN_TRY(cab_backward(c, B, C, N, s.E1, s.R1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 1, dR1, 1, g.event_ca));
+  if (std::getenv("FRN_NO_PROJ3") == nullptr) {
+    // block A = CAB(x0 = R1, x1 = E1), block B = CAB(x0 = E1, x1 = R1): the content paths write dR1 / dE1, then the
+    // projections are differentiated per MAP (R1: g_A, theta_B, phi_B; E1: g_B, theta_A, phi_A), see proj3_backward
+    const int d = C / 8;
+    size_t mark = c.ws.off;
+    QkvGrads qa = take_qkv_grads(c, B, N, d), qb = take_qkv_grads(c, B, N, d);
+    FRN_TRY(cab_backward_core(c, B, C, N, s.R1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, g.rgb_ca, qa));
+    FRN_TRY(cab_backward_core(c, B, C, N, s.E1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 0, g.event_ca, qb));
+    FRN_TRY(proj3_backward(c, B, C, N, s.R1, p.rgb_ca, p.event_ca, qa, qb, dR1, g.rgb_ca, g.event_ca));
+    FRN_TRY(proj3_backward(c, B, C, N, s.E1, p.event_ca, p.rgb_ca, qb, qa, dE1, g.event_ca, g.rgb_ca));
+    c.ws.release_to(mark);
+  } else {
+    FRN_TRY(cab_backward(c, B, C, N, s.R1, s.E1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, dE1, 0, g.rgb_ca));
+    FRN_TRY(cab_backward(c, B, C, N, s.E1, s.R1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 1, dR1, 1, g.event_ca));
+  }
   RUN(c, gate_backward(c.st, (long)cn, s.R0, s.E0, dR1, dE1, dR1, dE1));     // fusion.py:26-28
   FRN_TRY(conv1x1_dgrad(c, p.conv0_rgb_w, dR1, N, 1, cnl, da, B, C, C, N, 0));
   FRN_TRY(conv1x1_dgrad(c, p.conv0_evt_w, dE1, N, 1, cnl, de, B, C, C, N, 0));
@@ -534,7 +595,7 @@ const char* frn_kernel_inventory(void) {
          "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
          "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
          "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
-         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,stack3_kernel,"
+         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,stack3_kernel,unstack3_kernel,stack_cols3_kernel,"
          "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel,"
          "event_bounds_kernel,event_scatter_kernel,voxel_normalize_kernel,"
          "decode_clip_kernel,nms_keys_kernel,nms_class_kernel,nms_gather_kernel,row_sum_kernel,sum_parts_kernel";

@@ -415,6 +415,38 @@ int stack3(cudaStream_t st, long n, const float* a, const float* b, const float*
   return FRN_OK;
 }
 
+__global__ void unstack3_kernel(long n, const float* __restrict__ in, float* __restrict__ a, float* __restrict__ b,
+                                float* __restrict__ c) {
+  long stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < 3 * n; i += stride) {
+    float v = in[i];
+    if (i < n) a[i] = v; else if (i < 2 * n) b[i - n] = v; else c[i - 2 * n] = v;
+  }
+}
+int unstack3(cudaStream_t st, long n, const float* in, float* a, float* b, float* c) {
+  unstack3_kernel<<<grid_for(3 * n), 256, 0, st>>>(n, in, a, b, c);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+// out (rows, 3 d) = [a | b | c], each (rows, d) row-major: the position-major gradients of the three projections
+// that read the same map, side by side, so that their dgrads / wgrads run as one GEMM with K (resp. M) = 3 d.
+__global__ void stack_cols3_kernel(long rows, int d, const float* __restrict__ a, const float* __restrict__ b,
+                                   const float* __restrict__ c, float* __restrict__ out) {
+  const long total = rows * 3 * d, stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long r = i / (3 * d);
+    const int col = (int)(i - r * 3 * d), g = col / d, k = col - g * d;
+    const float* src = g == 0 ? a : (g == 1 ? b : c);
+    out[i] = __ldg(src + r * d + k);
+  }
+}
+int stack_cols3(cudaStream_t st, long rows, int d, const float* a, const float* b, const float* c, float* out) {
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  stack_cols3_kernel<<<grid_for(rows * 3 * d), 256, 0, st>>>(rows, d, a, b, c, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
 int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
                   const float* de1, float* dr0, float* de0) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
