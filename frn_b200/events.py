@@ -8,7 +8,6 @@
 DSEC h5 file, or torch tensors; CUDA tensors are used in place).  No CPU fallback."""
 from __future__ import annotations
 
-import ctypes as C
 
 import numpy as np
 import torch
