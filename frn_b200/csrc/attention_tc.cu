@@ -426,7 +426,11 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         tmem_ld16(tmem + lane_base + Cfg::kYMain + buf * DPAD + c0, a);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 16; q++) y[c0 + q] = fmaf(y[c0 + q], corr, a[q]);
+        for (int q = 0; q < 16; q += 2) {
+          const float2 r = __ffma2_rn(make_float2(y[c0 + q], y[c0 + q + 1]), make_float2(corr, corr),
+                                      make_float2(a[q], a[q + 1]));
+          y[c0 + q] = r.x; y[c0 + q + 1] = r.y;
+        }
       }
       tc_fence_before();
       mbar_arrive(&y_free[buf]);
@@ -460,10 +464,13 @@ attn_fwd_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       for (int c0 = 0; c0 < ABN; c0 += 16) {
         float hi[16], lo[16];
 #pragma unroll
-        for (int q = 0; q < 16; q++) {
-          float p = ex2_fast((s[c0 + q] - m_new) * kLog2e);
-          sum += p;
-          split_tf32(p, hi[q], lo[q]);
+        for (int q = 0; q < 16; q += 2) {                    // packed f32x2 arithmetic (same IEEE operations)
+          const float2 x = __fmul2_rn(sub2(make_float2(s[c0 + q], s[c0 + q + 1]), make_float2(m_new, m_new)),
+                                      make_float2(kLog2e, kLog2e));
+          const float2 p = make_float2(ex2_fast(x.x), ex2_fast(x.y));
+          sum += p.x;
+          sum += p.y;
+          split_tf32x2(p, hi[q], hi[q + 1], lo[q], lo[q + 1]);
         }
         tmem_st16(tmem + lane_base + Cfg::kSMain + buf * ABN + c0, hi);
         if (!FAST) tmem_st16(tmem + lane_base + Cfg::kSSmall + buf * ABN + c0, lo);
@@ -1211,7 +1218,10 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
       tmem_ld16(tb + Cfg::kK, s);
       tmem_wait_ld();
 #pragma unroll
-      for (int q = 0; q < 16; q++) { dv[q] += a[q]; dk[q] += s[q]; }
+      for (int q = 0; q < 16; q += 2) {
+        add2_into(dv[q], dv[q + 1], a[q], a[q + 1]);
+        add2_into(dk[q], dk[q + 1], s[q], s[q + 1]);
+      }
     };
     for (int j = 0; j < TQ; j++) {
       { ATR_T0();
@@ -1229,10 +1239,13 @@ attn_dkv2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
       const float* rw = sRows + (j % Cfg::kStages) * 2 * BT + half * 16;
       float phi[16], plo[16], dhi[16], dlo[16];
 #pragma unroll
-      for (int q = 0; q < 16; q++) {
-        const float p = ex2_fast((a[q] - rw[q]) * kLog2e);
-        split_tf32(p, phi[q], plo[q]);
-        split_tf32(p * (g[q] - rw[BT + q]), dhi[q], dlo[q]);
+      for (int q = 0; q < 16; q += 2) {                      // packed f32x2 arithmetic: same IEEE operations, half the
+        const float2 x = __fmul2_rn(sub2(make_float2(a[q], a[q + 1]), make_float2(rw[q], rw[q + 1])),   // issue slots
+                                    make_float2(kLog2e, kLog2e));
+        const float2 p = make_float2(ex2_fast(x.x), ex2_fast(x.y));
+        split_tf32x2(p, phi[q], phi[q + 1], plo[q], plo[q + 1]);
+        const float2 ds = __fmul2_rn(p, sub2(make_float2(g[q], g[q + 1]), make_float2(rw[BT + q], rw[BT + q + 1])));
+        split_tf32x2(ds, dhi[q], dhi[q + 1], dlo[q], dlo[q + 1]);
       }
       ATR_ADD(6);
       if (j > 0) {                                           // dV(j-1), dK(j-1) complete: promote, then reuse P^T / dS^T
@@ -1462,7 +1475,10 @@ attn_dkv3_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
         tmem_ld16(tl + Cfg::kK + 32 * half + c0, s2);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 16; q++) { dv[c0 + q] += a[q]; dk[c0 + q] += s2[q]; }
+        for (int q = 0; q < 16; q += 2) {
+          add2_into(dv[c0 + q], dv[c0 + q + 1], a[q], a[q + 1]);
+          add2_into(dk[c0 + q], dk[c0 + q + 1], s2[q], s2[q + 1]);
+        }
       }
     };
     for (int j = 0; j < TQ; j++) {
@@ -1478,10 +1494,13 @@ attn_dkv3_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitIma
       const float* rw = sRows + (j % Cfg::kStages) * 2 * BT + half * 16;
       float phi[16], plo[16], dhi[16], dlo[16];
 #pragma unroll
-      for (int q = 0; q < 16; q++) {
-        const float p = ex2_fast((a[q] - rw[q]) * kLog2e);
-        split_tf32(p, phi[q], plo[q]);
-        split_tf32(p * (g[q] - rw[BT + q]), dhi[q], dlo[q]);
+      for (int q = 0; q < 16; q += 2) {                      // packed f32x2, as in attn_dkv2_tc_kernel
+        const float2 x = __fmul2_rn(sub2(make_float2(a[q], a[q + 1]), make_float2(rw[q], rw[q + 1])),
+                                    make_float2(kLog2e, kLog2e));
+        const float2 p = make_float2(ex2_fast(x.x), ex2_fast(x.y));
+        split_tf32x2(p, phi[q], phi[q + 1], plo[q], plo[q + 1]);
+        const float2 ds = __fmul2_rn(p, sub2(make_float2(g[q], g[q + 1]), make_float2(rw[BT + q], rw[BT + q + 1])));
+        split_tf32x2(ds, dhi[q], dhi[q + 1], dlo[q], dlo[q + 1]);
       }
       if (j > 0) {
         mbar_wait(pv_done, (j - 1) & 1);
@@ -1689,7 +1708,7 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
         tmem_ld16(tl + Cfg::kAcc + half * CPT + c0, a);
         tmem_wait_ld();
 #pragma unroll
-        for (int q = 0; q < 16; q++) dq[c0 + q] += a[q];
+        for (int q = 0; q < 16; q += 2) add2_into(dq[c0 + q], dq[c0 + q + 1], a[q], a[q + 1]);
       }
     };
     for (int j = 0; j < TK; j++) {
@@ -1703,11 +1722,15 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
       mbar_arrive(&s_free[j & 1]);
       const int j0 = j * BT + half * 16;                      // first key of this thread's columns
       float hi[16], lo[16];
+      const float2 lse2 = make_float2(lse_i, lse_i), delta2 = make_float2(delta_i, delta_i);
 #pragma unroll
-      for (int q = 0; q < 16; q++) {
-        float p = ex2_fast((a[q] - lse_i) * kLog2e);
-        if (j0 + q >= N) p = 0.f;
-        split_tf32(p * (g[q] - delta_i), hi[q], lo[q]);
+      for (int q = 0; q < 16; q += 2) {                      // packed f32x2 arithmetic (same IEEE operations)
+        const float2 x = __fmul2_rn(sub2(make_float2(a[q], a[q + 1]), lse2), make_float2(kLog2e, kLog2e));
+        float2 p = make_float2(ex2_fast(x.x), ex2_fast(x.y));
+        if (j0 + q >= N) p.x = 0.f;
+        if (j0 + q + 1 >= N) p.y = 0.f;
+        const float2 ds = __fmul2_rn(p, sub2(make_float2(g[q], g[q + 1]), delta2));
+        split_tf32x2(ds, hi[q], hi[q + 1], lo[q], lo[q + 1]);
       }
       if (j > 0) {                                           // dQ(j-1) complete: promote, then reuse the dS columns
         mbar_wait(dq_done, (j - 1) & 1);

@@ -174,6 +174,19 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
   lo = x - hi;
 }
 
+// Packed fp32 pairs (FADD2 / FMUL2 on sm_100): the same IEEE results as the scalar operations, one issue slot for two.
+__device__ __forceinline__ float2 sub2(float2 x, float2 y) { return __fadd2_rn(x, make_float2(-y.x, -y.y)); }
+__device__ __forceinline__ void add2_into(float& d0, float& d1, float a0, float a1) {       // d += a, two lanes
+  const float2 r = __fadd2_rn(make_float2(d0, d1), make_float2(a0, a1));
+  d0 = r.x; d1 = r.y;
+}
+__device__ __forceinline__ void split_tf32x2(float2 x, float& hi0, float& hi1, float& lo0, float& lo1) {
+  const float2 h = make_float2(__uint_as_float((__float_as_uint(x.x) + 0x1000u) & 0xFFFFE000u),
+                               __uint_as_float((__float_as_uint(x.y) + 0x1000u) & 0xFFFFE000u));
+  const float2 l = sub2(x, h);
+  hi0 = h.x; hi1 = h.y; lo0 = l.x; lo1 = l.y;
+}
+
 // explicit shared-space accesses by 32-bit address (a generic pointer whose offset is only known at run time
 // compiles to generic LD / ST, which take the slower L1TEX path)
 __device__ __forceinline__ float4 lds128(uint32_t a) {
