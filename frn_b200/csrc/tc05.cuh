@@ -181,8 +181,17 @@ __device__ __forceinline__ void add2_into(float& d0, float& d1, float a0, float 
   d0 = r.x; d1 = r.y;
 }
 __device__ __forceinline__ void split_tf32x2(float2 x, float& hi0, float& hi1, float& lo0, float& lo1) {
+#ifdef FRN_SPLIT_INT
   const float2 h = make_float2(__uint_as_float((__float_as_uint(x.x) + 0x1000u) & 0xFFFFE000u),
                                __uint_as_float((__float_as_uint(x.y) + 0x1000u) & 0xFFFFE000u));
+#else
+  // Veltkamp split with C = 2^13 + 1: hi = x rounded to nearest (even) at 11 significant bits, i.e. a tf32 value,
+  // in three packed floating-point operations for two values (the integer form costs two unpackable instructions
+  // per value); lo = x - hi is exact.  |x| < 2^114 here (probabilities and dS values), so C x cannot overflow.
+  const float2 c = make_float2(8193.f, 8193.f);
+  const float2 p = __fmul2_rn(c, x);
+  const float2 h = __fadd2_rn(sub2(x, p), p);
+#endif
   const float2 l = sub2(x, h);
   hi0 = h.x; hi1 = h.y; lo0 = l.x; lo1 = l.y;
 }
