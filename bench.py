@@ -57,19 +57,22 @@ def measured_peaks():
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
-    capture (profiles/r1_d_attn_ncu_full.txt: B = 8, DSEC level 1, the shape the roofline line is quoted on)."""
-    path = os.path.join(ROOT, "profiles", "r1_d_attn_ncu_full.txt")
-    try:
-        total, on, unit = 0.0, False, {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
-        for line in open(path):
-            if line.startswith("=="):
-                on = kernel in line
-            elif on and ("dram__bytes_read.sum " in line or "dram__bytes_write.sum " in line):
-                parts = line.split()
-                total += float(parts[1]) * unit.get(parts[2], 1.0)
-        return (total if total > 0 else None), "profiles/r1_d_attn_ncu_full.txt (B=8, DSEC level 1, one launch)"
-    except OSError:
-        return None, "no ncu capture found"
+    captures (profiles/*_ncu_kernels.csv: name, duration us, read MB, write MB per launch at B = 8, DSEC level 1,
+    written by tools/ncu_kernel_table.py from the .ncu-rep).  The largest launch of the kernel is reported (the
+    level-1 full-size one).  Returns (bytes or None, source)."""
+    import glob
+    best, src = None, "no ncu capture found"
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r2_*_ncu_kernels.csv"))):
+        try:
+            for line in open(path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) >= 4 and kernel in f[0]:
+                    tot = (float(f[2]) + float(f[3])) * 1e6
+                    if best is None or tot > best:
+                        best, src = tot, os.path.relpath(path, ROOT)
+        except (OSError, ValueError):
+            continue
+    return best, src
 
 
 class ClockSampler:
@@ -109,18 +112,35 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_port_step(levels, batch, threads):
-    """One fwd+bwd of the 4-level stack for `batch` samples with the reference's ATen sequence on CPU."""
+_CPU_CASE = {}
+
+
+def cpu_port_inputs(levels):
+    """Parameters, inputs and upstream gradients of ONE sample per level, built once and outside any timed region."""
     from oracle import fusion_torch as ot
-    torch.set_num_threads(threads)
-    t0 = time.perf_counter()
-    for k, (c, h, w) in enumerate(levels):
-        g = torch.Generator().manual_seed(1000 + k)
-        prm = ot.init_params(c, seed=0)
-        for b in range(batch):     # B=1 at a time: the reference materialises N x N (1.47 GB at level 1)
+    key = tuple(levels)
+    if key not in _CPU_CASE:
+        case = []
+        for k, (c, h, w) in enumerate(levels):
+            g = torch.Generator().manual_seed(1000 + k)
+            prm = ot.init_params(c, seed=0)
             a = torch.randn(1, c, h, w, generator=g).relu()
             e = torch.randn(1, c, h, w, generator=g).relu()
             dout = torch.randn(1, 2 * c, h, w, generator=g)
+            case.append((a, e, prm, dout))
+        _CPU_CASE[key] = case
+    return _CPU_CASE[key]
+
+
+def cpu_port_step(levels, batch, threads):
+    """One fwd+bwd of the 4-level stack for `batch` samples with the reference's ATen sequence on CPU.  Only
+    ot.refusion_fwd_bwd is timed (parameter init and input generation happen in cpu_port_inputs)."""
+    from oracle import fusion_torch as ot
+    torch.set_num_threads(threads)
+    case = cpu_port_inputs(levels)
+    t0 = time.perf_counter()
+    for a, e, prm, dout in case:
+        for b in range(batch):     # B=1 at a time: the reference materialises N x N (1.47 GB at level 1)
             ot.refusion_fwd_bwd(a, e, prm, dout)
     return time.perf_counter() - t0
 
@@ -198,11 +218,33 @@ def run_ours(args):
     h2d_bytes = sum(t.numel() * 4 for t in host_a + host_e)
     norm_host = torch.empty(1, dtype=torch.float32).pin_memory()
 
-    def step_resident():
+    # The four levels are independent (model.py:305-308 calls them back to back on one stream): each gets its own
+    # stream, forked from and joined back into the current one, so one level's ragged last waves and small kernels
+    # fill under another level's.  --serial-levels keeps the reference's single-stream order.
+    lvl_streams = [torch.cuda.Stream(device=dev) for _ in levels] if not args.serial_levels else None
+    big_first = sorted(range(len(levels)), key=lambda k: -(levels[k][1] * levels[k][2]))    # level 1 (longest) first
+
+    def run_levels(inputs, serial=False):
+        """fwd+bwd of every level; inputs[k] = (a, e) leaf tensors."""
+        if lvl_streams is None or serial:
+            for k in range(len(levels)):
+                a, e = inputs[k]
+                mods[k](a, e).backward(douts[k])
+            return
+        main = torch.cuda.current_stream()
+        for k in big_first:
+            lvl_streams[k].wait_stream(main)
+            with torch.cuda.stream(lvl_streams[k]):
+                a, e = inputs[k]
+                mods[k](a, e).backward(douts[k])
+        for k in big_first:
+            main.wait_stream(lvl_streams[k])
+
+    def step_resident(serial=False):
         bucket.zero()
-        for m, a, e, go in zip(mods, dev_a, dev_e, douts):
+        for a, e in zip(dev_a, dev_e):
             a.grad = None; e.grad = None
-            m(a, e).backward(go)
+        run_levels(list(zip(dev_a, dev_e)), serial)
         bucket.allreduce(average=True)
 
     stage_a = [torch.empty_like(t, device=dev) for t in host_a]
@@ -211,24 +253,40 @@ def run_ours(args):
     copy_stream = torch.cuda.Stream(device=dev)
     order = sorted(range(len(levels)), key=lambda k: host_a[k].numel())      # smallest level first
 
-    def step_e2e():
+    out_host = [torch.empty((B, 2 * c, h, w), dtype=torch.float32).pin_memory() for c, h, w in levels] if args.e2e_full else None
+
+    def step_e2e(full=False):
         """Host inputs -> H2D (pinned, on a copy stream, smallest level first so that the 315 MB of level 1
-        travel while levels 4-2 compute) -> fwd+bwd through the public modules -> allreduce -> D2H of the result."""
+        travel while levels 4-2 compute) -> fwd+bwd through the public modules -> allreduce -> D2H of the result.
+        The result read back is the 4-byte norm of the reduced fusion gradients (the block sits between GPU-resident
+        trunks and an FPN, so its maps never leave the device in the model); full=True also returns the four
+        (B, 2C, H, W) outputs to pinned host memory (`e2e_full`)."""
         bucket.zero()
         main = torch.cuda.current_stream()
         copy_stream.wait_stream(main)                  # staging buffers are free again
-        ready = []
+        ready = {}
         with torch.cuda.stream(copy_stream):
             for k in order:
                 stage_a[k].copy_(host_a[k], non_blocking=True)
                 stage_e[k].copy_(host_e[k], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(copy_stream)
-                ready.append(ev)
-        for k, ev in zip(order, ready):
-            main.wait_event(ev)
-            a = stage_a[k].detach().requires_grad_(True); e = stage_e[k].detach().requires_grad_(True)
-            mods[k](a, e).backward(douts[k])
+                ready[k] = ev
+        outs = {}
+        for k in order:
+            st = lvl_streams[k] if lvl_streams is not None else main
+            if lvl_streams is not None:
+                st.wait_stream(main)
+            st.wait_event(ready[k])
+            with torch.cuda.stream(st):
+                a = stage_a[k].detach().requires_grad_(True); e = stage_e[k].detach().requires_grad_(True)
+                out = mods[k](a, e)
+                out.backward(douts[k])
+                if full:
+                    out_host[k].copy_(out.detach(), non_blocking=True)
+        if lvl_streams is not None:
+            for k in order:
+                main.wait_stream(lvl_streams[k])
         bucket.allreduce(average=True)
         norm_host.copy_(torch.linalg.vector_norm(bucket.flat).reshape(1), non_blocking=True)   # D2H result
         torch.cuda.current_stream().synchronize()
@@ -266,24 +324,41 @@ def run_ours(args):
     launches = lib.frn_launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- profiling pass (not the reported value): the same steps with the library's per-class CUDA-event
-    # hooks on; with the hooks on the two attention-backward kernels run back to back instead of overlapped,
-    # so that the dominant kernel's own launch duration is measured -------------------------------------
+    # ---- profiling pass (not the reported value): the same steps with the library's CUDA-event hooks on.  With
+    # the hooks on every kernel runs back to back on ONE stream (levels serial, no dQ || dK/dV overlap, no block A ||
+    # block B overlap), so that each kernel's own launch duration is measured -------------------------------------
     lib.frn_timing_enable(1)
+    kbuf = C.create_string_buffer(1 << 16)
     for cls in range(5):
         lib.frn_timing_read(cls, C.byref(C.c_double()), C.byref(C.c_long()))
-    ms_prof = timed(step_resident, args.steps)
+    lib.frn_timing_kernels(kbuf, len(kbuf))
+    ms_prof = timed(lambda: step_resident(serial=True), args.steps)
     classes = {}
     for name, cls in (("attn_fwd", 0), ("attn_bwd", 1), ("gemm", 2), ("rows", 3), ("attn_dkv", 4)):
         ms, n = C.c_double(), C.c_long()
         lib.frn_timing_read(cls, C.byref(ms), C.byref(n))
         classes[name] = {"ms": ms.value, "launches": n.value}
+    lib.frn_timing_kernels(kbuf, len(kbuf))
     lib.frn_timing_enable(0)
+    hbm_kernels = []
+    for ln in kbuf.value.decode().strip().splitlines():
+        f = [x.strip() for x in ln.split("|")]
+        if len(f) != 7 or int(f[4]) == 0:
+            continue                    # only launches larger than the L2 carry an HBM roofline figure
+        nl, msl, byl = int(f[4]), float(f[5]), float(f[6])
+        hbm_kernels.append({"kernel": f[0], "launches_per_step": nl / args.steps,
+                            "algorithmic_bytes": byl / nl, "ms": msl / nl,
+                            "achieved_gbs": byl / (msl / 1e3) / 1e9 if msl > 0 else 0.0})
+    hbm_kernels.sort(key=lambda r: -r["ms"] * r["launches_per_step"])
 
     # ---- timed region 2: end to end through the public modules, host inputs ------------
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
+    ms_e2e_full = None
+    if args.e2e_full:
+        step_e2e(True)
+        ms_e2e_full = timed(lambda: step_e2e(True), max(args.steps // 2, 2)) / max(args.steps // 2, 2)
 
     if rank != 0:
         if world > 1:
@@ -329,6 +404,17 @@ def run_ours(args):
     roofline.update(per_launch)
     if tc_attn:
         roofline["traffic"], roofline["traffic_source"] = ncu_traffic("attn_dkv2_tc_kernel")
+    # The second half of the metric ("achieved HBM GB/s vs peak"): every HBM-bound kernel of the block, launches
+    # larger than the 126 MB L2 only, timed by the library's CUDA-event hooks in the profiling pass; algorithmic bytes
+    # = each input element read once + each output element written once; traffic = dram bytes of the ncu capture.
+    for r in hbm_kernels:
+        r["frac"] = r["achieved_gbs"] / peaks["hbm_gbs"]
+        r["traffic"], _src = ncu_traffic(r["kernel"])
+    roofline["hbm_kernels"] = hbm_kernels
+    roofline["hbm_peak_gbs"] = peaks["hbm_gbs"]
+    roofline["hbm_note"] = ("per kernel: launches whose algorithmic bytes exceed the L2 (DSEC levels 1-2 at this batch), "
+                            "CUDA events on the launching stream, kernels serialised; peak = measured copy bandwidth "
+                            "(MEASURED_PEAKS.json)")
     cores = os.cpu_count() or 1
     cpu_s = cpu_port_step(levels, 1, cores) if not args.no_cpu else None
     if cpu_s is not None:
@@ -346,16 +432,57 @@ def run_ours(args):
                    "l2": f"inputs+saved state per step >> 126 MB L2 ({h2d_bytes / 1e6:.0f} MB of inputs alone); no flush"},
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
+                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
+                "returned": "the 4-byte norm of the all-reduced fusion-parameter gradients (the block's maps stay "
+                            "on the device between the trunks and the FPN); e2e_full also returns the 2C outputs"},
         "roofline": roofline,
         "cpu_baseline": None if cpu_s is None else {
             "value": 1.0 / cpu_s, "unit": "samples/s", "cores": cores, "kind": "port",
             "sample": "best of 2 passes of 1 sample through the 4-level DSEC stack fwd+bwd, fp32, "
                       "oracle/fusion_torch.py (ATen call sequence of retinanet/fusion.py)"},
     }
-    print(json.dumps(line))
+    if ms_e2e_full is not None:
+        out_bytes = sum(B * 2 * c * h * w * 4 for c, h, w in levels)
+        line["e2e_full"] = {"value": world * B / (ms_e2e_full / 1e3), "unit": "samples/s", "ms_per_step": ms_e2e_full,
+                            "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": out_bytes + 4,
+                            "h2d_gbs_per_rank": h2d_bytes / (ms_e2e_full / 1e3) / 1e9,
+                            "returned": "the four (B, 2C, H, W) fp32 outputs + the gradient norm, to pinned host memory"}
+    line["config"]["levels_concurrent"] = lvl_streams is not None
+    line["e2e"]["h2d_gbs_per_rank"] = h2d_bytes / (ms_e2e / args.steps / 1e3) / 1e9
     if world > 1:
         dist.destroy_process_group()
+    if world == 1 and not args.no_other:
+        line["other_configs"] = other_configs(args)
+    print(json.dumps(line))
+
+
+def other_configs(args):
+    """The BASELINE.json configs the headline does not cover plus the comparators and the widened rows, each
+    measured by its own tool in a fresh process on the same GPU (after this process's timed regions) with a
+    bounded step count, and reported verbatim: config 1 on the GPU, config 4 (DDD17 bf16 batch 32), DDD17 fp32
+    fwd+bwd, PyTorch eager on the B200 in fp32 / TF32 (the only pre-existing GPU implementation of the path), and
+    rows f2 / f3 / f4.  A tool that fails or times out is reported as such, never silently dropped."""
+    torch.cuda.empty_cache()
+    jobs = [("bench_configs", ["tools/bench_configs.py", "--steps", "10", "--warmup", "3"], 240),
+            ("eager_gpu", ["tools/bench_eager_fusion.py", "--steps", "3", "--warmup", "3", "--no-ours"], 240),
+            ("f2_detection", ["tools/bench_detection.py"], 180),
+            ("f3_postprocess", ["tools/bench_postprocess.py"], 180),
+            ("f4_events", ["tools/bench_events.py"], 180)]
+    out = {}
+    for name, cmd, limit in jobs:
+        try:
+            r = subprocess.run([sys.executable] + cmd, cwd=ROOT, capture_output=True, text=True, timeout=limit)
+            rows = []
+            for ln in r.stdout.splitlines():
+                if ln.startswith("{"):
+                    try:
+                        rows.append(json.loads(ln))
+                    except ValueError:
+                        pass
+            out[name] = rows if rows else {"failed": (r.stderr or r.stdout)[-300:]}
+        except subprocess.TimeoutExpired:
+            out[name] = {"failed": f"timeout after {limit} s"}
+    return out
 
 
 def main():
@@ -366,6 +493,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=8, help="samples per GPU per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-other", action="store_true", help="skip the other_configs block (N = 1 only)")
+    ap.add_argument("--serial-levels", action="store_true", help="run the four levels on one stream (model.py order)")
+    ap.add_argument("--no-e2e-full", dest="e2e_full", action="store_false",
+                    help="skip the e2e_full leg (outputs returned to the host)")
     args = ap.parse_args()
     args.steps_ref, args.warmup_ref = args.steps, args.warmup
     if args.impl == "reference":

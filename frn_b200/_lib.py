@@ -42,9 +42,9 @@ _SIGNATURES = {
     "frn_launch_count": (C.c_ulonglong, []),
     "frn_mean_std": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
                                C.c_void_p, C.c_void_p]),
-    "frn_adain_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+    "frn_adain_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p]),
-    "frn_adain_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+    "frn_adain_backward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_size_t]),
     "frn_adain_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
@@ -99,6 +99,7 @@ _SIGNATURES = {
     "frn_get_attn_engine": (C.c_int, []),
     "frn_timing_enable": (None, [C.c_int]),
     "frn_timing_read": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]),
+    "frn_timing_kernels": (C.c_long, [C.c_char_p, C.c_long]),
 }
 
 FRN_F32, FRN_BF16 = 0, 1

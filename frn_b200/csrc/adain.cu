@@ -6,9 +6,10 @@
 // pair per row, NCHW).  A row is owned by one warp (N < 1024) or one 256-thread
 // CTA (N >= 1024); loads are 128-bit when N % 4 == 0 (rows then start 16-byte
 // aligned), scalar otherwise (DDD17: N = 5655, 1452, 374, 99).  Variances are
-// two-pass (mean first, then sum of squared deviations; the second pass hits
-// L1/L2) because the near-constant maps produced by RGB blanking
-// (retinanet/model.py:279-280) break the E[x^2]-E[x]^2 form in fp32.
+// single-pass shifted sums merged Welford-style (see Moments below): the plain
+// E[x^2]-E[x]^2 form breaks in fp32 on the near-constant maps produced by RGB
+// blanking (retinanet/model.py:279-280), and a second pass over the row costs
+// a second trip to HBM at the full-size levels.
 #include <type_traits>
 #include "common.cuh"
 
@@ -62,30 +63,93 @@ __device__ __forceinline__ long my_row(long rows, int& lane) {
   long row = my_row<GS>(rows, lane);          \
   if (row < 0) return;
 
+// ---- single-pass statistics: shifted sums per thread, Chan / Welford merge across threads ---------------------
+// One pass over HBM instead of two (the second pass of a 2048-row x 154 KB working set does not stay in L2:
+// ncu showed 592 MB read for 315 MB of input in gate_stats at DSEC level 1).  Each thread accumulates
+// s1 = sum (x - K), s2 = sum (x - K)^2 with K = the first element it sees, so near-constant maps (|mean| = 1e3 sigma,
+// the blanked-RGB case of retinanet/model.py:279-280) lose nothing to cancellation: x - K is exact there and
+// M2 = s2 - s1^2 / n cancels at most the spread of the thread's own 75-odd samples.  The per-thread
+// (n, mean, M2) triples are then merged with the exact pairwise formula
+//   M2 = M2a + M2b + (mean_b - mean_a)^2 na nb / (na + nb)
+// by warp shuffles and, for CTA-wide rows, once more through shared memory (BASELINE.json north_star:
+// "warp-shuffle plus shared-memory Welford").
+struct Moments {
+  float n, mean, m2;
+  __device__ __forceinline__ void merge(float nb, float mb, float m2b) {
+    const float nt = n + nb;
+    if (nt > 0.f) {
+      const float dlt = mb - mean, w = nb / nt;
+      mean = fmaf(dlt, w, mean);
+      m2 = m2 + m2b + dlt * dlt * n * w;
+    }
+    n = nt;
+  }
+};
+struct ShiftedSum {
+  float k, s1, s2, n;
+  __device__ __forceinline__ void init() { k = 0.f; s1 = 0.f; s2 = 0.f; n = 0.f; }
+  __device__ __forceinline__ void add(float x) {
+    if (n == 0.f) k = x;
+    const float dlt = x - k;
+    s1 += dlt; s2 = fmaf(dlt, dlt, s2); n += 1.f;
+  }
+  __device__ __forceinline__ Moments finish() const {
+    Moments m;
+    m.n = n;
+    m.mean = n > 0.f ? k + s1 / n : 0.f;
+    m.m2 = n > 0.f ? fmaxf(s2 - s1 * s1 / n, 0.f) : 0.f;
+    return m;
+  }
+};
+__device__ __forceinline__ Moments warp_merge(Moments m) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float nb = __shfl_xor_sync(0xffffffffu, m.n, o), mb = __shfl_xor_sync(0xffffffffu, m.mean, o),
+                qb = __shfl_xor_sync(0xffffffffu, m.m2, o);
+    // both lanes of a pair must arrive at the same triple: merge in a fixed (lower lane first) order
+    Moments a = m;
+    if ((threadIdx.x & o) == 0) { a.merge(nb, mb, qb); }
+    else { a.n = nb; a.mean = mb; a.m2 = qb; a.merge(m.n, m.mean, m.m2); }
+    m = a;
+  }
+  return m;
+}
+// Merge over the thread group that owns the row (GS = 32: one warp, GS = 256: the CTA).  `sm` holds 3 * 8 floats.
+template <int GS>
+__device__ __forceinline__ Moments group_merge(Moments m, float* sm) {
+  m = warp_merge(m);
+  if (GS == 32) return m;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) { sm[w] = m.n; sm[8 + w] = m.mean; sm[16 + w] = m.m2; }
+  __syncthreads();
+  Moments t;
+  t.n = sm[0]; t.mean = sm[8]; t.m2 = sm[16];
+#pragma unroll
+  for (int i = 1; i < GS / 32; i++) t.merge(sm[i], sm[8 + i], sm[16 + i]);
+  return t;
+}
+
 // ---- calc_mean_std -----------------------------------------------------------
 template <int GS, int W>
 __global__ void __launch_bounds__(256) row_mean_std_kernel(long rows, int N, const float* __restrict__ x,
                                                            float eps, float* __restrict__ mean,
                                                            float* __restrict__ sd) {
-  ROW_KERNEL_PROLOGUE();
+  __shared__ float sm[24];
+  int lane;
+  long row = my_row<GS>(rows, lane);
+  if (row < 0) return;
   const float* xr = x + row * N;
-  float s = 0.f;
+  ShiftedSum a; a.init();
   for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> a; a.load(xr + n);
+    Vec<W> v; v.load(xr + n);
 #pragma unroll
-    for (int q = 0; q < W; q++) s += a.v[q];
+    for (int q = 0; q < W; q++) a.add(v.v[q]);
   }
-  float mu = group_sum<GS>(s, red) / (float)N;
-  float ss = 0.f;
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> a; a.load(xr + n);
-#pragma unroll
-    for (int q = 0; q < W; q++) { float dlt = a.v[q] - mu; ss = fmaf(dlt, dlt, ss); }
-  }
-  ss = group_sum<GS>(ss, red);
+  const Moments m = group_merge<GS>(a.finish(), sm);
   if (lane == 0) {
-    mean[row] = mu;
-    sd[row] = sqrtf(ss / (float)(N - 1) + eps);
+    mean[row] = m.mean;
+    sd[row] = sqrtf(m.m2 / (float)(N - 1) + eps);
   }
 }
 
@@ -98,9 +162,12 @@ __global__ void __launch_bounds__(256) gate_stats_kernel(long rows, int N, const
                                                          float* __restrict__ sd_r,
                                                          float* __restrict__ mu_e,
                                                          float* __restrict__ sd_e) {
-  ROW_KERNEL_PROLOGUE();
+  __shared__ float sm[24];
+  int lane;
+  long row = my_row<GS>(rows, lane);
+  if (row < 0) return;
   const long o = row * N;
-  float sr = 0.f, se = 0.f;
+  ShiftedSum ar, ae; ar.init(); ae.init();
   for (int n = lane * W; n < N; n += GS * W) {
     Vec<W> a, b, x, y;
     a.load(r0 + o + n); b.load(e0 + o + n);
@@ -108,28 +175,15 @@ __global__ void __launch_bounds__(256) gate_stats_kernel(long rows, int N, const
     for (int q = 0; q < W; q++) {
       float m = a.v[q] * b.v[q];
       x.v[q] = a.v[q] + m; y.v[q] = b.v[q] + m;
-      sr += x.v[q]; se += y.v[q];
+      ar.add(x.v[q]); ae.add(y.v[q]);
     }
     x.store(r1 + o + n); y.store(e1 + o + n);
   }
-  float mr = group_sum<GS>(sr, red) / (float)N;
-  float me = group_sum<GS>(se, red) / (float)N;
-  float qr = 0.f, qe = 0.f;
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> a, b;
-    a.load(r0 + o + n); b.load(e0 + o + n);
-#pragma unroll
-    for (int q = 0; q < W; q++) {
-      float m = a.v[q] * b.v[q];
-      float dx = (a.v[q] + m) - mr, dy = (b.v[q] + m) - me;
-      qr = fmaf(dx, dx, qr); qe = fmaf(dy, dy, qe);
-    }
-  }
-  qr = group_sum<GS>(qr, red);
-  qe = group_sum<GS>(qe, red);
+  const Moments mr = group_merge<GS>(ar.finish(), sm);
+  const Moments me = group_merge<GS>(ae.finish(), sm);
   if (lane == 0) {
-    mu_r[row] = mr; sd_r[row] = sqrtf(qr / (float)(N - 1) + eps);
-    mu_e[row] = me; sd_e[row] = sqrtf(qe / (float)(N - 1) + eps);
+    mu_r[row] = mr.mean; sd_r[row] = sqrtf(mr.m2 / (float)(N - 1) + eps);
+    mu_e[row] = me.mean; sd_e[row] = sqrtf(me.m2 / (float)(N - 1) + eps);
   }
 }
 
@@ -292,9 +346,10 @@ __global__ void __launch_bounds__(256) row_dot_kernel(long rows, int N, const fl
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // Dispatch on row length (warp- or CTA-per-row) and vector width.
-#define LAUNCH_ROWS(KERNEL, rows, N, vec, ...)                                            \
+#define LAUNCH_ROWS(KERNEL, passes, rows, N, vec, ...)                                    \
   do {                                                                                    \
     ScopedTimer tm__(st, FRN_TIME_ROWS);                                                  \
+    KernelTimer kt__(st, #KERNEL, 4.0 * (passes) * (double)(rows) * (N));                 \
     if ((N) >= 1024) {                                                                    \
       if (vec) KERNEL<256, 4><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);             \
       else KERNEL<256, 1><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);                 \
@@ -310,14 +365,14 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 int row_mean_std(cudaStream_t st, long rows, int N, const float* x, float eps, float* mean, float* sd) {
   bool vec = (N % 4 == 0) && aligned16(x);
-  LAUNCH_ROWS(row_mean_std_kernel, rows, N, vec, rows, N, x, eps, mean, sd);
+  LAUNCH_ROWS(row_mean_std_kernel, 1, rows, N, vec, rows, N, x, eps, mean, sd);
   return FRN_OK;
 }
 
 int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* e0, float* r1, float* e1,
                float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e) {
   bool vec = (N % 4 == 0) && aligned16(r0) && aligned16(e0) && aligned16(r1) && aligned16(e1);
-  LAUNCH_ROWS(gate_stats_kernel, rows, N, vec, rows, N, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e);
+  LAUNCH_ROWS(gate_stats_kernel, 4, rows, N, vec, rows, N, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e);
   return FRN_OK;
 }
 
@@ -325,7 +380,7 @@ int adain_apply(cudaStream_t st, int B, int C, int N, const float* x, const floa
                 const float* mu_t, const float* sd_t, float* out, long ob) {
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && (ob % 4 == 0) && aligned16(x) && aligned16(out);
-  LAUNCH_ROWS(adain_apply_kernel, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
+  LAUNCH_ROWS(adain_apply_kernel, 2, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
   return FRN_OK;
 }
 
@@ -333,7 +388,7 @@ int adain_apply_bf16(cudaStream_t st, int B, int C, int N, const float* x, const
                      const float* mu_t, const float* sd_t, uint16_t* out, long ob) {
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && (ob % 4 == 0) && aligned16(x) && ((reinterpret_cast<uintptr_t>(out) & 7) == 0);
-  LAUNCH_ROWS(adain_apply_bf16_kernel, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
+  LAUNCH_ROWS(adain_apply_bf16_kernel, 1.5, rows, N, vec, rows, C, N, x, mu_x, sd_x, mu_t, sd_t, out, ob);
   return FRN_OK;
 }
 
@@ -341,7 +396,7 @@ int adain_bwd_reduce(cudaStream_t st, int B, int C, int N, const float* g, long 
                      const float* mu_x, const float* sd_x, float* g1, float* g2) {
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && (gb % 4 == 0) && aligned16(x) && aligned16(g);
-  LAUNCH_ROWS(adain_bwd_reduce_kernel, rows, N, vec, rows, C, N, g, gb, x, mu_x, sd_x, g1, g2);
+  LAUNCH_ROWS(adain_bwd_reduce_kernel, 2, rows, N, vec, rows, C, N, g, gb, x, mu_x, sd_x, g1, g2);
   return FRN_OK;
 }
 
@@ -350,7 +405,7 @@ int adain_bwd_content(cudaStream_t st, int B, int C, int N, const float* g, long
                       const float* g2, float* dx, int accumulate) {
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && (gb % 4 == 0) && aligned16(x) && aligned16(g) && aligned16(dx);
-  LAUNCH_ROWS(adain_bwd_content_kernel, rows, N, vec, rows, C, N, g, gb, x, mu_x, sd_x, sd_t, g1, g2, dx,
+  LAUNCH_ROWS(adain_bwd_content_kernel, (accumulate ? 4 : 3), rows, N, vec, rows, C, N, g, gb, x, mu_x, sd_x, sd_t, g1, g2, dx,
               accumulate);
   return FRN_OK;
 }
@@ -359,25 +414,25 @@ int adain_bwd_style(cudaStream_t st, int B, int C, int N, const float* t, const 
                     const float* sd_t, const float* g1, const float* g2, float* dstyle) {
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && aligned16(t) && aligned16(dstyle);
-  LAUNCH_ROWS(adain_bwd_style_kernel, rows, N, vec, rows, N, t, mu_t, sd_t, g1, g2, dstyle);
+  LAUNCH_ROWS(adain_bwd_style_kernel, 2, rows, N, vec, rows, N, t, mu_t, sd_t, g1, g2, dstyle);
   return FRN_OK;
 }
 
 int center_rows(cudaStream_t st, long rows, int N, const float* y, const float* mean, float* yc) {
   bool vec = (N % 4 == 0) && aligned16(y) && aligned16(yc);
-  LAUNCH_ROWS(center_rows_kernel, rows, N, vec, rows, N, y, mean, yc);
+  LAUNCH_ROWS(center_rows_kernel, 2, rows, N, vec, rows, N, y, mean, yc);
   return FRN_OK;
 }
 
 int add_row_bias(cudaStream_t st, long rows, int N, const float* u, float* x) {
   bool vec = (N % 4 == 0) && aligned16(x);
-  LAUNCH_ROWS(add_row_bias_kernel, rows, N, vec, rows, N, u, x);
+  LAUNCH_ROWS(add_row_bias_kernel, 2, rows, N, vec, rows, N, u, x);
   return FRN_OK;
 }
 
 int row_dot(cudaStream_t st, long rows, int N, const float* x, const float* y, float* out) {
   bool vec = (N % 4 == 0) && aligned16(x) && aligned16(y);
-  LAUNCH_ROWS(row_dot_kernel, rows, N, vec, rows, N, x, y, out);
+  LAUNCH_ROWS(row_dot_kernel, 2, rows, N, vec, rows, N, x, y, out);
   return FRN_OK;
 }
 

@@ -1769,10 +1769,7 @@ attn_dq2_tc_kernel(int N, int NP, int d, SplitImage Qi, SplitImage Ki, SplitImag
 // host side
 // ------------------------------------------------------------------------------------------------
 template <typename K>
-int set_smem(K kern, int bytes) {
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  return e == cudaSuccess ? FRN_OK : (int)e;
-}
+int set_smem(K kern, int bytes) { return set_smem_once((const void*)kern, bytes); }
 
 template <int DPAD>
 int launch_pack(cudaStream_t st, int B, int d, int N, const float* X, const float* sub, long bs, long cs, long ns,
@@ -1799,21 +1796,10 @@ int launch_fwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
 }
 
 // The dQ kernel and the dK/dV kernel are independent (same inputs, different outputs) and each leaves a
-// ragged last wave (600 CTAs on 148 SMs at DSEC level 1 = 4.05 waves), so the dQ kernel is forked onto a
-// per-device side stream and joined back with events: the two tails fill each other.  The side streams
-// are the only cached objects of this file (created once per device, never destroyed); with the
-// measurement hooks on, the kernels run back to back on the caller's stream so that their times stay separable.
-cudaStream_t side_stream() {
-  static std::mutex mu;
-  static cudaStream_t streams[64] = {};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::lock_guard<std::mutex> lk(mu);
-  if (!streams[dev] && cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking) != cudaSuccess)
-    streams[dev] = nullptr;
-  return streams[dev];
-}
-
+// ragged last wave (600 CTAs on 148 SMs at DSEC level 1 = 4.05 waves), so the dQ kernel is forked onto a side
+// stream of the caller's stream (fork_stream, common.cuh) and joined back with events: the two tails fill each
+// other.  With the measurement hooks on, the kernels run back to back on the caller's stream so that their times
+// stay separable.
 template <int DPAD, int NT>
 int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, const SplitImage& K,
                   const SplitImage& V, const SplitImage& dY, const float* lse_pad, const float* delta_pad,
@@ -1843,19 +1829,10 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
       kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
   };
   ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
-  cudaStream_t side = timing_enabled() ? nullptr : side_stream();
-  cudaEvent_t fork = nullptr, join = nullptr;
-  if (side && (cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) != cudaSuccess ||
-               cudaEventCreateWithFlags(&join, cudaEventDisableTiming) != cudaSuccess)) {
-    if (fork) cudaEventDestroy(fork);
-    side = nullptr;
-  }
-  if (side) {
-    cudaEventRecord(fork, st);
-    cudaStreamWaitEvent(side, fork, 0);
-    launch_q(side);
+  const Fork fk = fork_stream(st, 0);
+  if (fk.side) {
+    launch_q(fk.side);
     FRN_LAUNCH_CHECK();
-    cudaEventRecord(join, side);
   }
   {
     ScopedTimer tk(st, FRN_TIME_ATTN_DKV);
@@ -1869,10 +1846,8 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
       kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
     FRN_LAUNCH_CHECK();
   }
-  if (side) {
-    cudaStreamWaitEvent(st, join, 0);
-    cudaEventDestroy(fork);        // destruction is deferred until the recorded work has completed
-    cudaEventDestroy(join);
+  if (fk.side) {
+    join_stream(fk);
   } else {
     launch_q(st);
     FRN_LAUNCH_CHECK();
@@ -1906,6 +1881,8 @@ int attn_tc_pack(cudaStream_t st, int B, int d, int N, const float* X, const flo
   if (d > 64) return FRN_ERR_UNSUPPORTED;
   if ((img.pos_lo && !img.pos_hi) || (img.chan_lo && !img.chan_hi)) return FRN_ERR_NULL_POINTER;
   ScopedTimer tm(st, FRN_TIME_ROWS);
+  const int planes = (img.pos_hi ? 1 : 0) + (img.pos_lo ? 1 : 0) + (img.chan_hi ? 1 : 0) + (img.chan_lo ? 1 : 0);
+  KernelTimer kt(st, "pack_split_kernel", 4.0 * B * ((double)d * N + (double)planes * (d <= 32 ? 32 : 64) * attn_tc_np(N)));
   return d <= 32 ? launch_pack<32>(st, B, d, N, X, sub, bs, cs, ns, img)
                  : launch_pack<64>(st, B, d, N, X, sub, bs, cs, ns, img);
 }

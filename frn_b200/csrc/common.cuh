@@ -31,6 +31,16 @@ struct ScopedTimer {
 
 bool timing_enabled();    // measurement hooks on (include/frn_b200.h)
 long shape_log_dump(char* buf, long cap);
+long kernel_log_dump(char* buf, long cap);
+
+// Per-kernel timing of the HBM-bound kernels (frn_timing_kernels): `bytes` = ALGORITHMIC bytes of the launch, i.e.
+// every input element read once and every output element written once.
+struct KernelTimer {
+  cudaStream_t st; cudaEvent_t e0; bool on; const char* name; double bytes;
+  KernelTimer(cudaStream_t s, const char* name_, double bytes_);
+  ~KernelTimer();
+};
+long shape_log_dump(char* buf, long cap);
 
 // Debug: per-shape GEMM times (FRN_GEMM_LOG=1 and the measurement hooks on); read with frn_debug_gemm_log.
 struct ShapeTimer {
@@ -38,6 +48,23 @@ struct ShapeTimer {
   ShapeTimer(cudaStream_t s, const char* engine, int M, int N, int K, int batch, int flags);
   ~ShapeTimer();
 };
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, device) instead of per launch.
+int set_smem_once(const void* kern, int bytes);
+
+// Side streams for independent work inside one call (block A / block B of REFusion, dQ / dK,dV of the attention
+// backward).  They belong to the CALLER's stream: one set per (device, caller stream), created on first use and kept
+// for the life of the process, so concurrent callers on different streams never share one, and a call that is being
+// captured into a CUDA graph pulls its side streams into the same capture (fork / join are event edges only).
+struct Fork {
+  cudaStream_t main, side;     // side == nullptr: run everything on `main` (measurement hooks on, or no stream)
+  cudaEvent_t ev_fork, ev_join;
+};
+// slot: 0 = attention backward (dQ), 1 = REFusion block B.  Returns a Fork whose side stream waits for the work
+// enqueued on `st` so far.
+Fork fork_stream(cudaStream_t st, int slot);
+// Make `f.main` wait for everything enqueued on the side stream.
+void join_stream(const Fork& f);
 
 static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -113,6 +140,11 @@ struct GemmDesc {
   // projections that read the same feature map.  group_m == 0: a single output.
   float* C1; float* C2;
   int group_m;
+  // tcgen05 engine only, with reduce_batch: K is split but the batch is NOT summed -- C[b] (batch stride sCb) =
+  // A[b] B[b] with the K range of every batch entry cut into per_batch_split pieces that run as separate CTAs
+  // (long-K, tiny-output products such as the d x d scatter matrix of Y: one CTA per sample would leave the GPU
+  // empty).  0: classic reduce_batch.
+  int per_batch_split;
 };
 enum { GEMM_EPI_STORE = 0, GEMM_EPI_ROWSUMSQ = 1, GEMM_EPI_GROUPS = 2 /* store with row-grouped outputs */ };
 

@@ -9,6 +9,7 @@
 // queries run the same code in "dry" mode (no launches) so the sizes can never
 // drift from the real allocation sequence.
 #include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace frn {
@@ -143,6 +144,18 @@ CabSaved cab_saved_layout(void* base, int B, int C, int N) {
   s.sd_t = a.take<float>((size_t)B * C);
   s.bytes = a.off;
   return s;
+}
+
+// FRN_NO_PROJ3=1: the six projections as separate GEMMs (debug / comparison).  Read once.
+bool proj3_enabled() {
+  static const bool on = std::getenv("FRN_NO_PROJ3") == nullptr;
+  return on;
+}
+
+// FRN_NO_F4=1: the backward of the style path through the materialised (B, C, N) gradient map (debug / comparison).
+bool style_shortcut_enabled() {
+  static const bool on = std::getenv("FRN_NO_F4") == nullptr;
+  return on;
 }
 
 int chunk_for_scores(int B, int N, int mats) {
@@ -365,7 +378,67 @@ int cab_backward_core(Ctx& c, int B, int C, int N, const float* x0, const frn_ca
   RUN(c, style_coeffs(c.st, rows, N, g1, g2, s.sd_t, alpha, beta));
   // style path: dT[b][c][n] = alpha + beta * (W (Y' - ybar))[c][n]
   float* dYp = c.ws.take<float>((size_t)B * N * d);     // gradient wrt Y (flat = Y' layout)
-  {
+  if (style_shortcut_enabled() && gemm_engine() == 1) {
+    // the (B, C, N) gradient map dT is never formed.  With Yc = Y' - ybar 1^T (rows sum to zero),
+    //   Sigma_b = Yc_b Yc_b^T (d x d),   G_b = W^T diag(beta_b) W (d x d),   u_b = W^T alpha_b (d):
+    //   dY'_b = u_b 1^T + G_b Yc_b
+    //   dW    = sum_b [ diag(beta_b) W Sigma_b + alpha_b (N ybar_b)^T ],   db = N sum_b alpha_b
+    // Only d x d and C x d work besides one read of Yc for Sigma and one K = d product for dY' -- instead of writing
+    // dT once and reading it twice (B C N floats each) through three GEMMs.
+    size_t m2 = c.ws.off;
+    float* Yc = c.ws.take<float>((size_t)B * d * N);
+    float* Wb = c.ws.take<float>((size_t)B * C * d);
+    float* Sig = c.ws.take<float>((size_t)B * d * d);
+    float* G = c.ws.take<float>((size_t)B * d * d);
+    float* U = c.ws.take<float>((size_t)B * d);
+    RUN(c, center_rows(c.st, (long)B * d, N, s.Y, s.ybar, Yc));
+    RUN(c, scale_rows(c.st, B, C, d, p.W_w, beta, Wb));
+    {
+      GemmDesc g = desc(Yc, Yc, Sig, d, d, N, B);                  // Sigma_b[i][j] = sum_n Yc[i][n] Yc[j][n]
+      g.sAm = N; g.sAk = 1; g.sAb = (long)d * N;
+      g.sBk = 1; g.sBn = N; g.sBb = (long)d * N;
+      g.sCm = d; g.sCn = 1; g.sCb = (long)d * d;
+      g.reduce_batch = 1;
+      const int ktiles = cdiv(N, 32);
+      int split = cdiv(148, B * cdiv(d, 128));
+      if (split > ktiles / 4) split = ktiles / 4;
+      g.per_batch_split = split < 1 ? 1 : split;
+      FRN_TRY(run_gemm(c, g));
+    }
+    {
+      GemmDesc g = desc(Wb, p.W_w, G, d, d, C, B);                 // G_b[i][j] = sum_c beta_b[c] W[c][i] W[c][j]
+      g.sAm = 1; g.sAk = d; g.sAb = (long)C * d;
+      g.sBk = d; g.sBn = 1; g.sBb = 0;
+      g.sCm = d; g.sCn = 1; g.sCb = (long)d * d;
+      FRN_TRY(run_gemm(c, g));
+    }
+    {
+      GemmDesc g = desc(p.W_w, alpha, U, d, B, C, 1);              // U[b][i] = sum_c W[c][i] alpha[b][c]
+      g.sAm = 1; g.sAk = d;
+      g.sBk = 1; g.sBn = C;
+      g.sCm = 1; g.sCn = d;
+      FRN_TRY(run_gemm(c, g));
+    }
+    {
+      GemmDesc g = desc(G, Yc, dYp, d, N, d, B);                   // dY'_b = G_b Yc_b + u_b 1^T
+      g.sAm = d; g.sAk = 1; g.sAb = (long)d * d;
+      g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
+      g.sCm = N; g.sCn = 1; g.sCb = (long)d * N;
+      g.bias_m = U; g.bias_bs = d;
+      FRN_TRY(run_gemm(c, g));
+    }
+    {
+      GemmDesc g = desc(Wb, Sig, gr.W_w, C, d, d, B);              // dW = sum_b (diag(beta_b) W) Sigma_b ...
+      g.sAm = d; g.sAk = 1; g.sAb = (long)C * d;
+      g.sBk = d; g.sBn = 1; g.sBb = (long)d * d;
+      g.sCm = d; g.sCn = 1;
+      g.reduce_batch = 1;
+      FRN_TRY(run_gemm(c, g));
+      RUN(c, outer_accumulate(c.st, B, C, d, alpha, s.ybar, (float)N, gr.W_w));   // ... + alpha_b (N ybar_b)^T
+    }
+    RUN(c, scale_sum_batch(c.st, B, C, alpha, (float)N, gr.W_b));
+    c.ws.release_to(m2);
+  } else {
     size_t m2 = c.ws.off;
     float* Yc = c.ws.take<float>((size_t)B * d * N);
     float* Wb = c.ws.take<float>((size_t)B * C * d);
@@ -491,7 +564,7 @@ int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e
   const long ob = 2L * C * N;
   // block A = CAB(x0 = R1, x1 = E1), block B = CAB(x0 = E1, x1 = R1): R1 feeds g_A, theta_B, phi_B and E1 feeds
   // g_B, theta_A, phi_A -- one GEMM per map on the tcgen05 engine (the FFMA engine keeps the six separate ones)
-  const bool fuse = gemm_engine() == 1 && std::getenv("FRN_NO_PROJ3") == nullptr;
+  const bool fuse = gemm_engine() == 1 && proj3_enabled();
   if (fuse) {
     const int d = C / 8;
     const frn_cab_params &pa = p.rgb_ca, &pb = p.event_ca;
@@ -513,7 +586,7 @@ int refusion_backward(Ctx& c, int B, int C, int N, const float* a, const float* 
   const long ob = 2L * C * N, cnl = (long)C * N;
   float* dR1 = c.ws.take<float>(cn);
   float* dE1 = c.ws.take<float>(cn);
-  if (std::getenv("FRN_NO_PROJ3") == nullptr) {
+  if (proj3_enabled()) {
     // block A = CAB(x0 = R1, x1 = E1), block B = CAB(x0 = E1, x1 = R1): the content paths write dR1 / dE1, then the
     // projections are differentiated per MAP (R1: g_A, theta_B, phi_B; E1: g_B, theta_A, phi_A), see proj3_backward
     const int d = C / 8;
@@ -663,14 +736,14 @@ int frn_mean_std(void* stream, int B, int C, int N, const float* feat, float eps
   return row_mean_std((cudaStream_t)stream, (long)B * C, N, feat, eps, mean, std_out);
 }
 
-int frn_adain_forward(void* stream, int B, int C, int N, const float* content, const float* style,
+int frn_adain_forward(void* stream, int B, int C, int N, int N_style, const float* content, const float* style,
                       float* out, float* stats) {
-  if (B <= 0 || C <= 0 || N < 2) return FRN_ERR_BAD_SHAPE;
+  if (B <= 0 || C <= 0 || N < 2 || N_style < 2) return FRN_ERR_BAD_SHAPE;
   if (!content || !style || !out || !stats) return FRN_ERR_NULL_POINTER;
   cudaStream_t st = (cudaStream_t)stream;
   long rows = (long)B * C;
   float *mu_c = stats, *sd_c = stats + rows, *mu_s = stats + 2 * rows, *sd_s = stats + 3 * rows;
-  FRN_TRY(row_mean_std(st, rows, N, style, kEps, mu_s, sd_s));      // AdaIN.py:22
+  FRN_TRY(row_mean_std(st, rows, N_style, style, kEps, mu_s, sd_s));   // AdaIN.py:22 (over the style map's own H*W)
   FRN_TRY(row_mean_std(st, rows, N, content, kEps, mu_c, sd_c));    // AdaIN.py:23
   return adain_apply(st, B, C, N, content, mu_c, sd_c, mu_s, sd_s, out, (long)C * N);  // AdaIN.py:24-26
 }
@@ -681,10 +754,10 @@ size_t frn_adain_workspace_bytes(int B, int C, int N) {
   return 2 * align_up((size_t)B * C * sizeof(float));
 }
 
-int frn_adain_backward(void* stream, int B, int C, int N, const float* content, const float* style,
+int frn_adain_backward(void* stream, int B, int C, int N, int N_style, const float* content, const float* style,
                        const float* stats, const float* dout, float* dcontent, float* dstyle, void* ws,
                        size_t ws_bytes) {
-  if (B <= 0 || C <= 0 || N < 2) return FRN_ERR_BAD_SHAPE;
+  if (B <= 0 || C <= 0 || N < 2 || N_style < 2) return FRN_ERR_BAD_SHAPE;
   if (!content || !style || !stats || !dout || !dcontent || !dstyle) return FRN_ERR_NULL_POINTER;
   if (!ws || ws_bytes < frn_adain_workspace_bytes(B, C, N)) return FRN_ERR_WORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
@@ -696,7 +769,7 @@ int frn_adain_backward(void* stream, int B, int C, int N, const float* content, 
   long cn = (long)C * N;
   FRN_TRY(adain_bwd_reduce(st, B, C, N, dout, cn, content, mu_c, sd_c, g1, g2));
   FRN_TRY(adain_bwd_content(st, B, C, N, dout, cn, content, mu_c, sd_c, sd_s, g1, g2, dcontent, 0));
-  return adain_bwd_style(st, B, C, N, style, mu_s, sd_s, g1, g2, dstyle);
+  return adain_bwd_style(st, B, C, N_style, style, mu_s, sd_s, g1, g2, dstyle);
 }
 
 // ---- CrossAttentionBlock -------------------------------------------------------

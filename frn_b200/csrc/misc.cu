@@ -6,6 +6,8 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <set>
+#include <tuple>
 #include <string>
 #include <utility>
 #include <vector>
@@ -307,6 +309,62 @@ ScopedTimer::~ScopedTimer() {
 }
 
 namespace {
+struct KernelRec { const char* name; double bytes; cudaEvent_t e0, e1; };
+std::vector<KernelRec> g_kernel_log;
+}  // namespace
+
+KernelTimer::KernelTimer(cudaStream_t s, const char* name_, double bytes_)
+    : st(s), e0(nullptr), on(false), name(name_), bytes(bytes_) {
+  if (!g_timing_on.load(std::memory_order_relaxed)) return;
+  if (cudaEventCreate(&e0) != cudaSuccess) return;
+  cudaEventRecord(e0, st);
+  on = true;
+}
+KernelTimer::~KernelTimer() {
+  if (!on) return;
+  cudaEvent_t e1;
+  if (cudaEventCreate(&e1) != cudaSuccess) { cudaEventDestroy(e0); return; }
+  cudaEventRecord(e1, st);
+  std::lock_guard<std::mutex> lk(g_timing_mu);
+  g_kernel_log.push_back({name, bytes, e0, e1});
+}
+
+// "name | launches | ms | bytes | launches_large | ms_large | bytes_large" per kernel; large = launches whose
+// algorithmic bytes exceed the 126 MB L2 (those are the ones an HBM roofline fraction is meaningful for).
+long kernel_log_dump(char* buf, long cap) {
+  std::vector<KernelRec> ev;
+  {
+    std::lock_guard<std::mutex> lk(g_timing_mu);
+    ev.swap(g_kernel_log);
+  }
+  struct Agg { long n = 0; double ms = 0, bytes = 0; long nl = 0; double msl = 0, bytesl = 0; };
+  std::map<std::string, Agg> agg;
+  for (auto& r : ev) {
+    float t = 0.f;
+    cudaEventSynchronize(r.e1);
+    cudaEventElapsedTime(&t, r.e0, r.e1);
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+    Agg& a = agg[r.name];
+    a.n++; a.ms += t; a.bytes += r.bytes;
+    if (r.bytes > 126e6) { a.nl++; a.msl += t; a.bytesl += r.bytes; }
+  }
+  std::string out;
+  char line[256];
+  for (auto& kv : agg) {
+    snprintf(line, sizeof line, "%s | %ld | %.5f | %.0f | %ld | %.5f | %.0f\n", kv.first.c_str(), kv.second.n, kv.second.ms,
+             kv.second.bytes, kv.second.nl, kv.second.msl, kv.second.bytesl);
+    out += line;
+  }
+  if (buf && cap > 0) {
+    long n = (long)out.size() < cap - 1 ? (long)out.size() : cap - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+  }
+  return (long)out.size();
+}
+
+namespace {
 struct ShapeRec { std::string key; cudaEvent_t e0, e1; };
 std::vector<ShapeRec> g_shape_log;
 int g_shape_on = -1;
@@ -329,6 +387,61 @@ ShapeTimer::~ShapeTimer() {
   cudaEventRecord(e1, st);
   std::lock_guard<std::mutex> lk(g_timing_mu);
   g_shape_log.push_back({key, e0, e1});
+}
+
+int set_smem_once(const void* kern, int bytes) {
+  static std::mutex mu;
+  static std::set<std::pair<const void*, int>> done;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (done.count({kern, dev})) return FRN_OK;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return (int)e;
+  done.insert({kern, dev});
+  return FRN_OK;
+}
+
+namespace {
+struct SideSet { cudaStream_t s; cudaEvent_t fork, join; };
+std::mutex g_side_mu;
+std::map<std::tuple<int, cudaStream_t, int>, SideSet> g_sides;
+int g_no_fork = -1;
+}  // namespace
+
+Fork fork_stream(cudaStream_t st, int slot) {
+  Fork f{st, nullptr, nullptr, nullptr};
+  if (g_no_fork < 0) g_no_fork = getenv("FRN_NO_FORK") ? 1 : 0;       // FRN_NO_FORK=1: everything on the caller's stream
+  if (g_no_fork || timing_enabled()) return f;                        // hooks on: kernels back to back, times separable
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return f;
+  SideSet set{};
+  {
+    std::lock_guard<std::mutex> lk(g_side_mu);
+    auto key = std::make_tuple(dev, st, slot);
+    auto it = g_sides.find(key);
+    if (it == g_sides.end()) {
+      SideSet n{};
+      if (cudaStreamCreateWithFlags(&n.s, cudaStreamNonBlocking) != cudaSuccess) return f;
+      if (cudaEventCreateWithFlags(&n.fork, cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&n.join, cudaEventDisableTiming) != cudaSuccess)
+        return f;
+      it = g_sides.emplace(key, n).first;
+    }
+    set = it->second;
+  }
+  if (cudaEventRecord(set.fork, st) != cudaSuccess || cudaStreamWaitEvent(set.s, set.fork, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return f;
+  }
+  f.side = set.s; f.ev_fork = set.fork; f.ev_join = set.join;
+  return f;
+}
+
+void join_stream(const Fork& f) {
+  if (!f.side) return;
+  cudaEventRecord(f.ev_join, f.side);
+  cudaStreamWaitEvent(f.main, f.ev_join, 0);
 }
 
 long shape_log_dump(char* buf, long cap) {
@@ -384,14 +497,20 @@ int batch_row_sum(cudaStream_t st, int B, int M, int N, const float* x, long sb,
   if (scratch && sm == 1 && sn == M && sb == (long)N * M && M <= 256) {
     // position-major (B, N, M): coalesced column sums over chunks of positions, then one small reduction
     const int G = center_cols_parts(N), rpb = cdiv(N, G);
-    col_partial_sum_kernel<<<dim3(G, B), 256, 0, st>>>(N, M, rpb, x, scratch);
+    {
+      KernelTimer kt(st, "col_partial_sum_kernel", 4.0 * B * N * M);
+      col_partial_sum_kernel<<<dim3(G, B), 256, 0, st>>>(N, M, rpb, x, scratch);
+    }
     FRN_LAUNCH_CHECK();
     batch_row_sum_kernel<<<M, 256, 0, st>>>(1, M, B * G, scratch, 0, 1, M, out);
     FRN_LAUNCH_CHECK();
     return FRN_OK;
   }
   if (scratch && sn == 1 && N >= 64 && B <= 65535 && center_cols_parts(N) >= 1) {     // scratch holds >= B * M floats
-    row_sum_kernel<<<dim3(M, B), 256, 0, st>>>(M, N, x, sb, sm, scratch);
+    {
+      KernelTimer kt(st, "row_sum_kernel", 4.0 * B * N * M);
+      row_sum_kernel<<<dim3(M, B), 256, 0, st>>>(M, N, x, sb, sm, scratch);
+    }
     FRN_LAUNCH_CHECK();
     sum_parts_kernel<<<cdiv(M, 256), 256, 0, st>>>(M, B, scratch, out);
     FRN_LAUNCH_CHECK();
@@ -453,6 +572,7 @@ __global__ void stack_cols3_v4_kernel(long rows, int d4, const float4* __restric
 }
 int stack_cols3(cudaStream_t st, long rows, int d, const float* a, const float* b, const float* c, float* out) {
   ScopedTimer tm(st, FRN_TIME_ROWS);
+  KernelTimer kt(st, "stack_cols3_kernel", 2.0 * 4 * rows * 3 * d);
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   if (d % 4 == 0 && al(a) && al(b) && al(c) && al(out)) {
     stack_cols3_v4_kernel<<<grid_for(rows * 3 * (d / 4)), 256, 0, st>>>(
@@ -466,6 +586,8 @@ int stack_cols3(cudaStream_t st, long rows, int d, const float* a, const float* 
 
 int gate_backward(cudaStream_t st, long count, const float* r0, const float* e0, const float* dr1,
                   const float* de1, float* dr0, float* de0) {
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  KernelTimer kt(st, "gate_backward_kernel", 6.0 * 4 * count);      // r0, e0, dr1, de1 read; dr0, de0 written
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   if (count % 4 == 0 && al(r0) && al(e0) && al(dr1) && al(de1) && al(dr0) && al(de0)) {
     gate_backward_kernel4<<<grid_for(count / 4), 256, 0, st>>>(
@@ -554,6 +676,7 @@ int ds_from_p(cudaStream_t st, long rows, int N, const float* P, float* dP, cons
 extern "C" {
 void frn_timing_enable(int on) { frn::g_timing_on.store(on ? 1 : 0); }
 long frn_debug_gemm_log(char* buf, long cap) { return frn::shape_log_dump(buf, cap); }
+long frn_timing_kernels(char* buf, long cap) { return frn::kernel_log_dump(buf, cap); }
 int frn_timing_read(int cls, double* ms, long* launches) {
   if (cls < 0 || cls >= FRN_TIME_CLASSES || !ms || !launches) return FRN_ERR_BAD_SHAPE;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;

@@ -21,26 +21,50 @@ def shard_batch(global_batch: int, rank: int, world: int):
 
 class GradBucket:
     """Flat fp32 bucket aliasing the .grad of every parameter, so the allreduce is one call
-    and needs no pack/unpack copies."""
+    and needs no pack/unpack copies.
+
+    Build it once and reuse it.  Between steps clear the gradients with ``bucket.zero()`` or
+    ``optimizer.zero_grad(set_to_none=False)``: both keep the aliasing.  The reference loop's
+    ``optimizer.zero_grad()`` (train_dsec_det_fast.py:237) defaults to ``set_to_none=True`` in torch >= 2.0,
+    which detaches every ``.grad`` from the bucket; ``allreduce()`` therefore re-attaches first (``attach()``):
+    a gradient that no longer lives in the bucket is copied in and ``p.grad`` is pointed at its view again, a
+    parameter without a gradient contributes zeros.  That costs one copy per detached parameter but can never
+    reduce a stale buffer."""
 
     def __init__(self, params):
         self.params = [p for p in params if p.requires_grad]
         total = sum(p.numel() for p in self.params)
         dev = self.params[0].device if self.params else torch.device("cpu")
         self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
-        off = 0
+        self.views, off = [], 0
         for p in self.params:
             n = p.numel()
-            view = self.flat[off:off + n].view_as(p)
-            if p.grad is not None:
-                view.copy_(p.grad)
-            p.grad = view
+            self.views.append(self.flat[off:off + n].view_as(p))
             off += n
+        self.attach()
+
+    def attach(self):
+        """Make every p.grad the bucket's view (copying gradients produced outside the bucket).  Returns the
+        number of parameters that had to be re-attached."""
+        moved = 0
+        for p, view in zip(self.params, self.views):
+            g = p.grad
+            if g is not None and g.data_ptr() == view.data_ptr() and g.dtype == view.dtype:
+                continue
+            if g is None:
+                view.zero_()
+            else:
+                view.copy_(g)
+            p.grad = view
+            moved += 1
+        return moved
 
     def zero(self):
         self.flat.zero_()
+        self.attach()
 
     def allreduce(self, average: bool = True, async_op: bool = False):
+        self.attach()
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
             return None
         if average:

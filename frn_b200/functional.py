@@ -25,6 +25,38 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def _autocast_dtype():
+    """dtype of the active CUDA autocast region or None (torch >= 2.4 and the older torch.cuda.amp API)."""
+    try:
+        if not torch.is_autocast_enabled("cuda"):
+            return None
+        return torch.get_autocast_dtype("cuda")
+    except TypeError:          # torch < 2.4: is_autocast_enabled() takes no argument
+        if not torch.is_autocast_enabled():
+            return None
+        return torch.get_autocast_gpu_dtype()
+
+
+def _wants_grad(*tensors):
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
+
+
+# SURVEY.md 8.2 b: behave under autocast (train_dsec_det_fast.py:240-241, torch.cuda.amp.autocast() = fp16 + GradScaler):
+# the Functions run with autocast disabled on fp32 copies of their inputs; the public wrappers cast the result to the
+# autocast dtype, which is what the reference's ATen ops return under the same context.
+try:
+    _custom_fwd = torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    _custom_bwd = torch.amp.custom_bwd(device_type="cuda")
+except (AttributeError, TypeError):      # torch < 2.4
+    _custom_fwd = torch.cuda.amp.custom_fwd(cast_inputs=torch.float32)
+    _custom_bwd = torch.cuda.amp.custom_bwd
+
+
+def _to_autocast(out):
+    ac = _autocast_dtype()
+    return out if ac is None or out.dtype == ac else out.to(ac)
+
+
 def _check_cuda(*tensors):
     for t in tensors:
         if not t.is_cuda:
@@ -75,45 +107,50 @@ def mean_std(feat, eps=1e-5):
 
 class _AdaINFn(torch.autograd.Function):
     @staticmethod
+    @_custom_fwd
     def forward(ctx, content, style):
         _check_cuda(content, style)
         lib = _lib.load()
         b, c = content.shape[:2]
         x, t = _f32c(content), _f32c(style)
-        n = x[0, 0].numel()
+        # the style statistics run over the style map's own H*W (AdaIN.py:12-14,22): the reference only asserts
+        # that the two maps agree in (N, C) (AdaIN.py:20)
+        n, ns = x[0, 0].numel(), t[0, 0].numel()
         out = torch.empty_like(x)
         stats = torch.empty(4 * b * c, dtype=torch.float32, device=x.device)
         with torch.cuda.device(x.device):
-            _lib.check(lib.frn_adain_forward(_stream(), b, c, n, _ptr(x), _ptr(t), _ptr(out), _ptr(stats)),
+            _lib.check(lib.frn_adain_forward(_stream(), b, c, n, ns, _ptr(x), _ptr(t), _ptr(out), _ptr(stats)),
                        "adain_forward")
         ctx.save_for_backward(x, t, stats)
-        ctx.dims = (b, c, n)
+        ctx.dims = (b, c, n, ns)
         ctx.in_dtypes = (content.dtype, style.dtype)
         return out.to(content.dtype)
 
     @staticmethod
+    @_custom_bwd
     def backward(ctx, dout):
         lib = _lib.load()
         x, t, stats = ctx.saved_tensors
-        b, c, n = ctx.dims
+        b, c, n, ns = ctx.dims
         g = _f32c(dout)
         dx, dt = torch.empty_like(x), torch.empty_like(t)
         with torch.cuda.device(x.device):
             ws_bytes = lib.frn_adain_workspace_bytes(b, c, n)
             ws = _bytes(ws_bytes, x.device)
-            _lib.check(lib.frn_adain_backward(_stream(), b, c, n, _ptr(x), _ptr(t), _ptr(stats), _ptr(g),
+            _lib.check(lib.frn_adain_backward(_stream(), b, c, n, ns, _ptr(x), _ptr(t), _ptr(stats), _ptr(g),
                                               _ptr(dx), _ptr(dt), _ptr(ws), ws_bytes), "adain_backward")
         return dx.to(ctx.in_dtypes[0]), dt.to(ctx.in_dtypes[1])
 
 
 def adain(content, style):
-    return _AdaINFn.apply(content, style)
+    return _to_autocast(_AdaINFn.apply(content, style))
 
 
 # --------------------------------------------------------------------------- CrossAttentionBlock
 class _CabFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x0, x1, *params):
+    @_custom_fwd
+    def forward(ctx, need_grad, x0, x1, *params):
         _check_cuda(x0, x1, *params)
         lib = _lib.load()
         b, c, h, w = x0.shape
@@ -121,7 +158,6 @@ class _CabFn(torch.autograd.Function):
         a, e = _f32c(x0), _f32c(x1)
         prm = [_f32c(p) for p in params]
         out = torch.empty_like(a)
-        need_grad = any(ctx.needs_input_grad)
         with torch.cuda.device(a.device):
             ws_bytes = lib.frn_cab_workspace_bytes(b, c, n)
             ws = _bytes(ws_bytes, a.device)
@@ -140,6 +176,7 @@ class _CabFn(torch.autograd.Function):
         return out.to(x0.dtype)
 
     @staticmethod
+    @_custom_bwd
     def backward(ctx, dout):
         lib = _lib.load()
         a, e, saved, *prm = ctx.saved_tensors
@@ -155,11 +192,12 @@ class _CabFn(torch.autograd.Function):
                                             _ptr(g), c * n, _ptr(da), _ptr(de), 0, C.byref(gst), _ptr(ws),
                                             ws_bytes), "cab_backward")
         dts = ctx.in_dtypes
-        return (da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
+        return (None, da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
 
 
 def cross_attention(x0, x1, g_w, g_b, theta_w, theta_b, phi_w, phi_b, W_w, W_b):
-    return _CabFn.apply(x0, x1, g_w, g_b, theta_w, theta_b, phi_w, phi_b, W_w, W_b)
+    params = (g_w, g_b, theta_w, theta_b, phi_w, phi_b, W_w, W_b)
+    return _to_autocast(_CabFn.apply(_wants_grad(x0, x1, *params), x0, x1, *params))
 
 
 # --------------------------------------------------------------------------- REFusion
@@ -167,7 +205,8 @@ class _REFusionFn(torch.autograd.Function):
     """params: conv0_rgb (w, b), conv0_evt (w, b), rgb_cross_attention (8), event_cross_attention (8)."""
 
     @staticmethod
-    def forward(ctx, rgb, evt, *params):
+    @_custom_fwd
+    def forward(ctx, need_grad, rgb, evt, *params):
         _check_cuda(rgb, evt, *params)
         lib = _lib.load()
         b, c, h, w = rgb.shape
@@ -175,7 +214,6 @@ class _REFusionFn(torch.autograd.Function):
         a, e = _f32c(rgb), _f32c(evt)
         prm = [_f32c(p) for p in params]
         out = torch.empty((b, 2 * c, h, w), dtype=torch.float32, device=a.device)
-        need_grad = any(ctx.needs_input_grad)
         with torch.cuda.device(a.device):
             ws_bytes = lib.frn_refusion_workspace_bytes(b, c, n)
             ws = _bytes(ws_bytes, a.device)
@@ -194,6 +232,7 @@ class _REFusionFn(torch.autograd.Function):
         return out.to(rgb.dtype)
 
     @staticmethod
+    @_custom_bwd
     def backward(ctx, dout):
         lib = _lib.load()
         a, e, saved, *prm = ctx.saved_tensors
@@ -210,12 +249,14 @@ class _REFusionFn(torch.autograd.Function):
                                                  _ptr(g), _ptr(da), _ptr(de), C.byref(gst), _ptr(ws), ws_bytes),
                        "refusion_backward")
         dts = ctx.in_dtypes
-        return (da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
+        return (None, da.to(dts[0]), de.to(dts[1])) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[2:]))
 
 
 def refusion_infer_bf16(rgb, evt, conv0, rgb_ca, event_ca):
-    """Inference with bf16 activations (BASELINE.json config 4; the reference under
-    torch.autocast(bfloat16) + no_grad, train_dsec_det_fast.py:241): bf16 in, bf16 out, fp32 parameters,
+    """Inference with bf16 activations (BASELINE.json config 4 "bf16 fusion kernels": the module under
+    torch.autocast(dtype=torch.bfloat16) + no_grad.  The reference's own trainer uses the fp16 default of
+    torch.cuda.amp.autocast() with a GradScaler, train_dsec_det_fast.py:240-265; that mode takes the fp32-parity
+    kernels through _REFusionFn, see refusion()): bf16 in, bf16 out, fp32 parameters,
     fp32 statistics / softmax / accumulation, single-pass TF32 products.  No autograd graph."""
     params = (*conv0, *rgb_ca, *event_ca)
     _check_cuda(rgb, evt, *params)
@@ -241,17 +282,18 @@ def refusion(rgb, evt, conv0, rgb_ca, event_ca):
     bf16 activations (bf16 inputs, or fp32 inputs under torch.autocast(bfloat16)) with no gradient required
     take the bf16 inference path; everything else runs the fp32-parity kernels."""
     params = (*conv0, *rgb_ca, *event_ca)
-    wants_grad = torch.is_grad_enabled() and any(t.requires_grad for t in (rgb, evt, *params))
-    autocast_bf16 = (torch.is_autocast_enabled("cuda") and
-                     torch.get_autocast_dtype("cuda") == torch.bfloat16)
+    wants_grad = _wants_grad(rgb, evt, *params)
+    autocast_bf16 = _autocast_dtype() == torch.bfloat16
     if not wants_grad and (autocast_bf16 or (rgb.dtype == torch.bfloat16 and evt.dtype == torch.bfloat16)):
         return refusion_infer_bf16(rgb, evt, conv0, rgb_ca, event_ca)
-    return _REFusionFn.apply(rgb, evt, *params)
+    # fp32, and fp16 autocast + GradScaler (train_dsec_det_fast.py:240-265): fp32-parity kernels on fp32 copies
+    return _to_autocast(_REFusionFn.apply(wants_grad, rgb, evt, *params))
 
 
 # --------------------------------------------------------------------------- 1x1 conv (FPN laterals, row f1)
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
+    @_custom_fwd
     def forward(ctx, x, weight, bias):
         _check_cuda(x, weight) if bias is None else _check_cuda(x, weight, bias)
         lib = _lib.load()
@@ -274,6 +316,7 @@ class _Conv1x1Fn(torch.autograd.Function):
         return y.to(x.dtype)
 
     @staticmethod
+    @_custom_bwd
     def backward(ctx, dy):
         lib = _lib.load()
         xf, wf = ctx.saved_tensors
@@ -296,4 +339,4 @@ class _Conv1x1Fn(torch.autograd.Function):
 
 def conv1x1(x, weight, bias=None):
     """F.conv2d(x, weight, bias) for a (Cout, Cin, 1, 1) weight, stride 1, no padding (model.py:28-40)."""
-    return _Conv1x1Fn.apply(x, weight, bias)
+    return _to_autocast(_Conv1x1Fn.apply(x, weight, bias))

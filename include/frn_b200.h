@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FRN_B200_ABI_VERSION 1
+#define FRN_B200_ABI_VERSION 2
 
 enum {
   FRN_OK = 0,
@@ -93,12 +93,15 @@ const char* frn_kernel_inventory(void);
 int frn_mean_std(void* stream, int B, int C, int N, const float* feat, float eps,
                  float* mean, float* std_out);
 
-/* AdaIN_block.forward(content, style) -> out (B, C, N).  stats (4*B*C floats:
- * mu_c, sd_c, mu_s, sd_s) is kept for backward.  AdaIN.py:17-26. */
-int frn_adain_forward(void* stream, int B, int C, int N, const float* content,
+/* AdaIN_block.forward(content, style) -> out (B, C, N).  content is (B, C, N), style is
+ * (B, C, N_style): the reference only asserts that the two agree in (B, C) (AdaIN.py:20) and takes
+ * the style statistics over the style map's own H*W, so N_style may differ from N.  stats
+ * (4*B*C floats: mu_c, sd_c, mu_s, sd_s) is kept for backward.  AdaIN.py:17-26. */
+int frn_adain_forward(void* stream, int B, int C, int N, int N_style, const float* content,
                       const float* style, float* out, float* stats);
-/* Gradients of AdaIN_block.forward wrt content and style. ws: frn_adain_workspace_bytes. */
-int frn_adain_backward(void* stream, int B, int C, int N, const float* content,
+/* Gradients of AdaIN_block.forward wrt content (B, C, N) and style (B, C, N_style).
+ * ws: frn_adain_workspace_bytes. */
+int frn_adain_backward(void* stream, int B, int C, int N, int N_style, const float* content,
                        const float* style, const float* stats, const float* dout,
                        float* dcontent, float* dstyle, void* ws, size_t ws_bytes);
 size_t frn_adain_workspace_bytes(int B, int C, int N);
@@ -280,6 +283,11 @@ enum { FRN_TIME_ATTN_FWD = 0, FRN_TIME_ATTN_BWD = 1, FRN_TIME_GEMM = 2, FRN_TIME
        FRN_TIME_CLASSES = 5 };
 void frn_timing_enable(int on);
 int frn_timing_read(int cls, double* ms, long* launches);
+/* Per-kernel record of the HBM-bound kernels since the last call (hooks on): one text line per kernel,
+ * "name | launches | ms | algorithmic bytes | launches_large | ms_large | bytes_large", where "large" restricts the
+ * sums to launches whose algorithmic bytes exceed the 126 MB L2.  Algorithmic = each input element read once, each
+ * output element written once.  Returns the length of the full text; at most cap - 1 characters are copied. */
+long frn_timing_kernels(char* buf, long cap);
 
 #ifdef __cplusplus
 }

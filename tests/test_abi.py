@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     lib = _lib.load()
     for name in declared_symbols():
         assert hasattr(lib, name), name
-    assert lib.frn_abi_version() == 1
+    assert lib.frn_abi_version() == 2
     assert b"attn_fwd_kernel" in lib.frn_kernel_inventory()
 
 

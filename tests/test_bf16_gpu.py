@@ -128,3 +128,30 @@ def test_infer_f32_is_the_training_forward():
                                   C.c_void_p(out.data_ptr()), None, 0) == -4
     assert lib.frn_refusion_infer(None, _lib.FRN_BF16, b, c, n, C.c_void_p(a.data_ptr()), C.c_void_p(e.data_ptr()),
                                   C.byref(st), C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()), 16) == -3
+
+
+def test_config4_batch32_by_sample_decomposition():
+    """BASELINE.json configs[3]: DDD17-shaped inference at batch 32 with bf16 kernels.  The B = 32 call must equal
+    the 32 single-sample calls (no cross-sample coupling) and, for the first and last sample of every level, meet
+    the stated bf16 tolerance against the fp64 oracle."""
+    for name, c, h, w in (("ddd17_L1", 256, 65, 87), ("ddd17_L2", 512, 33, 44), ("ddd17_L3", 1024, 17, 22),
+                          ("ddd17_L4", 2048, 9, 11)):
+        b = 32
+        a, e = _inputs(b, c, h, w, seed=4000 + c)
+        prm = make_params(c, seed=11)
+        m = frn_b200.REFusion(c, c)
+        load_into(m, {k: v.numpy() for k, v in prm.items()})
+        m = m.to(DEV).eval()
+        with torch.no_grad():
+            full = m(a.to(DEV), e.to(DEV))
+            assert full.dtype == torch.bfloat16 and full.shape == (b, 2 * c, h, w)
+            for i in range(b):
+                one = m(a[i:i + 1].to(DEV), e[i:i + 1].to(DEV))
+                # identical arithmetic per sample; allow one bf16 ulp (2^-8) on isolated elements
+                assert rel_l2(full[i:i + 1].float().cpu().numpy(), one.double().cpu().numpy()) <= 1e-4, (name, i)
+        for i in (0, b - 1):
+            ref, _ = onp.refusion_forward(a[i:i + 1].double().numpy(), e[i:i + 1].double().numpy(),
+                                          {k: v.numpy() for k, v in prm.items()})
+            err = rel_l2(full[i:i + 1].float().cpu().numpy(), ref)
+            floor = rel_l2(torch.tensor(ref).bfloat16().float().numpy(), ref)
+            assert err <= TOL_BF16 and err <= 1.25 * floor, (name, i, err, floor)

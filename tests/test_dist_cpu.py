@@ -38,6 +38,24 @@ def _worker(rank, world, port, q):
     allreduce_fusion_grads(params, average=False)
     ok = ok and all(torch.allclose(p.grad, torch.full_like(p, 1.0 + 2 * i)) for i, p in enumerate(params))
     ok = ok and all(p.grad.data_ptr() >= bucket.flat.data_ptr() for p in params)
+    # third step the way the reference loop runs (train_dsec_det_fast.py:237): optimizer.zero_grad() with the
+    # torch >= 2.0 default set_to_none=True detaches every .grad from the bucket; a backward then allocates fresh
+    # gradients outside it.  allreduce() must reduce THOSE, not the stale bucket, and re-alias them.
+    opt = torch.optim.SGD(params, lr=0.1)
+    opt.zero_grad()
+    ok = ok and all(p.grad is None for p in params)
+    loss = sum((p * float(rank + 1) * (i + 1)).sum() for i, p in enumerate(params))
+    loss.backward()                                     # dL/dp = (rank + 1) * (i + 1), in fresh tensors
+    ok = ok and all(p.grad.data_ptr() != v.data_ptr() for p, v in zip(params, bucket.views))
+    bucket.allreduce(average=True)
+    ok = ok and all(torch.allclose(p.grad, torch.full_like(p, 1.5 * (i + 1))) for i, p in enumerate(params))
+    ok = ok and all(p.grad.data_ptr() == v.data_ptr() for p, v in zip(params, bucket.views))
+    # a parameter that received no gradient this step contributes zeros, not last step's values
+    opt.zero_grad()
+    params[0].grad = torch.full_like(params[0], float(rank + 1))
+    bucket.allreduce(average=False)
+    ok = ok and torch.allclose(params[0].grad, torch.full_like(params[0], 3.0))
+    ok = ok and all(float(p.grad.abs().max()) == 0.0 for p in params[1:])
     q.put((rank, bool(ok)))
     dist.destroy_process_group()
 

@@ -49,6 +49,16 @@ CASES = [
     ("scores", 2, 300, 300, 256, "km", "kn", "mn"),
     ("tiny", 1, 5, 7, 3, "mk", "kn", "mn"),
     ("k_not_mult_4", 2, 130, 129, 35, "mk", "nk", "mn"),
+    # TMA-able strides (multiples of 4 floats): the v2 kernel, all four operand-major combinations, ragged M / N / K
+    # edges (zero fill), every tile width (BN = 128 / 64 / 32) and accumulation chains longer than one chunk
+    ("v2_kA_mnB_conv", 2, 256, 2400, 256, "mk", "kn", "mn"),
+    ("v2_mnA_mnB", 2, 200, 480, 96, "km", "kn", "mn"),
+    ("v2_kA_kB_ragged", 2, 384, 300, 200, "mk", "nk", "mn"),
+    ("v2_mnA_kB", 3, 132, 260, 72, "km", "nk", "mn"),
+    ("v2_bn64", 2, 512, 64, 256, "mk", "kn", "mn"),
+    ("v2_bn32_posmajor", 2, 320, 32, 128, "km", "nk", "nm"),
+    ("v2_long_k", 1, 128, 128, 4096, "mk", "nk", "mn"),
+    ("v2_swapped_small_M", 2, 96, 1200, 512, "mk", "kn", "mn"),
 ]
 
 

@@ -218,3 +218,134 @@ def test_native_library_is_loaded():
     assert lib.frn_launch_count() > before
     maps = open("/proc/self/maps").read()
     assert "libfrn_b200.so" in maps
+
+
+# ---- parity at the batch the headline number is quoted on (BASELINE.json configs[1]: B = 8) -----------------
+# chunk_for_scores (d > 64), the split-K plans of the weight gradients and the (tiles, B) grids all depend on B.
+HEADLINE_B8 = [("dsec_L4_b8", 2048, 15, 20), ("dsec_L3_b8", 1024, 30, 40), ("dsec_L2_b8", 512, 60, 80)]
+
+
+@pytest.mark.parametrize("name,c,h,w", HEADLINE_B8, ids=[l[0] for l in HEADLINE_B8])
+def test_refusion_headline_batch8_vs_oracle(name, c, h, w):
+    """fwd + bwd at B = 8, levels 2-4 of the DSEC stack, against the fp64 oracle directly."""
+    b = 8
+    a, e, dout = make_inputs("relu", (b, c, h, w), seed=8000 + c)
+    a, e, dout = a.float().double(), e.float().double(), dout.float().double()
+    prm = make_params(c, seed=0)
+    ref = onp.refusion_forward_backward(a.numpy(), e.numpy(), _np_params(prm), dout.numpy())
+    m = frn_b200.REFusion(c, c)
+    load_into(m, _np_params(prm))
+    got = run_module(m, a.numpy(), e.numpy(), dout.numpy())
+    errs = check_against(name, got, ref)
+    print(name, {k: f"{v:.2e}" for k, v in errs.items() if k in ("out", "da", "de")})
+
+
+def test_refusion_headline_batch8_level1_by_sample_decomposition():
+    """DSEC level 1 (256 x 120 x 160) at B = 8: the fp64 oracle needs ~7 GB and ~10 s per sample there, so the
+    B = 8 call is decomposed instead: its outputs and input gradients must equal the eight B = 1 calls (the block
+    has no cross-sample coupling), its parameter gradients their fixed-order sum, and the first
+    and last sample's B = 1 calls are themselves gated against the fp64 oracle at 1e-5."""
+    b, c, h, w = 8, 256, 120, 160
+    dev = torch.device("cuda:0")
+    a, e, dout = make_inputs("relu", (b, c, h, w), seed=8256)
+    a, e, dout = a.float(), e.float(), dout.float()
+    prm = make_params(c, seed=0)
+    m = frn_b200.REFusion(c, c)
+    load_into(m, _np_params(prm))
+    m = m.to(dev)
+
+    def run(sl):
+        x = a[sl].to(dev).requires_grad_(True)
+        y = e[sl].to(dev).requires_grad_(True)
+        m.zero_grad(set_to_none=True)
+        out = m(x, y)
+        out.backward(dout[sl].to(dev))
+        torch.cuda.synchronize()
+        return (out.detach().cpu(), x.grad.cpu(), y.grad.cpu(),
+                {k: p.grad.detach().cpu().double() for k, p in m.named_parameters()})
+
+    out8, da8, de8, g8 = run(slice(0, b))
+    gsum = None
+    for i in range(b):
+        oi, dai, dei, gi = run(slice(i, i + 1))
+        # per-sample work is independent of B: identical bits expected; 1e-6 relative is the stated bound
+        for nm, full, one in (("out", out8[i:i + 1], oi), ("da", da8[i:i + 1], dai), ("de", de8[i:i + 1], dei)):
+            assert rel_l2(full.numpy(), one.double().numpy()) <= 1e-6, (nm, i)
+        gsum = gi if gsum is None else {k: gsum[k] + gi[k] for k in gi}       # fixed order: sample 0, 1, ... 7
+        if i in (0, b - 1):
+            ref = onp.refusion_forward_backward(a[i:i + 1].double().numpy(), e[i:i + 1].double().numpy(),
+                                                _np_params(prm), dout[i:i + 1].double().numpy())
+            check_against(f"dsec_L1_sample{i}", (oi.numpy(), dai.numpy(), dei.numpy(), {k: v.numpy() for k, v in gi.items()}), ref)
+    gscale = max(float(v.abs().max()) for v in gsum.values())
+    for k, v in gsum.items():
+        if k.endswith("theta.bias"):      # analytically zero: rounding noise in every call
+            assert float(g8[k].abs().max()) <= 1e-4 * gscale, k
+        else:
+            assert rel_l2(g8[k].numpy(), v.numpy()) <= RTOL_F32, (k, rel_l2(g8[k].numpy(), v.numpy()))   # both are fp32 approximations of the same sum
+
+
+def test_adain_style_map_of_another_size():
+    """AdaIN.py:20 only asserts that content and style agree in (N, C); the style statistics run over the style
+    map's own H x W (AdaIN.py:12-14,22).  Forward and both gradients against fp64 autograd of the same ops."""
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(2, 6, 5, 7, generator=g, dtype=torch.float64)
+    t = 1.5 * torch.randn(2, 6, 3, 4, generator=g, dtype=torch.float64) + 0.3
+    gout = torch.randn(2, 6, 5, 7, generator=g, dtype=torch.float64)
+    xr, tr = x.clone().requires_grad_(True), t.clone().requires_grad_(True)
+    ot.adain(xr, tr).backward(gout)
+    blk = frn_b200.AdaIN_block()
+    xc = x.float().to(dev).requires_grad_(True)
+    tc = t.float().to(dev).requires_grad_(True)
+    out = blk(xc, tc)
+    out.backward(gout.float().to(dev))
+    assert out.shape == x.shape and tc.grad.shape == t.shape
+    assert rel_l2(out.detach().cpu().numpy(), ot.adain(x, t).numpy()) < RTOL_F32
+    assert rel_l2(xc.grad.cpu().numpy(), xr.grad.numpy()) < RTOL_F32
+    assert rel_l2(tc.grad.cpu().numpy(), tr.grad.numpy()) < RTOL_F32
+    with pytest.raises(AssertionError):
+        blk(xc, tc[:, :3])                         # (N, C) mismatch: the reference's assert (AdaIN.py:20)
+
+
+def test_fp16_autocast_with_grad_scaler():
+    """What the reference's fast trainer actually runs (train_dsec_det_fast.py:240-265): torch.cuda.amp.autocast()
+    = fp16, loss scaled by a GradScaler.  The block computes in fp32 on fp32 copies (custom_fwd cast_inputs), returns
+    the autocast dtype like the reference's ATen ops do, and the unscaled gradients match an fp32 run on the same
+    fp16-rounded inputs."""
+    dev = torch.device("cuda:0")
+    b, c, h, w = 2, 64, 9, 8
+    gen = torch.Generator().manual_seed(4)
+    a16 = torch.randn(b, c, h, w, generator=gen).relu().half().to(dev)
+    e16 = torch.randn(b, c, h, w, generator=gen).relu().half().to(dev)
+    tgt = torch.randn(b, 2 * c, h, w, generator=gen).to(dev)
+    torch.manual_seed(2)
+    m = frn_b200.REFusion(c, c).to(dev)
+    # fp32 run on the same (fp16-representable) inputs
+    a32, e32 = a16.float().requires_grad_(True), e16.float().requires_grad_(True)
+    out32 = m(a32, e32)
+    ((out32 - tgt) ** 2).mean().backward()
+    ref = {k: p.grad.clone() for k, p in m.named_parameters()}
+    ref_da = a32.grad.clone()
+    m.zero_grad(set_to_none=True)
+    # the reference's AMP recipe
+    scaler = torch.amp.GradScaler("cuda", init_scale=1024.0)
+    opt = torch.optim.SGD(m.parameters(), lr=0.0)
+    a, e = a16.clone().requires_grad_(True), e16.clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.float16):
+        out = m(a, e)
+        assert out.dtype == torch.float16
+        loss = ((out.float() - tgt) ** 2).mean()
+    scaler.scale(loss).backward()
+    scaler.unscale_(opt)
+    scaler.step(opt)
+    scaler.update()
+    assert rel_l2(out.detach().float().cpu().numpy(), out32.detach().double().cpu().numpy()) < 1e-3      # fp16 rounding of out
+    gscale = max(float(v.abs().max()) for v in ref.values())
+    for k, p in m.named_parameters():
+        assert torch.isfinite(p.grad).all(), k
+        if k.endswith("theta.bias"):
+            assert float(p.grad.abs().max()) <= 1e-3 * gscale
+        else:       # dL/dout passes through fp16 once (out is returned as fp16): ~5e-4 relative
+            assert rel_l2(p.grad.cpu().numpy(), ref[k].double().cpu().numpy()) < 5e-3, k
+    assert a.grad.dtype == torch.float16
+    assert rel_l2((a.grad.float() / 1024.0).cpu().numpy(), ref_da.double().cpu().numpy()) < 5e-3

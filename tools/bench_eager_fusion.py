@@ -66,12 +66,14 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--no-ours", action="store_true", help="only the two eager arms")
     args = ap.parse_args()
     import frn_b200
     from harness_model import EagerREFusion
     run("PyTorch eager on the GPU, fp32 (TF32 off)", EagerREFusion, False, args)
     run("PyTorch eager on the GPU, TF32 allowed", EagerREFusion, True, args)
-    run("frn_b200 (fp32 parity, split TF32 on tcgen05)", frn_b200.REFusion, False, args)
+    if not args.no_ours:
+        run("frn_b200 (fp32 parity, split TF32 on tcgen05)", frn_b200.REFusion, False, args)
 
 
 if __name__ == "__main__":

@@ -58,6 +58,9 @@ lib = _lib.load()
 if hasattr(lib, "frn_debug_gemm_trace"):
     names = ["ld cp.async wait", "ld bar", "ld wait empty", "ld convert", "mma wait acc_free", "mma wait full",
              "mma issue", "epi wait acc_full", "epi store", "cvt A", "cvt B", "fence+arrive", "issue"]
+    if os.environ.get("FRN_GEMM_V2", "1") != "0":      # v2 kernel slots (CTA 0; split / epi slots are summed over 8 warps)
+        names = ["tma wait empty", "split wait raw (x8)", "split work (x8)", "mma wait lo_full", "mma wait acc_free",
+                 "mma wait raw_full", "mma issue", "epi wait acc_full (x8)", "epi store (x8)"]
     buf = (C.c_ulonglong * 16)()
     if lib.frn_debug_gemm_trace(buf):
         for nm, fn in (("conv", lambda: run_gemm(eng, W, x, out, C_, N, C_, B, (C_, 1, 0), (N, 1, C_ * N), (N, 1, C_ * N))),
