@@ -180,18 +180,48 @@ def run_reference(args):
     }))
 
 
+def bind_to_gpu_numa_node(local):
+    """Pin this process (and therefore its pinned staging buffers, first touch) to the CPUs of the NUMA node the GPU
+    hangs off, so that eight ranks' host-to-device copies do not all cross one socket's memory controller.  Returns a
+    short description for the JSON line; never fails."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return "numa_node unknown (-1): not pinned"
+        cpus = []
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.extend(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus:
+            return f"node {node}: none of its CPUs is in this process's cpuset, not pinned"
+        os.sched_setaffinity(0, cpus)
+        return f"pinned to NUMA node {node} ({len(cpus)} CPUs)"
+    except Exception as ex:      # no NVML / sysfs in the container: report and carry on
+        return f"not pinned ({type(ex).__name__})"
+
+
 def run_ours(args):
     import torch.distributed as dist
 
     import frn_b200
     from frn_b200 import _lib
-    from frn_b200.dist import GradBucket
+    from frn_b200.dist import LevelBuckets
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    numa = bind_to_gpu_numa_node(local)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -206,7 +236,7 @@ def run_ours(args):
     params = [p for m in mods for p in m.parameters()]
     for p in params:
         p.grad = torch.zeros_like(p)
-    bucket = GradBucket(params)
+    bucket = LevelBuckets(mods)          # one flat bucket per level, reduced as soon as that level's backward is enqueued
     host_a, host_e, dev_a, dev_e, douts = [], [], [], [], []
     for k, (c, h, w) in enumerate(levels):
         g = torch.Generator().manual_seed(1000 + k + 17 * rank)
@@ -230,6 +260,7 @@ def run_ours(args):
             for k in range(len(levels)):
                 a, e = inputs[k]
                 mods[k](a, e).backward(douts[k])
+                bucket.allreduce_level(k)
             return
         main = torch.cuda.current_stream()
         for k in big_first:
@@ -237,6 +268,7 @@ def run_ours(args):
             with torch.cuda.stream(lvl_streams[k]):
                 a, e = inputs[k]
                 mods[k](a, e).backward(douts[k])
+                bucket.allreduce_level(k)            # NCCL picks it up behind this stream's work (SURVEY.md 8.2 e)
         for k in big_first:
             main.wait_stream(lvl_streams[k])
 
@@ -245,7 +277,7 @@ def run_ours(args):
         for a, e in zip(dev_a, dev_e):
             a.grad = None; e.grad = None
         run_levels(list(zip(dev_a, dev_e)), serial)
-        bucket.allreduce(average=True)
+        bucket.wait()
 
     stage_a = [torch.empty_like(t, device=dev) for t in host_a]
     stage_e = [torch.empty_like(t, device=dev) for t in host_e]
@@ -282,13 +314,14 @@ def run_ours(args):
                 a = stage_a[k].detach().requires_grad_(True); e = stage_e[k].detach().requires_grad_(True)
                 out = mods[k](a, e)
                 out.backward(douts[k])
+                bucket.allreduce_level(k)
                 if full:
                     out_host[k].copy_(out.detach(), non_blocking=True)
         if lvl_streams is not None:
             for k in order:
                 main.wait_stream(lvl_streams[k])
-        bucket.allreduce(average=True)
-        norm_host.copy_(torch.linalg.vector_norm(bucket.flat).reshape(1), non_blocking=True)   # D2H result
+        bucket.wait()
+        norm_host.copy_(bucket.grad_norm().reshape(1), non_blocking=True)   # D2H result
         torch.cuda.current_stream().synchronize()
         return float(norm_host[0])
 
@@ -426,7 +459,7 @@ def run_ours(args):
         "config": {"workload": f"full fusion stack, 4 FPN levels, batch={B} per GPU, DSEC 480x640 synthetic "
                                "features, fp32 (BASELINE.json configs[1])",
                    "levels": [[B, c, h, w] for c, h, w in levels], "global_batch": world * B,
-                   "parallelism": f"dp{world} (batch shard + NCCL allreduce of {bucket.flat.numel()} fusion grads)",
+                   "parallelism": f"dp{world} (batch shard + NCCL allreduce of {bucket.numel} fusion grads in 4 per-level buckets, issued as each level finishes)",
                    "engines": {"attention": ["ffma", "tcgen05"][lib.frn_get_attn_engine()],
                                "gemm": ["ffma", "tcgen05"][lib.frn_get_gemm_engine()]},
                    "l2": f"inputs+saved state per step >> 126 MB L2 ({h2d_bytes / 1e6:.0f} MB of inputs alone); no flush"},
@@ -448,6 +481,7 @@ def run_ours(args):
                             "h2d_gbs_per_rank": h2d_bytes / (ms_e2e_full / 1e3) / 1e9,
                             "returned": "the four (B, 2C, H, W) fp32 outputs + the gradient norm, to pinned host memory"}
     line["config"]["levels_concurrent"] = lvl_streams is not None
+    line["config"]["host_numa"] = numa
     line["e2e"]["h2d_gbs_per_rank"] = h2d_bytes / (ms_e2e / args.steps / 1e3) / 1e9
     if world > 1:
         dist.destroy_process_group()

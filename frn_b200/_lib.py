@@ -72,6 +72,13 @@ _SIGNATURES = {
     "frn_refusion_infer_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
     "frn_refusion_infer": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p, C.c_void_p,
                                      C.POINTER(RefusionParams), C.c_void_p, C.c_void_p, C.c_size_t]),
+    "frn_refusion_lateral_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
+    "frn_refusion_lateral_forward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p, C.c_void_p,
+                                               C.POINTER(RefusionParams)] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p,
+                                               C.c_size_t]),
+    "frn_refusion_lateral_backward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p, C.c_void_p,
+                                                C.POINTER(RefusionParams)] + [C.c_void_p] * 6 +
+                                      [C.POINTER(RefusionParams)] + [C.c_void_p] * 3 + [C.c_size_t]),
     "frn_conv1x1_workspace_bytes": (C.c_size_t, [C.c_int] * 4),
     "frn_conv1x1_forward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 5 + [C.c_size_t]),
     "frn_conv1x1_backward": (C.c_int, [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p] * 7 + [C.c_size_t]),

@@ -114,37 +114,45 @@ __device__ __forceinline__ Moments warp_merge(Moments m) {
   }
   return m;
 }
-// Merge over the thread group that owns the row (GS = 32: one warp, GS = 256: the CTA).  `sm` holds 3 * 8 floats.
+// Merge over the thread group that owns the row (GS = 32: one warp, GS = 256 / 1024: the CTA).  `sm` holds 3 * 32 floats.
 template <int GS>
 __device__ __forceinline__ Moments group_merge(Moments m, float* sm) {
   m = warp_merge(m);
   if (GS == 32) return m;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   __syncthreads();
-  if (lane == 0) { sm[w] = m.n; sm[8 + w] = m.mean; sm[16 + w] = m.m2; }
+  if (lane == 0) { sm[w] = m.n; sm[32 + w] = m.mean; sm[64 + w] = m.m2; }
   __syncthreads();
   Moments t;
-  t.n = sm[0]; t.mean = sm[8]; t.m2 = sm[16];
+  t.n = sm[0]; t.mean = sm[32]; t.m2 = sm[64];
 #pragma unroll
-  for (int i = 1; i < GS / 32; i++) t.merge(sm[i], sm[8 + i], sm[16 + i]);
+  for (int i = 1; i < GS / 32; i++) t.merge(sm[i], sm[32 + i], sm[64 + i]);
   return t;
 }
 
 // ---- calc_mean_std -----------------------------------------------------------
 template <int GS, int W>
-__global__ void __launch_bounds__(256) row_mean_std_kernel(long rows, int N, const float* __restrict__ x,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) row_mean_std_kernel(long rows, int N, const float* __restrict__ x,
                                                            float eps, float* __restrict__ mean,
                                                            float* __restrict__ sd) {
-  __shared__ float sm[24];
+  __shared__ float sm[96];
   int lane;
   long row = my_row<GS>(rows, lane);
   if (row < 0) return;
   const float* xr = x + row * N;
   ShiftedSum a; a.init();
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> v; v.load(xr + n);
+  constexpr int U = 4;
+  for (int n0 = lane * W; n0 < N; n0 += U * GS * W) {
+    Vec<W> v[U];
 #pragma unroll
-    for (int q = 0; q < W; q++) a.add(v.v[q]);
+    for (int u = 0; u < U; u++)
+      if (n0 + u * GS * W < N) v[u].load(xr + n0 + u * GS * W);
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (n0 + u * GS * W < N) {
+#pragma unroll
+        for (int q = 0; q < W; q++) a.add(v[u].v[q]);
+      }
   }
   const Moments m = group_merge<GS>(a.finish(), sm);
   if (lane == 0) {
@@ -155,29 +163,43 @@ __global__ void __launch_bounds__(256) row_mean_std_kernel(long rows, int N, con
 
 // ---- gate + statistics of both gated maps ------------------------------------
 template <int GS, int W>
-__global__ void __launch_bounds__(256) gate_stats_kernel(long rows, int N, const float* __restrict__ r0,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) gate_stats_kernel(long rows, int N, const float* __restrict__ r0,
                                                          const float* __restrict__ e0,
                                                          float* __restrict__ r1, float* __restrict__ e1,
                                                          float eps, float* __restrict__ mu_r,
                                                          float* __restrict__ sd_r,
                                                          float* __restrict__ mu_e,
                                                          float* __restrict__ sd_e) {
-  __shared__ float sm[24];
+  __shared__ float sm[96];
   int lane;
   long row = my_row<GS>(rows, lane);
   if (row < 0) return;
   const long o = row * N;
   ShiftedSum ar, ae; ar.init(); ae.init();
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> a, b, x, y;
-    a.load(r0 + o + n); b.load(e0 + o + n);
+  // U chunks per thread and trip, all loads issued before the first use: 2 U independent 16-byte loads in flight per
+  // thread (with one chunk per trip the kernel ran at 0.65 of the HBM peak, latency- not bandwidth-bound)
+  constexpr int U = 4;
+  for (int n0 = lane * W; n0 < N; n0 += U * GS * W) {
+    Vec<W> a[U], b[U];
 #pragma unroll
-    for (int q = 0; q < W; q++) {
-      float m = a.v[q] * b.v[q];
-      x.v[q] = a.v[q] + m; y.v[q] = b.v[q] + m;
-      ar.add(x.v[q]); ae.add(y.v[q]);
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * GS * W;
+      if (n < N) { a[u].load(r0 + o + n); b[u].load(e0 + o + n); }
     }
-    x.store(r1 + o + n); y.store(e1 + o + n);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * GS * W;
+      if (n < N) {
+        Vec<W> x, y;
+#pragma unroll
+        for (int q = 0; q < W; q++) {
+          float m = a[u].v[q] * b[u].v[q];
+          x.v[q] = a[u].v[q] + m; y.v[q] = b[u].v[q] + m;
+          ar.add(x.v[q]); ae.add(y.v[q]);
+        }
+        x.store(r1 + o + n); y.store(e1 + o + n);
+      }
+    }
   }
   const Moments mr = group_merge<GS>(ar.finish(), sm);
   const Moments me = group_merge<GS>(ae.finish(), sm);
@@ -187,9 +209,76 @@ __global__ void __launch_bounds__(256) gate_stats_kernel(long rows, int N, const
   }
 }
 
+// Long rows (N >= 4096): the row is cut into S segments, one CTA per (row, segment).  A CTA per whole row keeps only
+// 2 x 16 bytes per thread in flight over ~19 trips, i.e. ~7 GB/s per CTA whatever else runs on the SM, and 2048 such
+// CTAs are 2.3 waves of 6 per SM: 143 us for 629 MB at DSEC level 1 (0.66 of the HBM peak) however many bytes the
+// kernel moves (the two-pass version took the same time for 876 MB).  A segment is ~2 K elements: every load of the
+// CTA is issued before the first use, the CTA lives for a few microseconds and the grid is ~18 waves.  Each CTA
+// leaves its (n, mean, M2) pair in `part`; the last CTA of a row to arrive (ticket counter) merges the S triples in
+// segment order, so the result does not depend on which CTA is last.
+template <int U>
+__global__ void __launch_bounds__(256) gate_stats_seg_kernel(int N, int seg_len, int S, const float* __restrict__ r0,
+                                                             const float* __restrict__ e0, float* __restrict__ r1,
+                                                             float* __restrict__ e1, float eps, float* __restrict__ mu_r,
+                                                             float* __restrict__ sd_r, float* __restrict__ mu_e,
+                                                             float* __restrict__ sd_e, float* part,
+                                                             unsigned int* counter) {
+  __shared__ float sm[96];
+  __shared__ unsigned int ticket;
+  const long row = blockIdx.x;
+  const int seg = blockIdx.y, lane = threadIdx.x;
+  const int n_begin = seg * seg_len, n_end = min(N, n_begin + seg_len);
+  const long o = row * N;
+  ShiftedSum ar, ae; ar.init(); ae.init();
+  for (int n0 = n_begin + lane * 4; n0 < n_end; n0 += U * 1024) {
+    Vec<4> a[U], b[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * 1024;
+      if (n < n_end) { a[u].load(r0 + o + n); b[u].load(e0 + o + n); }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * 1024;
+      if (n < n_end) {
+        Vec<4> x, y;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const float m = a[u].v[q] * b[u].v[q];
+          x.v[q] = a[u].v[q] + m; y.v[q] = b[u].v[q] + m;
+          ar.add(x.v[q]); ae.add(y.v[q]);
+        }
+        x.store(r1 + o + n); y.store(e1 + o + n);
+      }
+    }
+  }
+  const Moments mr = group_merge<256>(ar.finish(), sm);
+  const Moments me = group_merge<256>(ae.finish(), sm);
+  if (lane == 0) {
+    float* p = part + (row * S + seg) * 6;
+    p[0] = mr.n; p[1] = mr.mean; p[2] = mr.m2; p[3] = me.n; p[4] = me.mean; p[5] = me.m2;
+    __threadfence();
+    ticket = atomicAdd(&counter[row], 1u);
+  }
+  __syncthreads();
+  if (ticket != (unsigned)(S - 1)) return;
+  if (lane == 0) {                          // last CTA of this row: merge in segment order
+    __threadfence();
+    const volatile float* p = part + row * S * 6;
+    Moments tr{p[0], p[1], p[2]}, te{p[3], p[4], p[5]};
+    for (int j = 1; j < S; j++) {
+      tr.merge(p[j * 6], p[j * 6 + 1], p[j * 6 + 2]);
+      te.merge(p[j * 6 + 3], p[j * 6 + 4], p[j * 6 + 5]);
+    }
+    mu_r[row] = tr.mean; sd_r[row] = sqrtf(tr.m2 / (float)(N - 1) + eps);
+    mu_e[row] = te.mean; sd_e[row] = sqrtf(te.m2 / (float)(N - 1) + eps);
+    counter[row] = 0;                       // ready for the next launch
+  }
+}
+
 // ---- AdaIN apply --------------------------------------------------------------
 template <int GS, int W>
-__global__ void __launch_bounds__(256) adain_apply_kernel(long rows, int C, int N, const float* __restrict__ x,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) adain_apply_kernel(long rows, int C, int N, const float* __restrict__ x,
                                                           const float* __restrict__ mu_x,
                                                           const float* __restrict__ sd_x,
                                                           const float* __restrict__ mu_t,
@@ -199,11 +288,19 @@ __global__ void __launch_bounds__(256) adain_apply_kernel(long rows, int C, int 
   const float* xr = x + row * N;
   float* orow = out + (row / C) * ob + (row % C) * (long)N;
   float mx = mu_x[row], a = sd_t[row] / sd_x[row], mt = mu_t[row];
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> v; v.load(xr + n);
+  constexpr int U = 4;
+  for (int n0 = lane * W; n0 < N; n0 += U * GS * W) {
+    Vec<W> v[U];
 #pragma unroll
-    for (int q = 0; q < W; q++) v.v[q] = fmaf(v.v[q] - mx, a, mt);
-    v.store(orow + n);
+    for (int u = 0; u < U; u++)
+      if (n0 + u * GS * W < N) v[u].load(xr + n0 + u * GS * W);
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (n0 + u * GS * W < N) {
+#pragma unroll
+        for (int q = 0; q < W; q++) v[u].v[q] = fmaf(v[u].v[q] - mx, a, mt);
+        v[u].store(orow + n0 + u * GS * W);
+      }
   }
 }
 
@@ -214,7 +311,7 @@ __device__ __forceinline__ uint32_t bf16_rn(float f) {
   return (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;
 }
 template <int GS, int W>
-__global__ void __launch_bounds__(256) adain_apply_bf16_kernel(long rows, int C, int N, const float* __restrict__ x,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) adain_apply_bf16_kernel(long rows, int C, int N, const float* __restrict__ x,
                                                                const float* __restrict__ mu_x,
                                                                const float* __restrict__ sd_x,
                                                                const float* __restrict__ mu_t,
@@ -236,7 +333,7 @@ __global__ void __launch_bounds__(256) adain_apply_bf16_kernel(long rows, int C,
 
 // ---- AdaIN backward -------------------------------------------------------------
 template <int GS, int W>
-__global__ void __launch_bounds__(256) adain_bwd_reduce_kernel(long rows, int C, int N,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) adain_bwd_reduce_kernel(long rows, int C, int N,
                                                                const float* __restrict__ g, long gb,
                                                                const float* __restrict__ x,
                                                                const float* __restrict__ mu_x,
@@ -248,10 +345,18 @@ __global__ void __launch_bounds__(256) adain_bwd_reduce_kernel(long rows, int C,
   const float* gr = g + (row / C) * gb + (row % C) * (long)N;
   float mx = mu_x[row];
   float s1 = 0.f, s2 = 0.f;
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> v, gg; v.load(xr + n); gg.load(gr + n);
+  constexpr int U = 4;
+  for (int n0 = lane * W; n0 < N; n0 += U * GS * W) {
+    Vec<W> v[U], gg[U];
 #pragma unroll
-    for (int q = 0; q < W; q++) { s1 += gg.v[q]; s2 = fmaf(gg.v[q], v.v[q] - mx, s2); }
+    for (int u = 0; u < U; u++)
+      if (n0 + u * GS * W < N) { v[u].load(xr + n0 + u * GS * W); gg[u].load(gr + n0 + u * GS * W); }
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (n0 + u * GS * W < N) {
+#pragma unroll
+        for (int q = 0; q < W; q++) { s1 += gg[u].v[q]; s2 = fmaf(gg[u].v[q], v[u].v[q] - mx, s2); }
+      }
   }
   s1 = group_sum<GS>(s1, red);
   s2 = group_sum<GS>(s2, red);
@@ -259,7 +364,7 @@ __global__ void __launch_bounds__(256) adain_bwd_reduce_kernel(long rows, int C,
 }
 
 template <int GS, int W>
-__global__ void __launch_bounds__(256) adain_bwd_content_kernel(
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) adain_bwd_content_kernel(
     long rows, int C, int N, const float* __restrict__ g, long gb, const float* __restrict__ x,
     const float* __restrict__ mu_x, const float* __restrict__ sd_x, const float* __restrict__ sd_t,
     const float* __restrict__ g1, const float* __restrict__ g2, float* __restrict__ dx, int accumulate) {
@@ -270,20 +375,34 @@ __global__ void __launch_bounds__(256) adain_bwd_content_kernel(
   float mx = mu_x[row], isx = 1.f / sd_x[row];
   float k = sd_t[row] * isx;
   float c1 = g1[row] / (float)N, c2 = g2[row] * isx / (float)(N - 1);
-  for (int n = lane * W; n < N; n += GS * W) {
-    Vec<W> v, gg, o; v.load(xr + n); gg.load(gr + n);
-    if (accumulate) o.load_rw(dr + n);
+  constexpr int U = 2;
+  for (int n0 = lane * W; n0 < N; n0 += U * GS * W) {
+    Vec<W> v[U], gg[U], o[U];
 #pragma unroll
-    for (int q = 0; q < W; q++) {
-      float r = k * (gg.v[q] - c1 - (v.v[q] - mx) * c2);
-      o.v[q] = accumulate ? o.v[q] + r : r;
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * GS * W;
+      if (n < N) {
+        v[u].load(xr + n); gg[u].load(gr + n);
+        if (accumulate) o[u].load_rw(dr + n);
+      }
     }
-    o.store(dr + n);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * GS * W;
+      if (n < N) {
+#pragma unroll
+        for (int q = 0; q < W; q++) {
+          float r = k * (gg[u].v[q] - c1 - (v[u].v[q] - mx) * c2);
+          o[u].v[q] = accumulate ? o[u].v[q] + r : r;
+        }
+        o[u].store(dr + n);
+      }
+    }
   }
 }
 
 template <int GS, int W>
-__global__ void __launch_bounds__(256) adain_bwd_style_kernel(long rows, int N, const float* __restrict__ t,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) adain_bwd_style_kernel(long rows, int N, const float* __restrict__ t,
                                                               const float* __restrict__ mu_t,
                                                               const float* __restrict__ sd_t,
                                                               const float* __restrict__ g1,
@@ -303,7 +422,7 @@ __global__ void __launch_bounds__(256) adain_bwd_style_kernel(long rows, int N, 
 }
 
 template <int GS, int W>
-__global__ void __launch_bounds__(256) center_rows_kernel(long rows, int N, const float* __restrict__ y,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) center_rows_kernel(long rows, int N, const float* __restrict__ y,
                                                           const float* __restrict__ mean,
                                                           float* __restrict__ yc) {
   ROW_KERNEL_PROLOGUE();
@@ -317,7 +436,7 @@ __global__ void __launch_bounds__(256) center_rows_kernel(long rows, int N, cons
 }
 
 template <int GS, int W>
-__global__ void __launch_bounds__(256) add_row_bias_kernel(long rows, int N, const float* __restrict__ u,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) add_row_bias_kernel(long rows, int N, const float* __restrict__ u,
                                                            float* __restrict__ x) {
   ROW_KERNEL_PROLOGUE();
   float b = u[row];
@@ -330,7 +449,7 @@ __global__ void __launch_bounds__(256) add_row_bias_kernel(long rows, int N, con
 }
 
 template <int GS, int W>
-__global__ void __launch_bounds__(256) row_dot_kernel(long rows, int N, const float* __restrict__ x,
+__global__ void __launch_bounds__(GS < 256 ? 256 : GS) row_dot_kernel(long rows, int N, const float* __restrict__ x,
                                                       const float* __restrict__ y, float* __restrict__ out) {
   ROW_KERNEL_PROLOGUE();
   float s = 0.f;
@@ -343,9 +462,96 @@ __global__ void __launch_bounds__(256) row_dot_kernel(long rows, int N, const fl
   if (lane == 0) out[row] = s;
 }
 
+// ---- bf16-inference fast path (frn_refusion_infer, FRN_BF16): padded rows, tf32-exact GEMM operands ------------------
+// Maps live in buffers whose rows are padded to ld = round_up(N, 4) floats, so that every row is 16-byte aligned and
+// TMA can describe them whatever N is (DDD17: N = 5655, 1452, 374, 99), and every value a GEMM will read is rounded
+// to tf32 by the kernel that WRITES it: the v2 GEMM then feeds the raw tiles to the tensor core with no staging
+// pass at all (kind::tf32 would truncate unrounded operands).
+__device__ __forceinline__ float rn_tf32(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+}
+// bf16 (rows, N) -> fp32 (rows, ld), exact (bf16 values are tf32 values); pad columns zero
+__global__ void __launch_bounds__(256) cast_pad_bf16_kernel(long rows, int N, int ld, const uint16_t* __restrict__ src,
+                                                            float* __restrict__ dst) {
+  const long total = rows * ld, stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long r = i / ld;
+    const int n = (int)(i - r * ld);
+    dst[i] = n < N ? __uint_as_float((uint32_t)__ldg(src + r * N + n) << 16) : 0.f;
+  }
+}
+__global__ void round_tf32_kernel(long n, const float* __restrict__ src, float* __restrict__ dst) {
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = rn_tf32(src[i]);
+}
+// gate (fusion.py:26-28) + statistics of both gated maps on padded rows; r1 / e1 are stored rounded to tf32 (they are
+// GEMM operands and the AdaIN content), the statistics come from the unrounded values
+template <int GS>
+__global__ void __launch_bounds__(256) gate_stats_pad_kernel(long rows, int N, int ld, const float* __restrict__ r0,
+                                                             const float* __restrict__ e0, float* __restrict__ r1,
+                                                             float* __restrict__ e1, float eps, float* __restrict__ mu_r,
+                                                             float* __restrict__ sd_r, float* __restrict__ mu_e,
+                                                             float* __restrict__ sd_e) {
+  __shared__ float sm[96];
+  int lane;
+  long row = my_row<GS>(rows, lane);
+  if (row < 0) return;
+  const long o = row * ld;
+  ShiftedSum ar, ae; ar.init(); ae.init();
+  for (int n = lane * 4; n < N; n += GS * 4) {
+    Vec<4> a, b, x, y;
+    a.load(r0 + o + n); b.load(e0 + o + n);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const bool ok = n + q < N;
+      const float m = a.v[q] * b.v[q];
+      const float xv = a.v[q] + m, yv = b.v[q] + m;
+      if (ok) { ar.add(xv); ae.add(yv); }
+      x.v[q] = ok ? rn_tf32(xv) : 0.f; y.v[q] = ok ? rn_tf32(yv) : 0.f;
+    }
+    x.store(r1 + o + n); y.store(e1 + o + n);
+  }
+  const Moments mr = group_merge<GS>(ar.finish(), sm);
+  const Moments me = group_merge<GS>(ae.finish(), sm);
+  if (lane == 0) {
+    mu_r[row] = mr.mean; sd_r[row] = sqrtf(mr.m2 / (float)(N - 1) + eps);
+    mu_e[row] = me.mean; sd_e[row] = sqrtf(me.m2 / (float)(N - 1) + eps);
+  }
+}
+// yc (rows, ld) = round_tf32(y (rows, N) - mean), pad columns zero
+template <int GS>
+__global__ void __launch_bounds__(256) center_rows_pad_kernel(long rows, int N, int ld, const float* __restrict__ y,
+                                                              const float* __restrict__ mean, float* __restrict__ yc) {
+  int lane;
+  long row = my_row<GS>(rows, lane);
+  if (row < 0) return;
+  const float mu = mean[row];
+  for (int n = lane; n < ld; n += GS) yc[row * ld + n] = n < N ? rn_tf32(__ldg(y + row * N + n) - mu) : 0.f;
+}
+// AdaIN affine of padded content rows -> bf16 output rows of N elements (batch stride ob)
+template <int GS>
+__global__ void __launch_bounds__(256) adain_apply_bf16_pad_kernel(long rows, int C, int N, int ld,
+                                                                   const float* __restrict__ x,
+                                                                   const float* __restrict__ mu_x,
+                                                                   const float* __restrict__ sd_x,
+                                                                   const float* __restrict__ mu_t,
+                                                                   const float* __restrict__ sd_t,
+                                                                   uint16_t* __restrict__ out, long ob) {
+  int lane;
+  long row = my_row<GS>(rows, lane);
+  if (row < 0) return;
+  const float* xr = x + row * ld;
+  uint16_t* orow = out + (row / C) * ob + (row % C) * (long)N;
+  const float mx = mu_x[row], a = sd_t[row] / sd_x[row], mt = mu_t[row];
+  for (int n = lane; n < N; n += GS) orow[n] = (uint16_t)bf16_rn(fmaf(__ldg(xr + n) - mx, a, mt));
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // Dispatch on row length (warp- or CTA-per-row) and vector width.
+// Dispatch on row length (warp- or CTA-per-row) and vector width.  (One 1024-thread CTA per long row was tried to
+// get rid of the ragged last wave -- 2048 rows are 2.3 waves of 6 CTAs per SM -- and lost: with one resident CTA per
+// SM nothing overlaps a CTA's load -> reduce -> exit phases; gate_stats went from 143 to 231 us.)
 #define LAUNCH_ROWS(KERNEL, passes, rows, N, vec, ...)                                    \
   do {                                                                                    \
     ScopedTimer tm__(st, FRN_TIME_ROWS);                                                  \
@@ -369,9 +575,28 @@ int row_mean_std(cudaStream_t st, long rows, int N, const float* x, float eps, f
   return FRN_OK;
 }
 
+int gate_stats_segments(int N) { return N >= 4096 && N % 4 == 0 ? (N / 2048 < 16 ? N / 2048 : 16) : 1; }
+size_t gate_stats_scratch_bytes(long rows, int N) {
+  const int S = gate_stats_segments(N);
+  return S > 1 ? align_up((size_t)rows * S * 6 * sizeof(float)) + align_up((size_t)rows * sizeof(unsigned int)) : 0;
+}
 int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* e0, float* r1, float* e1,
-               float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e) {
+               float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e, void* scratch) {
   bool vec = (N % 4 == 0) && aligned16(r0) && aligned16(e0) && aligned16(r1) && aligned16(e1);
+  const int S = gate_stats_segments(N);
+  if (vec && S > 1 && scratch && rows <= 2147483647L) {
+    ScopedTimer tm(st, FRN_TIME_ROWS);
+    KernelTimer kt(st, "gate_stats_kernel", 16.0 * (double)rows * N);
+    float* part = (float*)scratch;
+    unsigned int* counter = (unsigned int*)((char*)scratch + align_up((size_t)rows * S * 6 * sizeof(float)));
+    if (cudaMemsetAsync(counter, 0, (size_t)rows * sizeof(unsigned int), st) != cudaSuccess) return (int)cudaGetLastError();
+    const int seg_len = ((N + S - 1) / S + 3) / 4 * 4;
+    const dim3 grid((unsigned)rows, (unsigned)S);
+    if (seg_len <= 2048) gate_stats_seg_kernel<2><<<grid, 256, 0, st>>>(N, seg_len, S, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e, part, counter);
+    else gate_stats_seg_kernel<3><<<grid, 256, 0, st>>>(N, seg_len, S, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e, part, counter);
+    FRN_LAUNCH_CHECK();
+    return FRN_OK;
+  }
   LAUNCH_ROWS(gate_stats_kernel, 4, rows, N, vec, rows, N, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e);
   return FRN_OK;
 }
@@ -415,6 +640,48 @@ int adain_bwd_style(cudaStream_t st, int B, int C, int N, const float* t, const 
   long rows = (long)B * C;
   bool vec = (N % 4 == 0) && aligned16(t) && aligned16(dstyle);
   LAUNCH_ROWS(adain_bwd_style_kernel, 2, rows, N, vec, rows, N, t, mu_t, sd_t, g1, g2, dstyle);
+  return FRN_OK;
+}
+
+#define LAUNCH_PAD(KERNEL, name, bytes, rows, N, ...)                                     \
+  do {                                                                                    \
+    ScopedTimer tm__(st, FRN_TIME_ROWS);                                                  \
+    KernelTimer kt__(st, name, bytes);                                                    \
+    if ((N) >= 1024) KERNEL<256><<<(unsigned)(rows), 256, 0, st>>>(__VA_ARGS__);          \
+    else KERNEL<32><<<(unsigned)(((rows) + 7) / 8), 256, 0, st>>>(__VA_ARGS__);           \
+    FRN_LAUNCH_CHECK();                                                                   \
+  } while (0)
+
+int cast_pad_bf16(cudaStream_t st, long rows, int N, int ld, const uint16_t* src, float* dst) {
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  long blocks = (rows * ld + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  cast_pad_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, ld, src, dst);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+int round_tf32_copy(cudaStream_t st, long n, const float* src, float* dst) {
+  long blocks = (n + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  round_tf32_kernel<<<(unsigned)blocks, 256, 0, st>>>(n, src, dst);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+int gate_stats_pad(cudaStream_t st, long rows, int N, int ld, const float* r0, const float* e0, float* r1, float* e1,
+                   float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e) {
+  LAUNCH_PAD(gate_stats_pad_kernel, "gate_stats_pad_kernel", 16.0 * rows * N, rows, N, rows, N, ld, r0, e0, r1, e1, eps,
+             mu_r, sd_r, mu_e, sd_e);
+  return FRN_OK;
+}
+int center_rows_pad(cudaStream_t st, long rows, int N, int ld, const float* y, const float* mean, float* yc) {
+  LAUNCH_PAD(center_rows_pad_kernel, "center_rows_pad_kernel", 8.0 * rows * N, rows, N, rows, N, ld, y, mean, yc);
+  return FRN_OK;
+}
+int adain_apply_bf16_pad(cudaStream_t st, int B, int C, int N, int ld, const float* x, const float* mu_x,
+                         const float* sd_x, const float* mu_t, const float* sd_t, uint16_t* out, long ob) {
+  const long rows = (long)B * C;
+  LAUNCH_PAD(adain_apply_bf16_pad_kernel, "adain_apply_bf16_pad_kernel", 6.0 * rows * N, rows, N, rows, C, N, ld, x, mu_x,
+             sd_x, mu_t, sd_t, out, ob);
   return FRN_OK;
 }
 

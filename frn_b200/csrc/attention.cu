@@ -12,6 +12,7 @@
 //            kernels at the bottom of this file, one sample at a time.
 #include "common.cuh"
 
+#ifdef FRN_DEBUG_ENGINES      // FFMA streaming-softmax engine: debug builds only (A/B comparisons)
 namespace frn {
 namespace {
 
@@ -436,3 +437,15 @@ int attn_backward(cudaStream_t st, int B, int N, int d, const float* Qc, const f
   return FRN_ERR_UNSUPPORTED;
 }
 }  // namespace frn
+
+#else
+namespace frn {
+int attn_forward(cudaStream_t, int, int, int, const float*, const float*, const float*, float*, float*) {
+  return FRN_ERR_UNSUPPORTED;
+}
+int attn_backward(cudaStream_t, int, int, int, const float*, const float*, const float*, const float*, const float*,
+                  const float*, const float*, const float*, const float*, float*, float*, float*) {
+  return FRN_ERR_UNSUPPORTED;
+}
+}  // namespace frn
+#endif  // FRN_DEBUG_ENGINES

@@ -1805,19 +1805,25 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
                   const SplitImage& V, const SplitImage& dY, const float* lse_pad, const float* delta_pad,
                   float* dQp, float* dKp, float* dVp) {
   const int NP = attn_tc_np(N);
+  using CfgK2 = Dkv2Cfg<DPAD>;
+  auto kern_kv2 = attn_dkv2_tc_kernel<DPAD>;
+#ifdef FRN_DEBUG_ENGINES
+  // first designs (two tiles per CTA in ping-pong, operands in shared memory, one issuing warp): debug builds only,
+  // FRN_DQ_DESIGN=1 / FRN_DKV_DESIGN=1
   using CfgK = DkvCfg<DPAD, NT>;
   using CfgQ = DqCfg<DPAD, NT>;
-  using CfgK2 = Dkv2Cfg<DPAD>;
   auto kern_kv = attn_dkv_tc_kernel<DPAD, NT>;
-  auto kern_kv2 = attn_dkv2_tc_kernel<DPAD>;
   auto kern_q = attn_dq_tc_kernel<DPAD, NT>;
   static const int dkv_design = [] { const char* e = getenv("FRN_DKV_DESIGN"); return (e && e[0] == '1') ? 1 : 2; }();
+  static const int dq_design = [] { const char* e = getenv("FRN_DQ_DESIGN"); return (e && e[0] == '1') ? 1 : 2; }();
   FRN_TRY(set_smem(kern_kv, CfgK::kSmem));
-  FRN_TRY(set_smem(kern_kv2, CfgK2::kSmem));
   FRN_TRY(set_smem(kern_q, CfgQ::kSmem));
   const dim3 grid_kv(cdiv(NP / 128, NT), B, cdiv(d, 32)), grid_q(cdiv(NP / 128, NT), B);
+#else
+  constexpr int dkv_design = 2, dq_design = 2;
+#endif
+  FRN_TRY(set_smem(kern_kv2, CfgK2::kSmem));
   const dim3 grid_kv2(NP / 128, B, cdiv(d, 32));
-  static const int dq_design = [] { const char* e = getenv("FRN_DQ_DESIGN"); return (e && e[0] == '1') ? 1 : 2; }();
   const bool dq2 = dq_design == 2;
   if (dq2) FRN_TRY(set_smem(attn_dq2_tc_kernel<DPAD>, Dq2Cfg<DPAD>::kSmem));
   const dim3 grid_q2(NP / 128, B);
@@ -1825,8 +1831,10 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
     if (dq2)
       attn_dq2_tc_kernel<DPAD><<<grid_q2, Dq2Cfg<DPAD>::kThreads, Dq2Cfg<DPAD>::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad,
                                                                                               delta_pad, dQp);
+#ifdef FRN_DEBUG_ENGINES
     else
       kern_q<<<grid_q, CfgQ::kThreads, CfgQ::kSmem, s_>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dQp);
+#endif
   };
   ScopedTimer tm(st, FRN_TIME_ATTN_BWD);
   const Fork fk = fork_stream(st, 0);
@@ -1842,8 +1850,10 @@ int launch_bwd_tc(cudaStream_t st, int B, int N, int d, const SplitImage& Q, con
                                                                                           delta_pad, dKp, dVp);
     } else if (dkv_design == 2)
       kern_kv2<<<grid_kv2, CfgK2::kThreads, CfgK2::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+#ifdef FRN_DEBUG_ENGINES
     else
       kern_kv<<<grid_kv, CfgK::kThreads, CfgK::kSmem, st>>>(N, NP, d, Q, K, V, dY, lse_pad, delta_pad, dKp, dVp);
+#endif
     FRN_LAUNCH_CHECK();
   }
   if (fk.side) {

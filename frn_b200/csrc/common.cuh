@@ -49,6 +49,13 @@ struct ShapeTimer {
   ~ShapeTimer();
 };
 
+// NVTX range over a host-side stage: shows up as "frn.<stage>" in Nsight Systems / Compute;
+// costs a few ns when no tool is attached (nvtx3 is header-only and resolves its injection library lazily).
+struct NvtxRange {
+  explicit NvtxRange(const char* name);
+  ~NvtxRange();
+};
+
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, device) instead of per launch.
 int set_smem_once(const void* kern, int bytes);
 
@@ -134,7 +141,14 @@ struct GemmDesc {
   float alpha;
   int accumulate;        // C += result
   int reduce_batch;
-  int fast;              // tcgen05 engine only: single-pass TF32 (hi * hi), ~2^-11 relative; bf16-tolerance inference
+  int fast;              // tcgen05 engine only: single-pass TF32 (hi * hi), ~2^-11 relative; bf16-tolerance inference.
+                         // 1: operands are rounded to tf32 by the staging warps of the first kernel; 2: the operands
+                         // already hold tf32-exact values (their producers rounded them): v2 kernel, no staging at all
+  // tcgen05 v2 kernel only: drop the lo*lo product (3 tensor-core products instead of 4).  lo*lo is 2^-22 of the
+  // product on average (one-sided); it only matters when an operand is near-constant AND the result is normalised
+  // by its own variance afterwards (conv0 of a blanked RGB map, model.py:279-280), so the gradient GEMMs of conv0
+  // skip it.
+  int no_lolo;
   // tcgen05 engine only, plain stores (no reduce_batch / accumulate): rows [g * group_m, (g + 1) * group_m) of the
   // product go to the g-th of up to three output matrices (C, C1, C2; same strides) -- one GEMM for the three 1x1
   // projections that read the same feature map.  group_m == 0: a single output.
@@ -212,14 +226,24 @@ int attn_backward(cudaStream_t st, int B, int N, int d, const float* Qc, const f
 int row_mean_std(cudaStream_t st, long rows, int N, const float* x, float eps, float* mean,
                  float* sd);
 // r1 = r0 + r0*e0, e1 = e0 + r0*e0 fused with the row statistics of r1 and e1.
+// scratch (gate_stats_scratch_bytes, may be null): enables the segmented kernel for long rows
 int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* e0, float* r1,
-               float* e1, float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e);
+               float* e1, float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e, void* scratch = nullptr);
+size_t gate_stats_scratch_bytes(long rows, int N);
 // out[b][c][n] = (x - mu_x)/sd_x * sd_t + mu_t   (out has batch stride ob)
 int adain_apply(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x,
                 const float* sd_x, const float* mu_t, const float* sd_t, float* out, long ob);
 // the same with a bf16 output (inference with bf16 activations); ob in elements
 int adain_apply_bf16(cudaStream_t st, int B, int C, int N, const float* x, const float* mu_x,
                      const float* sd_x, const float* mu_t, const float* sd_t, uint16_t* out, long ob);
+// bf16-inference fast path (adain.cu): padded rows (ld = round_up(N, 4)), tf32-exact values
+int cast_pad_bf16(cudaStream_t st, long rows, int N, int ld, const uint16_t* src, float* dst);
+int round_tf32_copy(cudaStream_t st, long n, const float* src, float* dst);
+int gate_stats_pad(cudaStream_t st, long rows, int N, int ld, const float* r0, const float* e0, float* r1, float* e1,
+                   float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e);
+int center_rows_pad(cudaStream_t st, long rows, int N, int ld, const float* y, const float* mean, float* yc);
+int adain_apply_bf16_pad(cudaStream_t st, int B, int C, int N, int ld, const float* x, const float* mu_x,
+                         const float* sd_x, const float* mu_t, const float* sd_t, uint16_t* out, long ob);
 // dst[i] = float(src[i]) for bf16 src
 int cast_bf16_to_f32(cudaStream_t st, size_t count, const uint16_t* src, float* dst);
 // g1 = sum_n g, g2 = sum_n g * xhat per (b, c) row; g has batch stride gb.
@@ -272,5 +296,12 @@ int fill_zero(cudaStream_t st, float* p, size_t count);
 int center_cols_parts(int N);
 int center_cols(cudaStream_t st, int B, int N, int d, float* x, float* part);
 int scale_sum_batch(cudaStream_t st, int B, int C, const float* alpha, float scale, float* out);
+// REFusion + lateral conv (row f1), see misc.cu
+int affine_coeffs(cudaStream_t st, int B, int C, const float* mxa, const float* sxa, const float* mta, const float* sta,
+                  const float* mxb, const float* sxb, const float* mtb, const float* stb, float* sc, float* tc);
+int scale_cols(cudaStream_t st, int B, int M, int K, const float* w, const float* sc, float* out);
+int row_sums(cudaStream_t st, int B, int M, int N, const float* x, float* out);
+int lateral_wgrad_combine(cudaStream_t st, int B, int M, int K, const float* P, const float* S, const float* sc,
+                          const float* tc, float* dW, float* db);
 
 }  // namespace frn

@@ -24,14 +24,42 @@ struct Ctx {
   Arena ws;
   size_t splitk_need;   // dry: max split-K partial bytes over all reduce GEMMs
   void* splitk;
+  void* splitk_alt;     // second split-K buffer: GEMMs enqueued on the side stream (block B) never share partials with block A
   size_t splitk_cap;
   int attn_eng;         // 0 = FFMA streaming kernels, 1 = tcgen05 kernels
   int fast;             // frn_refusion_infer(FRN_BF16): single-pass TF32 products on the tcgen05 engines
   bool out_bf16;        // ... and the AdaIN affine writes the block output as bf16
+  bool no_apply;        // REFusion + lateral (row f1): the 2C map is not written, only its statistics are needed
   Ctx(cudaStream_t s, void* p, size_t bytes, bool dry_)
-      : st(s), dry(dry_), ws(p, bytes, dry_), splitk_need(0), splitk(nullptr), splitk_cap(0),
-        attn_eng(attn_engine()), fast(0), out_bf16(false) {}
+      : st(s), dry(dry_), ws(p, bytes, dry_), splitk_need(0), splitk(nullptr), splitk_alt(nullptr), splitk_cap(0),
+        attn_eng(attn_engine()), fast(0), out_bf16(false), no_apply(false) {}
 };
+
+// Two independent pieces of work (CrossAttentionBlock A / B of REFusion, the two per-map halves of their projection
+// gradients, the two conv0 gradient pairs): `first` runs on the caller's stream, `second` on its side stream
+// (fork_stream slot 1) with its own scratch region and its own split-K buffer, then the streams are joined.  The
+// arena sequence is the same whether or not a side stream is available (dry runs, measurement hooks on).
+template <typename F1, typename F2>
+int run_pair(Ctx& c, F1 first, F2 second) {
+  const size_t m0 = c.ws.off, peak0 = c.ws.peak;
+  Fork fk{c.st, nullptr, nullptr, nullptr};
+  if (!c.dry) fk = fork_stream(c.st, 1);
+  c.ws.peak = m0;
+  int rc = first();
+  const size_t used = c.ws.peak - m0;                    // scratch of `first`: stays reserved while `second` runs
+  c.ws.peak = std::max(peak0, c.ws.peak);
+  c.ws.release_to(m0);
+  if (rc == FRN_OK) {
+    c.ws.take<char>(used);
+    cudaStream_t main = c.st;
+    if (fk.side) { c.st = fk.side; std::swap(c.splitk, c.splitk_alt); }
+    rc = second();
+    if (fk.side) { c.st = main; std::swap(c.splitk, c.splitk_alt); }
+  }
+  join_stream(fk);
+  c.ws.release_to(m0);
+  return rc;
+}
 
 #define RUN(c, expr)              \
   do {                            \
@@ -40,7 +68,7 @@ struct Ctx {
 
 int run_gemm(Ctx& c, const GemmDesc& d_in) {
   GemmDesc d = d_in;
-  d.fast = c.fast;
+  if (!d.fast) d.fast = c.fast;
   if (c.dry) {
     c.splitk_need = std::max(c.splitk_need, gemm_workspace_bytes(d));
     return FRN_OK;
@@ -91,8 +119,9 @@ int proj3(Ctx& c, const float* w0, const float* b0, const float* w1, const float
 }
 // dx (batch, K, N) (+)= W^T (K, M) @ dy (batch, M, N), dy element (m, n) at dy[m*sm + n*sn]
 int conv1x1_dgrad(Ctx& c, const float* W, const float* dy, long sm, long sn, long sb, float* dx,
-                  int batch, int M, int K, int N, int accumulate) {
+                  int batch, int M, int K, int N, int accumulate, int no_lolo = 0) {
   GemmDesc d = desc(W, dy, dx, K, N, M, batch);
+  d.no_lolo = no_lolo;
   d.sAm = 1; d.sAk = K; d.sAb = 0;
   d.sBk = sm; d.sBn = sn; d.sBb = sb;
   d.sCm = N; d.sCn = 1; d.sCb = (long)K * N;
@@ -101,8 +130,9 @@ int conv1x1_dgrad(Ctx& c, const float* W, const float* dy, long sm, long sn, lon
 }
 // dW (M, K) = sum_b dy_b (M, N) @ x_b^T (N, K);  db (M) = sum_b sum_n dy_b
 int conv1x1_wgrad(Ctx& c, const float* dy, long sm, long sn, long sb, const float* x, float* dW,
-                  float* db, int batch, int M, int K, int N) {
+                  float* db, int batch, int M, int K, int N, int no_lolo = 0) {
   GemmDesc d = desc(dy, x, dW, M, K, N, batch);
+  d.no_lolo = no_lolo;
   d.sAm = sm; d.sAk = sn; d.sAb = sb;
   d.sBk = 1; d.sBn = N; d.sBb = (long)K * N;
   d.sCm = K; d.sCn = 1;
@@ -177,6 +207,7 @@ SplitImage take_image(Ctx& c, int B, int N, int d, bool pos, bool chan, bool lo 
 
 // softmax(Q K) V for all samples.  d <= 64: fused streaming kernel; else GEMM + row softmax.
 int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
+  NvtxRange nv("frn.attention.fwd");
   if (d <= 64) {
     if (c.attn_eng == 1 || c.dry) {     // dry: count both engines' scratch, the arena keeps the peak
       const size_t m0 = c.ws.off;
@@ -229,6 +260,7 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
 // statistics of x0 (REFusion computes them inside the gate kernel).
 int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, const frn_cab_params& p,
                 float* out, long ob, const CabSaved& s, bool have_x_stats, bool have_qkv = false) {
+  NvtxRange nv("frn.cab.fwd");
   const int d = C / 8;
   if (!have_qkv) {                                                  // REFusion projects both blocks at once (proj3)
     FRN_TRY(conv1x1(c, p.g_w, p.g_b, x0, s.Vc, B, d, C, N));        // Attention.py:24
@@ -263,7 +295,9 @@ int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, c
     FRN_TRY(run_gemm(c, m));
   }
   if (!have_x_stats) RUN(c, row_mean_std(c.st, (long)B * C, N, x0, kEps, s.mu_x, s.sd_x));
-  if (c.out_bf16)     // `out` is a bf16 buffer; ob is in elements either way
+  if (c.no_apply) {
+    // the consumer folds the AdaIN affine into its own weights (refusion_lateral_forward)
+  } else if (c.out_bf16)     // `out` is a bf16 buffer; ob is in elements either way
     RUN(c, adain_apply_bf16(c.st, B, C, N, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, (uint16_t*)out, ob));
   else
     RUN(c, adain_apply(c.st, B, C, N, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, out, ob));  // AdaIN.py:24-26
@@ -274,6 +308,7 @@ int cab_forward(Ctx& c, int B, int C, int N, const float* x0, const float* x1, c
 // Gradients of softmax(Q K) V wrt Q, K, V given dY; outputs position-major (B, N, d).
 int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* dYp, float* dQp,
                   float* dKp, float* dVp) {
+  NvtxRange nv("frn.attention.bwd");
   if (d <= 64 && (c.attn_eng == 1 || c.dry)) {
     const size_t m0 = c.ws.off;
     const long dn = (long)d * N;
@@ -365,6 +400,7 @@ QkvGrads take_qkv_grads(Ctx& c, int B, int N, int d) {
 // Writes the content-path gradient into dx0 and leaves dQ / dK / dV in `q`.
 int cab_backward_core(Ctx& c, int B, int C, int N, const float* x0, const frn_cab_params& p, const CabSaved& s,
                       const float* g, long gb, float* dx0, int acc0, const frn_cab_grads& gr, const QkvGrads& q) {
+  NvtxRange nv("frn.cab.bwd.core");
   const int d = C / 8;
   const long rows = (long)B * C;
   size_t mark = c.ws.off;
@@ -556,11 +592,17 @@ FusionSaved fusion_saved_layout(void* base, int B, int C, int N) {
 
 int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e,
                      const frn_refusion_params& p, float* out, const FusionSaved& s) {
+  NvtxRange nv("frn.refusion.fwd");
   FRN_TRY(conv1x1(c, p.conv0_rgb_w, p.conv0_rgb_b, a, s.R0, B, C, C, N));   // fusion.py:23
   FRN_TRY(conv1x1(c, p.conv0_evt_w, p.conv0_evt_b, e, s.E0, B, C, C, N));   // fusion.py:24
   // fusion.py:26-28 fused with the content statistics both AdaINs need (AdaIN.py:23)
-  RUN(c, gate_stats(c.st, (long)B * C, N, s.R0, s.E0, s.R1, s.E1, kEps, s.blkA.mu_x, s.blkA.sd_x,
-                    s.blkB.mu_x, s.blkB.sd_x));
+  {
+    size_t m0 = c.ws.off;
+    void* scratch = c.ws.take<char>(gate_stats_scratch_bytes((long)B * C, N));
+    RUN(c, gate_stats(c.st, (long)B * C, N, s.R0, s.E0, s.R1, s.E1, kEps, s.blkA.mu_x, s.blkA.sd_x,
+                      s.blkB.mu_x, s.blkB.sd_x, scratch));
+    c.ws.release_to(m0);
+  }
   const long ob = 2L * C * N;
   // block A = CAB(x0 = R1, x1 = E1), block B = CAB(x0 = E1, x1 = R1): R1 feeds g_A, theta_B, phi_B and E1 feeds
   // g_B, theta_A, phi_A -- one GEMM per map on the tcgen05 engine (the FFMA engine keeps the six separate ones)
@@ -573,15 +615,17 @@ int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e
     FRN_TRY(proj3(c, pb.g_w, pb.g_b, pa.theta_w, pa.theta_b, pa.phi_w, pa.phi_b, s.E1, s.blkB.Vc, s.blkA.Kc,
                   s.blkA.Qc, B, d, C, N));
   }
-  FRN_TRY(cab_forward(c, B, C, N, s.R1, s.E1, p.rgb_ca, out, ob, s.blkA, true, fuse));           // fusion.py:31
   float* out_b = c.out_bf16 ? (float*)((uint16_t*)out + (long)C * N) : out + (long)C * N;
-  FRN_TRY(cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out_b, ob, s.blkB, true, fuse));  // fusion.py:32,34
-  return FRN_OK;
+  // the two blocks are independent (fusion.py:31-32): block B runs on the side stream
+  return run_pair(c,
+      [&] { return cab_forward(c, B, C, N, s.R1, s.E1, p.rgb_ca, out, ob, s.blkA, true, fuse); },          // fusion.py:31
+      [&] { return cab_forward(c, B, C, N, s.E1, s.R1, p.event_ca, out_b, ob, s.blkB, true, fuse); });    // fusion.py:32,34
 }
 
 int refusion_backward(Ctx& c, int B, int C, int N, const float* a, const float* e,
                       const frn_refusion_params& p, const FusionSaved& s, const float* dout, float* da,
                       float* de, const frn_refusion_grads& g) {
+  NvtxRange nv("frn.refusion.bwd");
   const size_t cn = (size_t)B * C * N;
   const long ob = 2L * C * N, cnl = (long)C * N;
   float* dR1 = c.ws.take<float>(cn);
@@ -592,20 +636,129 @@ int refusion_backward(Ctx& c, int B, int C, int N, const float* a, const float* 
     const int d = C / 8;
     size_t mark = c.ws.off;
     QkvGrads qa = take_qkv_grads(c, B, N, d), qb = take_qkv_grads(c, B, N, d);
-    FRN_TRY(cab_backward_core(c, B, C, N, s.R1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, g.rgb_ca, qa));
-    FRN_TRY(cab_backward_core(c, B, C, N, s.E1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 0, g.event_ca, qb));
-    FRN_TRY(proj3_backward(c, B, C, N, s.R1, p.rgb_ca, p.event_ca, qa, qb, dR1, g.rgb_ca, g.event_ca));
-    FRN_TRY(proj3_backward(c, B, C, N, s.E1, p.event_ca, p.rgb_ca, qb, qa, dE1, g.event_ca, g.rgb_ca));
+    FRN_TRY(run_pair(c,
+        [&] { return cab_backward_core(c, B, C, N, s.R1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, g.rgb_ca, qa); },
+        [&] { return cab_backward_core(c, B, C, N, s.E1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 0, g.event_ca, qb); }));
+    FRN_TRY(run_pair(c,
+        [&] { return proj3_backward(c, B, C, N, s.R1, p.rgb_ca, p.event_ca, qa, qb, dR1, g.rgb_ca, g.event_ca); },
+        [&] { return proj3_backward(c, B, C, N, s.E1, p.event_ca, p.rgb_ca, qb, qa, dE1, g.event_ca, g.rgb_ca); }));
     c.ws.release_to(mark);
   } else {
     FRN_TRY(cab_backward(c, B, C, N, s.R1, s.E1, p.rgb_ca, s.blkA, dout, ob, dR1, 0, dE1, 0, g.rgb_ca));
     FRN_TRY(cab_backward(c, B, C, N, s.E1, s.R1, p.event_ca, s.blkB, dout + cnl, ob, dE1, 1, dR1, 1, g.event_ca));
   }
   RUN(c, gate_backward(c.st, (long)cn, s.R0, s.E0, dR1, dE1, dR1, dE1));     // fusion.py:26-28
-  FRN_TRY(conv1x1_dgrad(c, p.conv0_rgb_w, dR1, N, 1, cnl, da, B, C, C, N, 0));
-  FRN_TRY(conv1x1_dgrad(c, p.conv0_evt_w, dE1, N, 1, cnl, de, B, C, C, N, 0));
-  FRN_TRY(conv1x1_wgrad(c, dR1, N, 1, cnl, a, g.conv0_rgb_w, g.conv0_rgb_b, B, C, C, N));
-  FRN_TRY(conv1x1_wgrad(c, dE1, N, 1, cnl, e, g.conv0_evt_w, g.conv0_evt_b, B, C, C, N));
+  return run_pair(c,
+      [&] {
+        FRN_TRY(conv1x1_dgrad(c, p.conv0_rgb_w, dR1, N, 1, cnl, da, B, C, C, N, 0, 1));
+        return conv1x1_wgrad(c, dR1, N, 1, cnl, a, g.conv0_rgb_w, g.conv0_rgb_b, B, C, C, N, 1);
+      },
+      [&] {
+        FRN_TRY(conv1x1_dgrad(c, p.conv0_evt_w, dE1, N, 1, cnl, de, B, C, C, N, 0, 1));
+        return conv1x1_wgrad(c, dE1, N, 1, cnl, e, g.conv0_evt_w, g.conv0_evt_b, B, C, C, N, 1);
+      });
+}
+
+// ---- REFusion followed by the FPN lateral 1x1 conv that consumes it --------------------------
+// model.py:28,32,36,40: P{5,4,3,2}_1 = Conv2d(2C, Cout, 1) reads the concatenated (B, 2C, H, W) map right after
+// fusion.py:34 wrote it.  Each half of that map is a per-(sample, channel) affine function of R1 / E1
+// (AdaIN.py:24-26: z = sc * x + tc with sc = sd_t / sd_x, tc = mu_t - mu_x sc), so
+//   P_1(out)_b = (Wl[:, :C] diag(scA_b)) R1_b + (Wl[:, C:] diag(scB_b)) E1_b + (Wl tc_b + bl):
+// the lateral GEMM runs on the gated maps with per-sample scaled weights and the 2C map is never written or read.
+// Backward: dout = Wl^T dlat feeds the ordinary REFusion backward; dWl = sum_b [ (dlat_b X_b^T) diag(sc_b) +
+// rowsum(dlat_b) tc_b^T ] needs only the per-sample products with the SAVED gated maps, again without the 2C map.
+struct LateralScratch { float *sc, *tc, *Wlp, *biasb; };
+LateralScratch lateral_fold(Ctx& c, int B, int C, int Cout, const FusionSaved& s, const float* lat_w, const float* lat_b) {
+  LateralScratch L;
+  const int K2 = 2 * C;
+  L.sc = c.ws.take<float>((size_t)B * K2);
+  L.tc = c.ws.take<float>((size_t)B * K2);
+  L.Wlp = c.ws.take<float>((size_t)B * Cout * K2);
+  L.biasb = c.ws.take<float>((size_t)B * Cout);
+  if (!c.dry) {
+    affine_coeffs(c.st, B, C, s.blkA.mu_x, s.blkA.sd_x, s.blkA.mu_t, s.blkA.sd_t, s.blkB.mu_x, s.blkB.sd_x, s.blkB.mu_t,
+                  s.blkB.sd_t, L.sc, L.tc);
+    if (lat_w) scale_cols(c.st, B, Cout, K2, lat_w, L.sc, L.Wlp);
+  }
+  (void)lat_b;
+  return L;
+}
+
+int refusion_lateral_forward(Ctx& c, int B, int C, int N, int Cout, const float* a, const float* e,
+                             const frn_refusion_params& p, const float* lat_w, const float* lat_b, float* lat,
+                             float* out, const FusionSaved& s) {
+  c.no_apply = (out == nullptr);
+  FRN_TRY(refusion_forward(c, B, C, N, a, e, p, out, s));
+  c.no_apply = false;
+  const int K2 = 2 * C;
+  size_t mark = c.ws.off;
+  LateralScratch L = lateral_fold(c, B, C, Cout, s, lat_w, lat_b);
+  {
+    GemmDesc g = desc(lat_w, L.tc, L.biasb, Cout, B, K2, 1);       // biasb[b][o] = sum_k Wl[o][k] tc[b][k] + bl[o]
+    g.sAm = K2; g.sAk = 1;
+    g.sBk = 1; g.sBn = K2;
+    g.sCm = 1; g.sCn = Cout;
+    g.bias_m = lat_b;
+    FRN_TRY(run_gemm(c, g));
+  }
+  for (int half = 0; half < 2; half++) {
+    GemmDesc g = desc(L.Wlp + (long)half * C, half ? s.E1 : s.R1, lat, Cout, N, C, B);
+    g.sAm = K2; g.sAk = 1; g.sAb = (long)Cout * K2;
+    g.sBk = N; g.sBn = 1; g.sBb = (long)C * N;
+    g.sCm = N; g.sCn = 1; g.sCb = (long)Cout * N;
+    if (half == 0) { g.bias_m = L.biasb; g.bias_bs = Cout; }
+    g.accumulate = half;
+    FRN_TRY(run_gemm(c, g));
+  }
+  c.ws.release_to(mark);
+  return FRN_OK;
+}
+
+int refusion_lateral_backward(Ctx& c, int B, int C, int N, int Cout, const float* a, const float* e,
+                              const frn_refusion_params& p, const float* lat_w, const FusionSaved& s, const float* dlat,
+                              const float* dout_extra, float* da, float* de, const frn_refusion_grads& g,
+                              float* dlat_w, float* dlat_b) {
+  const int K2 = 2 * C;
+  const long cn = (long)C * N;
+  size_t mark = c.ws.off;
+  float* dout = c.ws.take<float>((size_t)B * K2 * N);
+  if (dout_extra) {        // another consumer of the 2C map (P6 reads C5, model.py:44) already contributed a gradient
+    if (!c.dry && cudaMemcpyAsync(dout, dout_extra, (size_t)B * K2 * N * sizeof(float), cudaMemcpyDeviceToDevice, c.st) != cudaSuccess)
+      return (int)cudaGetLastError();
+  }
+  {
+    GemmDesc d = desc(lat_w, dlat, dout, K2, N, Cout, B);          // dout_b = Wl^T dlat_b
+    d.sAm = 1; d.sAk = K2; d.sAb = 0;
+    d.sBk = N; d.sBn = 1; d.sBb = (long)Cout * N;
+    d.sCm = N; d.sCn = 1; d.sCb = (long)K2 * N;
+    d.accumulate = dout_extra ? 1 : 0;
+    d.no_lolo = 1;
+    FRN_TRY(run_gemm(c, d));
+  }
+  {
+    size_t m2 = c.ws.off;
+    LateralScratch L = lateral_fold(c, B, C, Cout, s, nullptr, nullptr);
+    float* P = c.ws.take<float>((size_t)B * Cout * K2);
+    float* S = c.ws.take<float>((size_t)B * Cout);
+    RUN(c, row_sums(c.st, B, Cout, N, dlat, S));
+    const int ktiles = cdiv(N, 32);
+    int split = cdiv(148, (long)B * cdiv(Cout, 128) * cdiv(C, 128));
+    if (split > ktiles / 4) split = ktiles / 4;
+    if (split < 1) split = 1;
+    for (int half = 0; half < 2; half++) {
+      GemmDesc w = desc(dlat, half ? s.E1 : s.R1, P + (long)half * C, Cout, C, N, B);    // P_b = dlat_b X_b^T
+      w.sAm = N; w.sAk = 1; w.sAb = (long)Cout * N;
+      w.sBk = 1; w.sBn = N; w.sBb = cn;
+      w.sCm = K2; w.sCn = 1; w.sCb = (long)Cout * K2;
+      w.reduce_batch = 1; w.per_batch_split = split;
+      w.no_lolo = 1;
+      FRN_TRY(run_gemm(c, w));
+    }
+    RUN(c, lateral_wgrad_combine(c.st, B, Cout, K2, P, S, L.sc, L.tc, dlat_w, dlat_b));
+    c.ws.release_to(m2);
+  }
+  FRN_TRY(refusion_backward(c, B, C, N, a, e, p, s, dout, da, de, g));
+  c.ws.release_to(mark);
   return FRN_OK;
 }
 
@@ -616,12 +769,13 @@ template <typename F>
 int with_ctx(void* stream, void* ws, size_t ws_bytes, F body, int attn_eng = -1) {
   Ctx dry(nullptr, nullptr, 0, true);
   FRN_TRY(body(dry));
-  size_t need = dry.ws.peak + align_up(dry.splitk_need);
+  size_t need = dry.ws.peak + 2 * align_up(dry.splitk_need);
   if (need > 0 && (!ws || ws_bytes < need)) return FRN_ERR_WORKSPACE;
   Ctx c((cudaStream_t)stream, ws, ws_bytes, false);
   if (attn_eng >= 0) c.attn_eng = attn_eng;
   if (dry.splitk_need) {
     c.splitk = c.ws.take<char>(dry.splitk_need);
+    c.splitk_alt = c.ws.take<char>(dry.splitk_need);
     c.splitk_cap = dry.splitk_need;
   }
   int rc = body(c);
@@ -632,7 +786,7 @@ template <typename F>
 size_t dry_bytes(F body) {
   Ctx dry(nullptr, nullptr, 0, true);
   if (body(dry) != FRN_OK) return 0;
-  return dry.ws.peak + align_up(dry.splitk_need) + 256;
+  return dry.ws.peak + 2 * align_up(dry.splitk_need) + 256;
 }
 
 }  // namespace
@@ -866,10 +1020,105 @@ int frn_refusion_backward(void* stream, int B, int C, int N, const float* a, con
 }
 
 // ---- REFusion, inference only (no state kept), fp32 or bf16 activations --------------------------
+// bf16 inference, fast path: padded tf32-exact maps, every large GEMM on the v2 kernel with NO staging pass
+// (see adain.cu "bf16-inference fast path").  Same arithmetic as the first path (operands rounded to nearest tf32,
+// fp32 accumulation, statistics and softmax in fp32), so the stated tolerance is unchanged.
+static bool infer_fast_enabled() {
+  static const bool on = std::getenv("FRN_INFER_V1") == nullptr;
+  return on;
+}
+static int refusion_infer_fast(Ctx& c, int B, int C, int N, const uint16_t* a, const uint16_t* e,
+                               const frn_refusion_params& p, uint16_t* out) {
+  NvtxRange nv("frn.refusion.infer_bf16");
+  const int d = C / 8, ld = (N + 3) / 4 * 4;
+  const size_t cl = (size_t)B * C * ld;
+  const long rows = (long)B * C;
+  c.fast = 1;                          // GEMMs that are not marked fast = 2 below round their operands in staging
+  float* af = c.ws.take<float>(cl);
+  float* ef = c.ws.take<float>(cl);
+  float* R0 = c.ws.take<float>(cl);
+  float* E0 = c.ws.take<float>(cl);
+  float* R1 = c.ws.take<float>(cl);
+  float* E1 = c.ws.take<float>(cl);
+  float* Wr = c.ws.take<float>((size_t)C * C);
+  float* We = c.ws.take<float>((size_t)C * C);
+  float* W3[2] = {c.ws.take<float>((size_t)3 * d * C), c.ws.take<float>((size_t)3 * d * C)};
+  float* b3[2] = {c.ws.take<float>((size_t)3 * d), c.ws.take<float>((size_t)3 * d)};
+  float* Ww[2] = {c.ws.take<float>((size_t)C * d), c.ws.take<float>((size_t)C * d)};
+  const size_t cab = cab_saved_layout(nullptr, B, C, N).bytes;
+  char* pa = c.ws.take<char>(cab);
+  char* pb = c.ws.take<char>(cab);
+  CabSaved sv[2] = {cab_saved_layout(c.dry ? nullptr : pa, B, C, N), cab_saved_layout(c.dry ? nullptr : pb, B, C, N)};
+  const frn_cab_params* cp[2] = {&p.rgb_ca, &p.event_ca};
+  RUN(c, cast_pad_bf16(c.st, rows, N, ld, a, af));
+  RUN(c, cast_pad_bf16(c.st, rows, N, ld, e, ef));
+  RUN(c, round_tf32_copy(c.st, (long)C * C, p.conv0_rgb_w, Wr));
+  RUN(c, round_tf32_copy(c.st, (long)C * C, p.conv0_evt_w, We));
+  for (int k = 0; k < 2; k++) {        // map k: R1 (k = 0) feeds g of block k and theta, phi of the other block
+    const frn_cab_params &own = *cp[k], &oth = *cp[1 - k];
+    RUN(c, stack3(c.st, (long)d * C, own.g_w, oth.theta_w, oth.phi_w, W3[k]));
+    RUN(c, round_tf32_copy(c.st, (long)3 * d * C, W3[k], W3[k]));
+    RUN(c, stack3(c.st, d, own.g_b, oth.theta_b, oth.phi_b, b3[k]));
+    RUN(c, round_tf32_copy(c.st, (long)C * d, own.W_w, Ww[k]));
+  }
+  for (int k = 0; k < 2; k++) {        // conv0 (fusion.py:23-24)
+    GemmDesc g = desc(k ? We : Wr, k ? ef : af, k ? E0 : R0, C, N, C, B);
+    g.sAm = C; g.sAk = 1;
+    g.sBk = ld; g.sBn = 1; g.sBb = (long)C * ld;
+    g.sCm = ld; g.sCn = 1; g.sCb = (long)C * ld;
+    g.bias_m = k ? p.conv0_evt_b : p.conv0_rgb_b;
+    g.fast = 2;
+    FRN_TRY(run_gemm(c, g));
+  }
+  RUN(c, gate_stats_pad(c.st, rows, N, ld, R0, E0, R1, E1, kEps, sv[0].mu_x, sv[0].sd_x, sv[1].mu_x, sv[1].sd_x));
+  for (int k = 0; k < 2; k++) {        // the three projections that read map k (Attention.py:24-27)
+    GemmDesc g = desc(W3[k], k ? E1 : R1, sv[k].Vc, 3 * d, N, C, B);
+    g.sAm = C; g.sAk = 1;
+    g.sBk = ld; g.sBn = 1; g.sBb = (long)C * ld;
+    g.sCm = N; g.sCn = 1; g.sCb = (long)d * N;
+    g.bias_m = b3[k];
+    g.C1 = sv[1 - k].Kc; g.C2 = sv[1 - k].Qc; g.group_m = d;
+    g.fast = 2;
+    FRN_TRY(run_gemm(c, g));
+  }
+  const long ob = 2L * C * N;
+  auto block = [&](int k) -> int {
+    const CabSaved& s = sv[k];
+    const float* x0 = k ? E1 : R1;
+    size_t mark = c.ws.off;
+    FRN_TRY(attention_fwd(c, B, N, d, s));                         // Attention.py:29-32
+    c.ws.release_to(mark);
+    float* scratch = c.ws.take<float>((size_t)B * d);
+    float* Yc = c.ws.take<float>((size_t)B * d * ld);
+    const int nparts = gemm_rowsumsq_parts(N);
+    float* parts = c.ws.take<float>((size_t)B * C * nparts);
+    RUN(c, row_mean_std(c.st, (long)B * d, N, s.Y, kEps, s.ybar, scratch));
+    RUN(c, center_rows_pad(c.st, (long)B * d, N, ld, s.Y, s.ybar, Yc));
+    GemmDesc g = desc(Ww[k], Yc, nullptr, C, N, d, B);             // style variance without storing W(y) (F4)
+    g.sAm = d; g.sAk = 1; g.sAb = 0;
+    g.sBk = ld; g.sBn = 1; g.sBb = (long)d * ld;
+    g.fast = 2;
+    RUN(c, gemm_rowsumsq(c.st, g, parts));
+    RUN(c, finish_style_std(c.st, rows, nparts, N, parts, kEps, s.sd_t));
+    GemmDesc m = desc(cp[k]->W_w, s.ybar, s.mu_t, C, B, d, 1);
+    m.sAm = d; m.sAk = 1;
+    m.sBk = 1; m.sBn = d;
+    m.sCm = 1; m.sCn = C;
+    m.bias_m = cp[k]->W_b;
+    FRN_TRY(run_gemm(c, m));
+    RUN(c, adain_apply_bf16_pad(c.st, B, C, N, ld, x0, s.mu_x, s.sd_x, s.mu_t, s.sd_t, out + (long)k * C * N, ob));
+    c.ws.release_to(mark);
+    return FRN_OK;
+  };
+  return run_pair(c, [&] { return block(0); }, [&] { return block(1); });
+}
+
 static int refusion_infer_body(Ctx& c, int dtype, int B, int C, int N, const void* a, const void* e,
                                const frn_refusion_params& p, void* out) {
   const size_t cn = (size_t)B * C * N;
   const float *a32 = (const float*)a, *e32 = (const float*)e;
+  if (dtype == FRN_BF16 && infer_fast_enabled())
+    return refusion_infer_fast(c, B, C, N, (const uint16_t*)a, (const uint16_t*)e, p, (uint16_t*)out);
   if (dtype == FRN_BF16) {
     // bf16 activations in and out, fp32 parameters, fp32 statistics and accumulation; every tensor-core product
     // single-pass TF32 (11 significant bits against bf16's 8)
@@ -900,6 +1149,46 @@ int frn_refusion_infer(void* stream, int dtype, int B, int C, int N, const void*
   if (dtype == FRN_BF16 && (gemm_engine() != 1 || attn_engine() != 1)) return FRN_ERR_UNSUPPORTED;
   return with_ctx(stream, ws, ws_bytes,
                   [&](Ctx& c) { return refusion_infer_body(c, dtype, B, C, N, a, e, *p, out); });
+}
+
+// ---- REFusion + FPN lateral conv (row f1) -----------------------------------------------------------
+size_t frn_refusion_lateral_workspace_bytes(int B, int C, int N, int Cout) {
+  if (!shape_ok(B, C, N) || Cout <= 0) return 0;
+  frn_refusion_params p{};
+  frn_refusion_grads g{};
+  FusionSaved s = fusion_saved_layout(nullptr, B, C, N);
+  size_t fwd = dry_bytes([&](Ctx& c) {
+    return refusion_lateral_forward(c, B, C, N, Cout, nullptr, nullptr, p, nullptr, nullptr, nullptr, nullptr, s);
+  });
+  size_t bwd = dry_bytes([&](Ctx& c) {
+    return refusion_lateral_backward(c, B, C, N, Cout, nullptr, nullptr, p, nullptr, s, nullptr, (const float*)16, nullptr,
+                                     nullptr, g, nullptr, nullptr);
+  });
+  return std::max(fwd, bwd);
+}
+int frn_refusion_lateral_forward(void* stream, int B, int C, int N, int Cout, const float* a, const float* e,
+                                 const frn_refusion_params* p, const float* lat_w, const float* lat_b, float* lat,
+                                 float* out, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N) || Cout <= 0) return FRN_ERR_BAD_SHAPE;
+  if (!a || !e || !p || !lat_w || !lat || !saved) return FRN_ERR_NULL_POINTER;
+  if (gemm_engine() != 1) return FRN_ERR_UNSUPPORTED;
+  if (saved_bytes < fusion_saved_layout(nullptr, B, C, N).bytes) return FRN_ERR_WORKSPACE;
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
+    FusionSaved s = fusion_saved_layout(c.dry ? nullptr : saved, B, C, N);
+    return refusion_lateral_forward(c, B, C, N, Cout, a, e, *p, lat_w, lat_b, lat, out, s);
+  });
+}
+int frn_refusion_lateral_backward(void* stream, int B, int C, int N, int Cout, const float* a, const float* e,
+                                  const frn_refusion_params* p, const float* lat_w, const void* saved, const float* dlat,
+                                  const float* dout_extra, float* da, float* de, const frn_refusion_grads* grads,
+                                  float* dlat_w, float* dlat_b, void* ws, size_t ws_bytes) {
+  if (!shape_ok(B, C, N) || Cout <= 0) return FRN_ERR_BAD_SHAPE;
+  if (!a || !e || !p || !lat_w || !saved || !dlat || !da || !de || !grads || !dlat_w) return FRN_ERR_NULL_POINTER;
+  if (gemm_engine() != 1) return FRN_ERR_UNSUPPORTED;
+  FusionSaved s = fusion_saved_layout(const_cast<void*>(saved), B, C, N);
+  return with_ctx(stream, ws, ws_bytes, [&](Ctx& c) {
+    return refusion_lateral_backward(c, B, C, N, Cout, a, e, *p, lat_w, s, dlat, dout_extra, da, de, *grads, dlat_w, dlat_b);
+  });
 }
 
 // ---- 1x1 convolution (FPN laterals, model.py:28-40) ---------------------------------

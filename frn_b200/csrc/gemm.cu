@@ -12,6 +12,7 @@
 
 namespace frn {
 
+#ifdef FRN_DEBUG_ENGINES      // the FFMA engine: scaffolding of round 1, kept for A/B comparisons in debug builds only
 namespace {
 
 template <int BM, int BN, int BK, int TM, int TN, int EPI>
@@ -216,6 +217,7 @@ sgemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_spli
 }
 
 }  // namespace
+#endif  // FRN_DEBUG_ENGINES
 // C[m][n] (+)= sum_z part[z][m][n]
 __global__ void splitk_reduce_kernel(const float* __restrict__ part, int nsplit, int M, int N,
                                      float* __restrict__ C, long sCm, long sCn, int accumulate) {
@@ -230,6 +232,7 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, int nsplit,
   }
 }
 
+#ifdef FRN_DEBUG_ENGINES
 namespace {
 struct Plan { int bm, bn, ktiles, nsplit, tiles_per_split; };
 constexpr int kBK = 16;
@@ -301,8 +304,14 @@ int ffma_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes) {
   return launch<GEMM_EPI_STORE>(st, d, pl, nullptr);
 }
 
+#else
+size_t ffma_gemm_workspace_bytes(const GemmDesc&) { return 0; }
+int ffma_gemm(cudaStream_t, const GemmDesc&, void*, size_t) { return FRN_ERR_UNSUPPORTED; }
+#endif  // FRN_DEBUG_ENGINES
+
 int gemm_rowsumsq_parts(int N) { return cdiv(N, 128); }
 
+#ifdef FRN_DEBUG_ENGINES
 int ffma_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
   if (d.M <= 0 || d.N <= 0 || d.K <= 0 || d.batch <= 0 || d.reduce_batch) return FRN_ERR_BAD_SHAPE;
   Plan pl = make_plan(d);
@@ -310,11 +319,18 @@ int ffma_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial) {
   return launch<GEMM_EPI_ROWSUMSQ>(st, d, pl, out_partial);
 }
 
+#else
+int ffma_gemm_rowsumsq(cudaStream_t, const GemmDesc&, float*) { return FRN_ERR_UNSUPPORTED; }
+#endif
+
 // ---- engine dispatch ---------------------------------------------------------------
 namespace {
 std::atomic<int> g_engine{-1};
 }
 int gemm_engine() {
+#ifndef FRN_DEBUG_ENGINES
+  return 1;        // product build: tcgen05 only
+#endif
   int e = g_engine.load(std::memory_order_relaxed);
   if (e < 0) {
     const char* s = getenv("FRN_GEMM_ENGINE");
@@ -329,6 +345,9 @@ namespace {
 std::atomic<int> g_attn_engine{-1};
 }
 int attn_engine() {
+#ifndef FRN_DEBUG_ENGINES
+  return 1;
+#endif
   int e = g_attn_engine.load(std::memory_order_relaxed);
   if (e < 0) {
     const char* s = getenv("FRN_ATTN_ENGINE");

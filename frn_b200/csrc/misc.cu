@@ -11,6 +11,7 @@
 #include <string>
 #include <utility>
 #include <vector>
+#include <nvtx3/nvToolsExt.h>
 #include "common.cuh"
 
 namespace frn {
@@ -64,10 +65,19 @@ __global__ void __launch_bounds__(256) row_sum_kernel(int M, int N, const float*
   float s = 0.f;
   if ((N & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
     const float4* p4 = reinterpret_cast<const float4*>(p);
-    for (int n = threadIdx.x; n < N / 4; n += blockDim.x) {
+    const int n4 = N / 4, step = blockDim.x;
+    float s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int n = threadIdx.x;
+    for (; n + 3 * step < n4; n += 4 * step) {        // four independent loads in flight per thread
+      const float4 v0 = __ldg(p4 + n), v1 = __ldg(p4 + n + step), v2 = __ldg(p4 + n + 2 * step), v3 = __ldg(p4 + n + 3 * step);
+      s += (v0.x + v0.y) + (v0.z + v0.w); s1 += (v1.x + v1.y) + (v1.z + v1.w);
+      s2 += (v2.x + v2.y) + (v2.z + v2.w); s3 += (v3.x + v3.y) + (v3.z + v3.w);
+    }
+    for (; n < n4; n += step) {
       float4 v = __ldg(p4 + n);
       s += (v.x + v.y) + (v.z + v.w);
     }
+    s = (s + s1) + (s2 + s3);
   } else {
     for (int n = threadIdx.x; n < N; n += blockDim.x) s += __ldg(p + n);
   }
@@ -330,7 +340,8 @@ KernelTimer::~KernelTimer() {
 }
 
 // "name | launches | ms | bytes | launches_large | ms_large | bytes_large" per kernel; large = launches whose
-// algorithmic bytes exceed the 126 MB L2 (those are the ones an HBM roofline fraction is meaningful for).
+// algorithmic bytes are at least twice the 126 MB L2 (those are the ones an HBM roofline fraction is meaningful for,
+// and long enough that the two event records around a launch do not distort the time).
 long kernel_log_dump(char* buf, long cap) {
   std::vector<KernelRec> ev;
   {
@@ -347,7 +358,7 @@ long kernel_log_dump(char* buf, long cap) {
     cudaEventDestroy(r.e1);
     Agg& a = agg[r.name];
     a.n++; a.ms += t; a.bytes += r.bytes;
-    if (r.bytes > 126e6) { a.nl++; a.msl += t; a.bytesl += r.bytes; }
+    if (r.bytes > 250e6) { a.nl++; a.msl += t; a.bytesl += r.bytes; }
   }
   std::string out;
   char line[256];
@@ -388,6 +399,9 @@ ShapeTimer::~ShapeTimer() {
   std::lock_guard<std::mutex> lk(g_timing_mu);
   g_shape_log.push_back({key, e0, e1});
 }
+
+NvtxRange::NvtxRange(const char* name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
 
 int set_smem_once(const void* kern, int bytes) {
   static std::mutex mu;
@@ -650,6 +664,76 @@ int cast_bf16_to_f32(cudaStream_t st, size_t count, const uint16_t* src, float* 
 
 int scale_sum_batch(cudaStream_t st, int B, int C, const float* alpha, float scale, float* out) {
   scale_sum_batch_kernel<<<cdiv(C, 256), 256, 0, st>>>(B, C, alpha, scale, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+
+// ---- REFusion + FPN lateral (row f1): the AdaIN affine folded into the lateral weights -------------------------------
+// z[b][c][n] = sc[b][c] * x[b][c][n] + tc[b][c] with sc = sd_t / sd_x, tc = mu_t - mu_x * sc (AdaIN.py:24-26); the two
+// blocks' coefficients side by side: columns [0, C) from block A, [C, 2C) from block B.
+__global__ void affine_coeffs_kernel(int B, int C, const float* __restrict__ mxa, const float* __restrict__ sxa,
+                                     const float* __restrict__ mta, const float* __restrict__ sta,
+                                     const float* __restrict__ mxb, const float* __restrict__ sxb,
+                                     const float* __restrict__ mtb, const float* __restrict__ stb,
+                                     float* __restrict__ sc, float* __restrict__ tc) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C) return;
+  const int b = i / C, ch = i - b * C;
+  const float sa = sta[i] / sxa[i], sb = stb[i] / sxb[i];
+  sc[(long)b * 2 * C + ch] = sa;      tc[(long)b * 2 * C + ch] = mta[i] - mxa[i] * sa;
+  sc[(long)b * 2 * C + C + ch] = sb;  tc[(long)b * 2 * C + C + ch] = mtb[i] - mxb[i] * sb;
+}
+int affine_coeffs(cudaStream_t st, int B, int C, const float* mxa, const float* sxa, const float* mta, const float* sta,
+                  const float* mxb, const float* sxb, const float* mtb, const float* stb, float* sc, float* tc) {
+  affine_coeffs_kernel<<<cdiv((long)B * C, 256), 256, 0, st>>>(B, C, mxa, sxa, mta, sta, mxb, sxb, mtb, stb, sc, tc);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+// out[b][o][k] = w[o][k] * sc[b][k]
+__global__ void scale_cols_kernel(long total, int M, int K, const float* __restrict__ w, const float* __restrict__ sc,
+                                  float* __restrict__ out) {
+  const long stride = (long)gridDim.x * blockDim.x, mk = (long)M * K;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long b = i / mk, r = i - b * mk;
+    out[i] = w[r] * sc[b * K + r % K];
+  }
+}
+int scale_cols(cudaStream_t st, int B, int M, int K, const float* w, const float* sc, float* out) {
+  const long total = (long)B * M * K;
+  scale_cols_kernel<<<grid_for(total), 256, 0, st>>>(total, M, K, w, sc, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+// out[b * M + m] = sum_n x[b][m][n]   (x contiguous (B, M, N))
+int row_sums(cudaStream_t st, int B, int M, int N, const float* x, float* out) {
+  ScopedTimer tm(st, FRN_TIME_ROWS);
+  KernelTimer kt(st, "row_sum_kernel", 4.0 * B * N * M);
+  row_sum_kernel<<<dim3(M, B), 256, 0, st>>>(M, N, x, (long)M * N, N, out);
+  FRN_LAUNCH_CHECK();
+  return FRN_OK;
+}
+// dW[o][k] = sum_b sc[b][k] P[b][o][k] + tc[b][k] S[b][o];  db[o] = sum_b S[b][o]
+__global__ void lateral_wgrad_combine_kernel(int B, int M, int K, const float* __restrict__ P,
+                                             const float* __restrict__ S, const float* __restrict__ sc,
+                                             const float* __restrict__ tc, float* __restrict__ dW,
+                                             float* __restrict__ db) {
+  const long total = (long)M * K, stride = (long)gridDim.x * blockDim.x;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int o = (int)(i / K), k = (int)(i - (long)o * K);
+    float acc = 0.f;
+    for (int b = 0; b < B; b++)
+      acc += sc[(long)b * K + k] * P[(long)b * total + i] + tc[(long)b * K + k] * S[(long)b * M + o];
+    dW[i] = acc;
+    if (k == 0 && db) {
+      float t = 0.f;
+      for (int b = 0; b < B; b++) t += S[(long)b * M + o];
+      db[o] = t;
+    }
+  }
+}
+int lateral_wgrad_combine(cudaStream_t st, int B, int M, int K, const float* P, const float* S, const float* sc,
+                          const float* tc, float* dW, float* db) {
+  lateral_wgrad_combine_kernel<<<grid_for((long)M * K), 256, 0, st>>>(B, M, K, P, S, sc, tc, dW, db);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }

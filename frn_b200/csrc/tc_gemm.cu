@@ -586,11 +586,8 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
 // 18 warps: 0 = TMA producer (one lane), 1 = MMA issue, 2-9 = lo split, 10-17 = accumulator drain + epilogue.
 constexpr int kV2Threads = 18 * 32;
 constexpr int kV2SplitWarp0 = 2, kV2EpiWarp0 = 10;
-// Accumulation chain of the v2 kernel: 2 stages (K = 64).  Its two N = 2 BN instructions per K slice put two
-// truncating additions per slice into every accumulator column (the first kernel: one into the main accumulator), so
-// the chain is half as long to keep the truncation bias per chain where it was (tools/tc_error_vs_k.py; the phi
-// weight gradient of the materialised attention at DSEC level 3 is the canary: 1.03e-5 with 4-stage chains).
-constexpr int kChunk2 = 2;
+// Accumulation chain of the v2 kernel, in stages (K = 128), as in the first kernel.
+constexpr int kChunk2 = 4;
 
 template <int BN> struct Tc2Cfg {
   static constexpr int kStages = BN == 128 ? 3 : 4;
@@ -687,11 +684,13 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     }
   } else if (warp == 1) {
     // ===== MMA issue =====
-    // [b_hi | b_lo] are adjacent in shared memory (both majors), so ONE instruction with N = 2 BN multiplies an A
-    // slice with both: a_hi.[b_hi | b_lo] and a_lo.[b_hi | b_lo] land in the column halves [hh + lh | hl + ll] of the
-    // accumulator buffer.  Two instructions per K slice instead of four: the same tensor time (N / 2 cycles each) but
-    // the A slice crosses the shared-memory port twice instead of four times -- the kernel is bound by that port
-    // (operand fetch + split traffic + TMA writes share 128 B/clk), not by the math.
+    // [b_hi | b_lo] are adjacent in shared memory (both majors), so ONE instruction with N = 2 BN forms
+    // a_hi.[b_hi | b_lo] = [hh | hl] in the column halves [main | small] of the accumulator buffer; a_lo.b_hi and
+    // a_lo.b_lo follow as two N = BN instructions into the small half.  Same tensor time as four N = BN instructions
+    // (N / 2 cycles each), but the a_hi slice crosses the shared-memory port once instead of twice, and the main
+    // accumulator still receives ONE truncating addition per K slice (with a_lo.[b_hi | b_lo] as a second N = 2 BN
+    // instruction it received two, and the phi weight gradient of the materialised attention at DSEC level 3 -- the
+    // canary for truncation bias -- went from under the 1e-5 gate to 1.03e-5).
     const uint32_t majors = ((uint32_t)g.a_mn << 15) | ((uint32_t)g.b_mn << 16);
     const uint32_t idesc2 = umma_idesc_tf32(TBM, 2 * BN) | majors, idesc1 = umma_idesc_tf32(TBM, BN) | majors;
     long it = 0;
@@ -728,8 +727,11 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
             const uint64_t b_both = g.b_mn ? umma_desc(sB + ob, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sB + ob);
             const bool acc = !(first && k == 0);
             if (!p.fast) {
-              umma_tf32_ss(d_acc, a_lo, b_both, idesc2, acc);
-              umma_tf32_ss(d_acc, a_hi, b_both, idesc2, true);
+              const uint64_t b_lo = g.b_mn ? umma_desc(sB + Cfg::kBBytes + ob, 4096, g.mn_sbo, g.mn_layout)
+                                           : umma_desc_sw128(sB + Cfg::kBBytes + ob);
+              umma_tf32_ss(d_acc, a_hi, b_both, idesc2, acc);                  // [hh | hl]
+              umma_tf32_ss(d_acc + BN, a_lo, b_both, idesc1, true);            // lh (b_both starts at b_hi)
+              if (!p.no_lolo) umma_tf32_ss(d_acc + BN, a_lo, b_lo, idesc1, true);   // ll
             } else {
               umma_tf32_ss(d_acc, a_hi, b_both, idesc1, acc);
             }
@@ -967,9 +969,10 @@ int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
   memset(&tmA, 0, sizeof tmA);
   memset(&tmB, 0, sizeof tmB);
   const bool a_mn = d.sAk != 1, b_mn = d.sBk != 1;
-  // single-pass mode (bf16-tolerance inference) stays on the first kernel: its staging ROUNDS the operands to tf32,
-  // raw operands would be truncated (2 x the error, and biased)
-  if (env.tma && env.v2 && !d.fast && (env.v2 == 2 || (!a_mn && !b_mn)) &&
+  // single-pass mode with arbitrary fp32 operands (fast == 1) stays on the first kernel: its staging ROUNDS the
+  // operands to tf32, raw operands would be truncated (2 x the error, and biased).  fast == 2: the caller guarantees
+  // tf32-exact operands, so the raw tiles go straight to the tensor core.
+  if (env.tma && env.v2 && d.fast != 1 && (env.v2 == 2 || (!a_mn && !b_mn)) &&
       make_operand_map_v2(&tmA, d.A, d.M, d.K, d.batch, d.sAm, d.sAk, d.sAb, TBM, env.mn_swizzle) &&
       make_operand_map_v2(&tmB, d.B, d.N, d.K, d.batch, d.sBn, d.sBk, d.sBb, BN, env.mn_swizzle)) {
     using Cfg2 = Tc2Cfg<BN>;

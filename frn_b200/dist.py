@@ -72,6 +72,40 @@ class GradBucket:
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=async_op)
 
 
+class LevelBuckets:
+    """One GradBucket per REFusion module (FPN level): 0.79 / 3.2 / 12.6 / 50.4 MB at the four DSEC levels
+    (SURVEY.md 8.2 e).  ``allreduce_level(k)`` is called right after level k's backward has been enqueued -- on the
+    stream that ran it -- with ``async_op=True``: NCCL orders the collective after that stream's work and runs it on its
+    own stream, so the reduction of one level's gradients overlaps the backward of the levels still running.
+    ``wait()`` makes the current stream wait for all of them.  Every rank must call the levels in the same order."""
+
+    def __init__(self, modules):
+        self.buckets = [GradBucket(list(m.parameters())) for m in modules]
+        self._pending = []
+
+    @property
+    def numel(self):
+        return sum(b.flat.numel() for b in self.buckets)
+
+    def zero(self):
+        for b in self.buckets:
+            b.zero()
+
+    def allreduce_level(self, k: int, average: bool = True):
+        work = self.buckets[k].allreduce(average=average, async_op=True)
+        if work is not None:
+            self._pending.append(work)
+        return work
+
+    def wait(self):
+        for w in self._pending:
+            w.wait()
+        self._pending = []
+
+    def grad_norm(self):
+        return torch.linalg.vector_norm(torch.stack([torch.linalg.vector_norm(b.flat) for b in self.buckets]))
+
+
 def allreduce_fusion_grads(params, average: bool = True):
     """One-shot allreduce of the given parameters' gradients (packs, reduces, unpacks).
     For the zero-copy path build a GradBucket once and reuse it."""

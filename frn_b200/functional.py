@@ -290,6 +290,79 @@ def refusion(rgb, evt, conv0, rgb_ca, event_ca):
     return _to_autocast(_REFusionFn.apply(wants_grad, rgb, evt, *params))
 
 
+# --------------------------------------------------------------------------- REFusion + lateral conv (row f1)
+class _REFusionLateralFn(torch.autograd.Function):
+    """P_1(REFusion(rgb, evt)) without writing the (B, 2C, H, W) map (include/frn_b200.h, frn_refusion_lateral_*).
+    params: lateral (w, b), then the 20 REFusion tensors in _REFusionFn order.  return_map: also return the map."""
+
+    @staticmethod
+    @_custom_fwd
+    def forward(ctx, return_map, rgb, evt, lat_w, lat_b, *params):
+        _check_cuda(rgb, evt, lat_w, *params)
+        lib = _lib.load()
+        b, c, h, w = rgb.shape
+        n, cout = h * w, lat_w.shape[0]
+        a, e = _f32c(rgb), _f32c(evt)
+        lw = _f32c(lat_w).view(cout, 2 * c)
+        lb = _f32c(lat_b) if lat_b is not None else None
+        prm = [_f32c(p) for p in params]
+        lat = torch.empty((b, cout, h, w), dtype=torch.float32, device=a.device)
+        out = torch.empty((b, 2 * c, h, w), dtype=torch.float32, device=a.device) if return_map else None
+        with torch.cuda.device(a.device):
+            ws_bytes = lib.frn_refusion_lateral_workspace_bytes(b, c, n, cout)
+            ws = _bytes(ws_bytes, a.device)
+            saved_bytes = lib.frn_refusion_saved_bytes(b, c, n)
+            saved = _bytes(saved_bytes, a.device)
+            st = _fusion_struct(prm[0:4], prm[4:12], prm[12:20])
+            _lib.check(lib.frn_refusion_lateral_forward(
+                _stream(), b, c, n, cout, _ptr(a), _ptr(e), C.byref(st), _ptr(lw), _ptr(lb) if lb is not None else None,
+                _ptr(lat), _ptr(out) if out is not None else None, _ptr(saved), saved_bytes, _ptr(ws), ws_bytes),
+                "refusion_lateral_forward")
+        ctx.save_for_backward(a, e, saved, lw, *prm)
+        ctx.dims = (b, c, n, cout)
+        ctx.has_bias = lb is not None
+        ctx.lat_w_shape = tuple(lat_w.shape)
+        ctx.in_dtypes = (rgb.dtype, evt.dtype, lat_w.dtype, lat_b.dtype if lat_b is not None else None) + \
+            tuple(p.dtype for p in params)
+        if return_map:
+            return lat.to(rgb.dtype), out.to(rgb.dtype)
+        return lat.to(rgb.dtype)
+
+    @staticmethod
+    @_custom_bwd
+    def backward(ctx, dlat, dout=None):
+        lib = _lib.load()
+        a, e, saved, lw, *prm = ctx.saved_tensors
+        b, c, n, cout = ctx.dims
+        g = _f32c(dlat)
+        gx = _f32c(dout) if dout is not None else None
+        da, de = torch.empty_like(a), torch.empty_like(e)
+        grads = [torch.empty_like(p) for p in prm]
+        dlw = torch.empty_like(lw)
+        dlb = torch.empty(cout, dtype=torch.float32, device=a.device) if ctx.has_bias else None
+        with torch.cuda.device(a.device):
+            ws_bytes = lib.frn_refusion_lateral_workspace_bytes(b, c, n, cout)
+            ws = _bytes(ws_bytes, a.device)
+            st = _fusion_struct(prm[0:4], prm[4:12], prm[12:20])
+            gst = _fusion_struct(grads[0:4], grads[4:12], grads[12:20])
+            _lib.check(lib.frn_refusion_lateral_backward(
+                _stream(), b, c, n, cout, _ptr(a), _ptr(e), C.byref(st), _ptr(lw), _ptr(saved), _ptr(g),
+                _ptr(gx) if gx is not None else None, _ptr(da), _ptr(de), C.byref(gst), _ptr(dlw),
+                _ptr(dlb) if dlb is not None else None, _ptr(ws), ws_bytes), "refusion_lateral_backward")
+        dts = ctx.in_dtypes
+        return (None, da.to(dts[0]), de.to(dts[1]), dlw.view(ctx.lat_w_shape).to(dts[2]),
+                dlb.to(dts[3]) if dlb is not None else None) + tuple(gr.to(dt) for gr, dt in zip(grads, dts[4:]))
+
+
+def refusion_lateral(rgb, evt, lat_w, lat_b, conv0, rgb_ca, event_ca, return_map=False):
+    """P_1(REFusion(rgb, evt)) for the lateral conv P_1 = (lat_w (Cout, 2C, 1, 1), lat_b) of model.py:28-40 with the
+    AdaIN affine folded into the lateral weights; return_map=True also returns the (B, 2C, H, W) map."""
+    res = _REFusionLateralFn.apply(bool(return_map), rgb, evt, lat_w, lat_b, *conv0, *rgb_ca, *event_ca)
+    if return_map:
+        return _to_autocast(res[0]), _to_autocast(res[1])
+    return _to_autocast(res)
+
+
 # --------------------------------------------------------------------------- 1x1 conv (FPN laterals, row f1)
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod

@@ -107,6 +107,32 @@ class Conv1x1(nn.Conv2d):
         return F.conv1x1(x, self.weight, self.bias)
 
 
+class REFusionLateral(nn.Module):
+    """One FPN level's REFusion together with the lateral 1x1 conv that consumes its output (model.py:305-308 followed
+    by P{5,4,3,2}_1 at model.py:59-76): forward(rgb, evt) == lateral(fusion(rgb, evt)), computed
+    without writing or re-reading the (B, 2C, H, W) map -- the AdaIN affine is folded into per-sample scaled lateral
+    weights and the GEMM reads the gated maps.  `fusion` and `lateral` are the model's own modules (parameters and
+    state-dict keys shared, nothing copied).  return_map=True also returns the 2C map (level 4: P6 reads C5 too,
+    model.py:44)."""
+
+    def __init__(self, fusion: REFusion, lateral: nn.Conv2d, return_map: bool = False):
+        super().__init__()
+        if lateral.kernel_size != (1, 1) or lateral.stride != (1, 1) or lateral.padding != (0, 0) or lateral.groups != 1:
+            raise ValueError("REFusionLateral: the lateral must be a dense 1x1 stride-1 unpadded convolution")
+        if lateral.in_channels != 2 * fusion.out_planes:
+            raise ValueError("REFusionLateral: lateral.in_channels must be 2 * fusion.out_planes")
+        self.fusion, self.lateral, self.return_map = fusion, lateral, return_map
+
+    def forward(self, rgb, evt):
+        assert len(rgb.size()) == 4
+        assert rgb.size() == evt.size()
+        f = self.fusion
+        conv0 = (*_conv_params(f.conv0_rgb), *_conv_params(f.conv0_evt))
+        return F.refusion_lateral(rgb, evt, self.lateral.weight, self.lateral.bias, conv0,
+                                  f.rgb_cross_attention.kernel_params(), f.event_cross_attention.kernel_params(),
+                                  self.return_map)
+
+
 def convert_fpn_laterals(model: nn.Module):
     """Replace the lateral 1x1 convs (attributes P5_1, P4_1, P3_1, P2_1 of a PyramidFeatures-like module,
     model.py:28-40) by Conv1x1 sharing the same Parameter objects.  Returns the rebound names."""

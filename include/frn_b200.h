@@ -15,9 +15,16 @@
  *   - Every pointer is a DEVICE pointer on the current CUDA device unless the
  *     parameter is documented otherwise.  Feature maps are NCHW-contiguous
  *     (the layout retinanet/model.py:305-308 hands over), N = H*W.
- *   - `stream` is a cudaStream_t passed as void*.  Calls only enqueue work;
- *     they never synchronise, never allocate, and keep no global mutable
- *     state (re-entrant: nn.DataParallel calls one thread per device).
+ *   - `stream` is a cudaStream_t passed as void*.  Calls only enqueue work; they never synchronise and never
+ *     allocate device memory, so they may be captured into a CUDA graph.  Re-entrant: nn.DataParallel calls one
+ *     thread per device, and concurrent callers on different streams never share anything.  What the library keeps
+ *     between calls, all of it created lazily, guarded by a mutex and never freed: (1) per (device, caller stream)
+ *     the side streams and fork / join events on which independent halves of a call run (block A / block B of
+ *     REFusion, dQ / dK,dV of the attention backward) -- they always rejoin the caller's stream before the call
+ *     returns; (2) the set of kernels whose shared-memory limit has been raised; (3) switches read ONCE from the
+ *     environment at first use (FRN_GEMM_TMA, FRN_GEMM_V2, FRN_NO_PROJ3, FRN_NO_F4, FRN_NO_FORK, FRN_INFER_V1: debug
+ *     and comparison only); (4) the launch counter and, when enabled, the measurement hooks at the end of this file.
+ *     The engine switches (frn_set_*_engine) only have an effect in a -DFRN_DEBUG_ENGINES build.
  *   - The caller owns every buffer, including `saved` (forward state kept for
  *     backward) and `ws` (scratch, free to reuse after the call's work is
  *     complete on `stream`).  Sizes come from the *_bytes() queries.
@@ -208,6 +215,23 @@ int frn_conv1x1_forward(void* stream, int B, int Cin, int Cout, int N, const flo
 int frn_conv1x1_backward(void* stream, int B, int Cin, int Cout, int N, const float* x, const float* w,
                          const float* dy, float* dx, float* dw, float* db, void* ws, size_t ws_bytes);
 
+/* ---- REFusion fused with the lateral conv that consumes it --------------------------------
+ * lat (B, Cout, N) = P_1(REFusion(a, e)) with P_1 = nn.Conv2d(2C, Cout, 1) of retinanet/model.py:28,32,36,40
+ * (lat_w (Cout, 2C), lat_b (Cout) or NULL) applied to the concatenated map of fusion.py:34.  The AdaIN affine that
+ * produces each half of that map is folded into per-sample scaled lateral weights, so the GEMM reads the gated maps
+ * directly and the (B, 2C, N) map is neither written nor read; pass out != NULL to have it written as well (level 4:
+ * P6 also reads C5, model.py:44).  saved (frn_refusion_saved_bytes) is required.
+ * backward: dlat (B, Cout, N); dout_extra (B, 2C, N) or NULL = gradient that reached the 2C map from another
+ * consumer; da, de, grads as frn_refusion_backward; dlat_w (Cout, 2C) and dlat_b (Cout, may be NULL) overwritten. */
+size_t frn_refusion_lateral_workspace_bytes(int B, int C, int N, int Cout);
+int frn_refusion_lateral_forward(void* stream, int B, int C, int N, int Cout, const float* a, const float* e,
+                                 const frn_refusion_params* p, const float* lat_w, const float* lat_b, float* lat,
+                                 float* out, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes);
+int frn_refusion_lateral_backward(void* stream, int B, int C, int N, int Cout, const float* a, const float* e,
+                                  const frn_refusion_params* p, const float* lat_w, const void* saved, const float* dlat,
+                                  const float* dout_extra, float* da, float* de, const frn_refusion_grads* grads,
+                                  float* dlat_w, float* dlat_b, void* ws, size_t ws_bytes);
+
 /* ---- anchors + focal loss ----------------------------------------------------
  * frn_anchors_generate replaces Anchors.forward (retinanet/anchors.py:25-45, generate_anchors :47-82, shift
  * :120-147): all boxes of an H x W image over the pyramid levels, (1, A, 4) fp32 (x1, y1, x2, y2), cells
@@ -285,7 +309,7 @@ void frn_timing_enable(int on);
 int frn_timing_read(int cls, double* ms, long* launches);
 /* Per-kernel record of the HBM-bound kernels since the last call (hooks on): one text line per kernel,
  * "name | launches | ms | algorithmic bytes | launches_large | ms_large | bytes_large", where "large" restricts the
- * sums to launches whose algorithmic bytes exceed the 126 MB L2.  Algorithmic = each input element read once, each
+ * sums to launches whose algorithmic bytes exceed 250 MB (twice the L2).  Algorithmic = each input element read once, each
  * output element written once.  Returns the length of the full text; at most cap - 1 characters are copied. */
 long frn_timing_kernels(char* buf, long cap);
 

@@ -98,3 +98,15 @@ def check_against(name, got, ref, tol=RTOL_F32):
     bad = {k: v for k, v in errs.items() if not (v <= tol)}
     assert not bad, f"{name}: over tolerance {tol}: {bad}\nall: {errs}"
     return errs
+
+
+def debug_engines_available():
+    """True when the library was built with -DFRN_DEBUG_ENGINES (make DEBUG_ENGINES=1): the FFMA engines of round 1
+    are then selectable through frn_set_*_engine.  The product build is tcgen05-only and ignores the switches."""
+    from frn_b200 import _lib
+    lib = _lib.load()
+    old = lib.frn_get_gemm_engine()
+    lib.frn_set_gemm_engine(0)
+    ok = lib.frn_get_gemm_engine() == 0
+    lib.frn_set_gemm_engine(old)
+    return ok

@@ -5,7 +5,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from frn_b200.dist import GradBucket, allreduce_fusion_grads, shard_batch
+from frn_b200.dist import GradBucket, LevelBuckets, allreduce_fusion_grads, shard_batch
 
 
 def test_shard_batch_covers_everything():
@@ -56,6 +56,16 @@ def _worker(rank, world, port, q):
     bucket.allreduce(average=False)
     ok = ok and torch.allclose(params[0].grad, torch.full_like(params[0], 3.0))
     ok = ok and all(float(p.grad.abs().max()) == 0.0 for p in params[1:])
+    # per-level buckets issued asynchronously in a fixed level order (bench.py / SURVEY.md 8.2 e)
+    mods = [frn_b200.REFusion(8, 8), frn_b200.REFusion(16, 16)]
+    lb = LevelBuckets(mods)
+    for k, mod in enumerate(mods):
+        for i, p in enumerate(mod.parameters()):
+            p.grad.fill_(float(rank + 1) * (k + 1))
+        lb.allreduce_level(k, average=True)
+    lb.wait()
+    ok = ok and all(torch.allclose(p.grad, torch.full_like(p, 1.5 * (k + 1))) for k, mod in enumerate(mods) for p in mod.parameters())
+    ok = ok and lb.numel == sum(p.numel() for mod in mods for p in mod.parameters())
     q.put((rank, bool(ok)))
     dist.destroy_process_group()
 

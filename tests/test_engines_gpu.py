@@ -8,7 +8,8 @@ import torch
 
 import frn_b200
 from frn_b200 import _lib
-from helpers import check_against, golden_files, load_golden, load_into, make_inputs, make_params, run_module
+from helpers import (check_against, debug_engines_available, golden_files, load_golden, load_into, make_inputs,
+                     make_params, run_module)
 from oracle import fusion_numpy as onp
 
 pytestmark = pytest.mark.gpu
@@ -18,6 +19,8 @@ ENGINES = [(1, 0), (0, 1), (1, 1)]          # (attention, gemm): 1 = tcgen05
 
 @pytest.fixture(params=ENGINES, ids=["attn_tc", "gemm_tc", "both_tc"])
 def engines(request):
+    if request.param != (1, 1) and not debug_engines_available():
+        pytest.skip("FFMA engines are compiled into -DFRN_DEBUG_ENGINES builds only (make DEBUG_ENGINES=1)")
     lib = _lib.load()
     old = lib.frn_get_attn_engine(), lib.frn_get_gemm_engine()
     lib.frn_set_attn_engine(request.param[0])

@@ -9,6 +9,7 @@ import pytest
 import torch
 
 from frn_b200 import _lib
+from helpers import debug_engines_available
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -74,6 +75,8 @@ def make(layout, rows, cols, batch, g):
 @pytest.mark.parametrize("engine", [0, 1], ids=["ffma", "tcgen05"])
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_gemm_orientations(engine, case):
+    if engine == 0 and not debug_engines_available():
+        pytest.skip("FFMA engine: -DFRN_DEBUG_ENGINES builds only")
     name, batch, M, N, K, la, lb, lc = case
     g = torch.Generator().manual_seed(hash(name) % 1000)
     A, sA, Av = make("mk" if la == "mk" else "T", M, K, batch, g)
@@ -100,6 +103,8 @@ def test_gemm_orientations(engine, case):
                          ids=str)
 def test_gemm_wgrad_reduce_batch(engine, shape):
     """dW (M, K') = sum_b dy_b (M, n) x_b^T (n, K'): contraction over (batch, n), deterministic split-K."""
+    if engine == 0 and not debug_engines_available():
+        pytest.skip("FFMA engine: -DFRN_DEBUG_ENGINES builds only")
     batch, M, Kp, n = shape
     g = torch.Generator().manual_seed(n)
     dy = torch.randn(batch, M, n, generator=g).to(DEV)

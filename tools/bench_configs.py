@@ -82,6 +82,27 @@ def run(name, levels, B, dtype, train, steps, warmup, peaks):
     n0 = lib.frn_launch_count()
     ms = timed(step_resident, steps)
     launches = lib.frn_launch_count() - n0
+    # the same step replayed from ONE captured CUDA graph (the library only enqueues: no allocation, no
+    # synchronisation, side streams fork from / join into the capturing stream), i.e. without the ~1300 - 4600 launch
+    # calls per step that bound these small shapes
+    ms_graph, graph_err = None, None
+    try:
+        static_in = [(a.clone(), e.clone()) for a, e in devin]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                step(static_in)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            step(static_in)
+        graph.replay()
+        ms_graph = timed(graph.replay, steps)
+    except Exception as ex:      # reported, not hidden
+        graph_err = f"{type(ex).__name__}: {ex}"[:200]
+        torch.cuda.synchronize()
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, steps)
@@ -97,6 +118,8 @@ def run(name, levels, B, dtype, train, steps, warmup, peaks):
         "value": sps, "unit": "samples/s", "ms_per_step": ms, "steps": steps, "warmup": max(warmup, 3),
         "dtype": "bf16 I/O, single-pass tf32 products, fp32 accumulation" if esz == 2 else "f32 (split tf32)",
         "levels": [[B, c, h, w] for c, h, w in levels], "gpu_launches": int(launches),
+        "cuda_graph": ({"value": B / (ms_graph / 1e3), "unit": "samples/s", "ms_per_step": ms_graph}
+                       if ms_graph else {"failed": graph_err}),
         "e2e": {"value": B / (ms_e2e / 1e3), "unit": "samples/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": 2 * B * esz * sum_nc, "d2h_bytes_per_step": 4},
         "block_hbm_frac": hbm * sps / 1e9 / peaks["hbm_gbs"],
