@@ -495,10 +495,11 @@ def other_configs(args):
     measured by its own tool in a fresh process on the same GPU (after this process's timed regions) with a
     bounded step count, and reported verbatim: config 1 on the GPU, config 4 (DDD17 bf16 batch 32), DDD17 fp32
     fwd+bwd, PyTorch eager on the B200 in fp32 / TF32 (the only pre-existing GPU implementation of the path), and
-    rows f2 / f3 / f4.  A tool that fails or times out is reported as such, never silently dropped."""
+    rows f1 (lateral conv alone vs cuDNN, fused vs unfused) / f2 / f3 / f4.  A tool that fails or times out is reported as such, never silently dropped."""
     torch.cuda.empty_cache()
     jobs = [("bench_configs", ["tools/bench_configs.py", "--steps", "10", "--warmup", "3"], 240),
             ("eager_gpu", ["tools/bench_eager_fusion.py", "--steps", "3", "--warmup", "3", "--no-ours"], 240),
+            ("f1_lateral", ["tools/bench_lateral.py", "--steps", "5"], 180),
             ("f2_detection", ["tools/bench_detection.py"], 180),
             ("f3_postprocess", ["tools/bench_postprocess.py"], 180),
             ("f4_events", ["tools/bench_events.py"], 180)]

@@ -12,6 +12,7 @@
 // a second trip to HBM at the full-size levels.
 #include <type_traits>
 #include "common.cuh"
+#include "tc05.cuh"
 
 namespace frn {
 namespace {
@@ -209,70 +210,74 @@ __global__ void __launch_bounds__(GS < 256 ? 256 : GS) gate_stats_kernel(long ro
   }
 }
 
-// Long rows (N >= 4096): the row is cut into S segments, one CTA per (row, segment).  A CTA per whole row keeps only
-// 2 x 16 bytes per thread in flight over ~19 trips, i.e. ~7 GB/s per CTA whatever else runs on the SM, and 2048 such
-// CTAs are 2.3 waves of 6 per SM: 143 us for 629 MB at DSEC level 1 (0.66 of the HBM peak) however many bytes the
-// kernel moves (the two-pass version took the same time for 876 MB).  A segment is ~2 K elements: every load of the
-// CTA is issued before the first use, the CTA lives for a few microseconds and the grid is ~18 waves.  Each CTA
-// leaves its (n, mean, M2) pair in `part`; the last CTA of a row to arrive (ticket counter) merges the S triples in
-// segment order, so the result does not depend on which CTA is last.
-template <int U>
-__global__ void __launch_bounds__(256) gate_stats_seg_kernel(int N, int seg_len, int S, const float* __restrict__ r0,
-                                                             const float* __restrict__ e0, float* __restrict__ r1,
-                                                             float* __restrict__ e1, float eps, float* __restrict__ mu_r,
-                                                             float* __restrict__ sd_r, float* __restrict__ mu_e,
-                                                             float* __restrict__ sd_e, float* part,
-                                                             unsigned int* counter) {
+// Long rows (N >= 4096, 16-byte aligned): the two input rows are streamed through shared memory by bulk async copies
+// (cp.async.bulk, completion on an mbarrier), three 8 KB chunks per map in flight per CTA.  The register-staged
+// kernel above keeps 2 x 16 bytes per thread in flight: 6 CTAs x 256 threads = 48 KB per SM against the ~66 KB that
+// 44 GB/s per SM x ~1.5 us of loaded latency need, which is exactly the 0.66 - 0.75 of the HBM peak it reached
+// however many bytes it moved (143 us at DSEC level 1 for both the two-pass and the one-pass version; more loads per
+// thread cost the occupancy they bought; one CTA per (row, 2 K-element segment) with a last-arriver merge was
+// slower still: 18 K CTAs of two block-wide merges each).  With bulk copies the bytes in flight do not occupy
+// registers: 4 CTAs x 3 stages x 16 KB = 192 KB per SM.
+constexpr int kGsChunk = 2048;      // floats per map and stage
+constexpr int kGsStages = 3;
+__global__ void __launch_bounds__(256) gate_stats_bulk_kernel(int N, const float* __restrict__ r0,
+                                                              const float* __restrict__ e0, float* __restrict__ r1,
+                                                              float* __restrict__ e1, float eps, float* __restrict__ mu_r,
+                                                              float* __restrict__ sd_r, float* __restrict__ mu_e,
+                                                              float* __restrict__ sd_e) {
+  using namespace tc;
+  extern __shared__ __align__(128) uint8_t gs_smem[];
+  float (*buf)[2][kGsChunk] = reinterpret_cast<float (*)[2][kGsChunk]>(gs_smem);
+  uint64_t* full = reinterpret_cast<uint64_t*>(gs_smem + sizeof(float) * kGsStages * 2 * kGsChunk);
   __shared__ float sm[96];
-  __shared__ unsigned int ticket;
-  const long row = blockIdx.x;
-  const int seg = blockIdx.y, lane = threadIdx.x;
-  const int n_begin = seg * seg_len, n_end = min(N, n_begin + seg_len);
-  const long o = row * N;
+  const long row = blockIdx.x, o = row * N;
+  const int tid = threadIdx.x;
+  const int nchunks = (N + kGsChunk - 1) / kGsChunk;
+  if (tid == 0) {
+    for (int s = 0; s < kGsStages; s++) mbar_init(&full[s], 1);
+    mbar_init_fence();
+  }
+  __syncthreads();
+  auto issue = [&](int c) {
+    const int s = c % kGsStages, n0 = c * kGsChunk;
+    const uint32_t bytes = (uint32_t)(min(kGsChunk, N - n0) * 4);
+    mbar_expect_tx(&full[s], 2 * bytes);
+    bulk_g2s(&buf[s][0][0], r0 + o + n0, bytes, &full[s]);
+    bulk_g2s(&buf[s][1][0], e0 + o + n0, bytes, &full[s]);
+  };
+  if (tid == 0)
+    for (int c = 0; c < kGsStages && c < nchunks; c++) issue(c);
   ShiftedSum ar, ae; ar.init(); ae.init();
-  for (int n0 = n_begin + lane * 4; n0 < n_end; n0 += U * 1024) {
-    Vec<4> a[U], b[U];
+  for (int c = 0; c < nchunks; c++) {
+    const int s = c % kGsStages, n0 = c * kGsChunk, len = min(kGsChunk, N - n0);
+    mbar_wait(&full[s], (uint32_t)((c / kGsStages) & 1));
 #pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int n = n0 + u * 1024;
-      if (n < n_end) { a[u].load(r0 + o + n); b[u].load(e0 + o + n); }
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int n = n0 + u * 1024;
-      if (n < n_end) {
-        Vec<4> x, y;
+    for (int u = 0; u < kGsChunk / 1024; u++) {
+      const int i = (tid + u * 256) * 4;
+      if (i < len) {
+        const float4 a = *reinterpret_cast<const float4*>(&buf[s][0][i]);
+        const float4 b = *reinterpret_cast<const float4*>(&buf[s][1][i]);
+        const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+        float x[4], y[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-          const float m = a[u].v[q] * b[u].v[q];
-          x.v[q] = a[u].v[q] + m; y.v[q] = b[u].v[q] + m;
-          ar.add(x.v[q]); ae.add(y.v[q]);
+          const float m = av[q] * bv[q];
+          x[q] = av[q] + m; y[q] = bv[q] + m;
+          ar.add(x[q]); ae.add(y[q]);
         }
-        x.store(r1 + o + n); y.store(e1 + o + n);
+        *reinterpret_cast<float4*>(r1 + o + n0 + i) = make_float4(x[0], x[1], x[2], x[3]);
+        *reinterpret_cast<float4*>(e1 + o + n0 + i) = make_float4(y[0], y[1], y[2], y[3]);
       }
     }
+    fence_proxy_async_smem();        // generic reads of this stage are ordered before the bulk copy that refills it
+    __syncthreads();
+    if (tid == 0 && c + kGsStages < nchunks) issue(c + kGsStages);
   }
   const Moments mr = group_merge<256>(ar.finish(), sm);
   const Moments me = group_merge<256>(ae.finish(), sm);
-  if (lane == 0) {
-    float* p = part + (row * S + seg) * 6;
-    p[0] = mr.n; p[1] = mr.mean; p[2] = mr.m2; p[3] = me.n; p[4] = me.mean; p[5] = me.m2;
-    __threadfence();
-    ticket = atomicAdd(&counter[row], 1u);
-  }
-  __syncthreads();
-  if (ticket != (unsigned)(S - 1)) return;
-  if (lane == 0) {                          // last CTA of this row: merge in segment order
-    __threadfence();
-    const volatile float* p = part + row * S * 6;
-    Moments tr{p[0], p[1], p[2]}, te{p[3], p[4], p[5]};
-    for (int j = 1; j < S; j++) {
-      tr.merge(p[j * 6], p[j * 6 + 1], p[j * 6 + 2]);
-      te.merge(p[j * 6 + 3], p[j * 6 + 4], p[j * 6 + 5]);
-    }
-    mu_r[row] = tr.mean; sd_r[row] = sqrtf(tr.m2 / (float)(N - 1) + eps);
-    mu_e[row] = te.mean; sd_e[row] = sqrtf(te.m2 / (float)(N - 1) + eps);
-    counter[row] = 0;                       // ready for the next launch
+  if (tid == 0) {
+    mu_r[row] = mr.mean; sd_r[row] = sqrtf(mr.m2 / (float)(N - 1) + eps);
+    mu_e[row] = me.mean; sd_e[row] = sqrtf(me.m2 / (float)(N - 1) + eps);
   }
 }
 
@@ -470,14 +475,21 @@ __global__ void __launch_bounds__(GS < 256 ? 256 : GS) row_dot_kernel(long rows,
 __device__ __forceinline__ float rn_tf32(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
-// bf16 (rows, N) -> fp32 (rows, ld), exact (bf16 values are tf32 values); pad columns zero
+// bf16 (rows, N) -> fp32 (rows, ld), exact (bf16 values are tf32 values); pad columns zero.  One CTA per row
+// segment of 2048 outputs: four consecutive outputs per thread and trip, one 16-byte store each (rows of ld floats
+// are 16-byte aligned); the bf16 source rows are only 2-byte aligned, so they are read element-wise (coalesced).
 __global__ void __launch_bounds__(256) cast_pad_bf16_kernel(long rows, int N, int ld, const uint16_t* __restrict__ src,
                                                             float* __restrict__ dst) {
-  const long total = rows * ld, stride = (long)gridDim.x * blockDim.x;
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += stride) {
-    const long r = i / ld;
-    const int n = (int)(i - r * ld);
-    dst[i] = n < N ? __uint_as_float((uint32_t)__ldg(src + r * N + n) << 16) : 0.f;
+  const long row = blockIdx.x;
+  const uint16_t* s = src + row * N;
+  float* d = dst + row * ld;
+  for (int n = (blockIdx.y * 256 + threadIdx.x) * 4; n < ld; n += gridDim.y * 1024) {
+    float4 v;
+    v.x = n < N ? __uint_as_float((uint32_t)__ldg(s + n) << 16) : 0.f;
+    v.y = n + 1 < N ? __uint_as_float((uint32_t)__ldg(s + n + 1) << 16) : 0.f;
+    v.z = n + 2 < N ? __uint_as_float((uint32_t)__ldg(s + n + 2) << 16) : 0.f;
+    v.w = n + 3 < N ? __uint_as_float((uint32_t)__ldg(s + n + 3) << 16) : 0.f;
+    *reinterpret_cast<float4*>(d + n) = v;
   }
 }
 __global__ void round_tf32_kernel(long n, const float* __restrict__ src, float* __restrict__ dst) {
@@ -498,18 +510,30 @@ __global__ void __launch_bounds__(256) gate_stats_pad_kernel(long rows, int N, i
   if (row < 0) return;
   const long o = row * ld;
   ShiftedSum ar, ae; ar.init(); ae.init();
-  for (int n = lane * 4; n < N; n += GS * 4) {
-    Vec<4> a, b, x, y;
-    a.load(r0 + o + n); b.load(e0 + o + n);
+  constexpr int U = 3;
+  for (int n0 = lane * 4; n0 < N; n0 += U * GS * 4) {
+    Vec<4> a[U], b[U];
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const bool ok = n + q < N;
-      const float m = a.v[q] * b.v[q];
-      const float xv = a.v[q] + m, yv = b.v[q] + m;
-      if (ok) { ar.add(xv); ae.add(yv); }
-      x.v[q] = ok ? rn_tf32(xv) : 0.f; y.v[q] = ok ? rn_tf32(yv) : 0.f;
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * GS * 4;
+      if (n < N) { a[u].load(r0 + o + n); b[u].load(e0 + o + n); }
     }
-    x.store(r1 + o + n); y.store(e1 + o + n);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int n = n0 + u * GS * 4;
+      if (n < N) {
+        Vec<4> x, y;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const bool ok = n + q < N;
+          const float m = a[u].v[q] * b[u].v[q];
+          const float xv = a[u].v[q] + m, yv = b[u].v[q] + m;
+          if (ok) { ar.add(xv); ae.add(yv); }
+          x.v[q] = ok ? rn_tf32(xv) : 0.f; y.v[q] = ok ? rn_tf32(yv) : 0.f;
+        }
+        x.store(r1 + o + n); y.store(e1 + o + n);
+      }
+    }
   }
   const Moments mr = group_merge<GS>(ar.finish(), sm);
   const Moments me = group_merge<GS>(ae.finish(), sm);
@@ -575,25 +599,17 @@ int row_mean_std(cudaStream_t st, long rows, int N, const float* x, float eps, f
   return FRN_OK;
 }
 
-int gate_stats_segments(int N) { return N >= 4096 && N % 4 == 0 ? (N / 2048 < 16 ? N / 2048 : 16) : 1; }
-size_t gate_stats_scratch_bytes(long rows, int N) {
-  const int S = gate_stats_segments(N);
-  return S > 1 ? align_up((size_t)rows * S * 6 * sizeof(float)) + align_up((size_t)rows * sizeof(unsigned int)) : 0;
-}
+size_t gate_stats_scratch_bytes(long rows, int N) { (void)rows; (void)N; return 0; }
 int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* e0, float* r1, float* e1,
                float eps, float* mu_r, float* sd_r, float* mu_e, float* sd_e, void* scratch) {
+  (void)scratch;
   bool vec = (N % 4 == 0) && aligned16(r0) && aligned16(e0) && aligned16(r1) && aligned16(e1);
-  const int S = gate_stats_segments(N);
-  if (vec && S > 1 && scratch && rows <= 2147483647L) {
+  if (vec && N >= 4096 && rows <= 2147483647L) {
     ScopedTimer tm(st, FRN_TIME_ROWS);
     KernelTimer kt(st, "gate_stats_kernel", 16.0 * (double)rows * N);
-    float* part = (float*)scratch;
-    unsigned int* counter = (unsigned int*)((char*)scratch + align_up((size_t)rows * S * 6 * sizeof(float)));
-    if (cudaMemsetAsync(counter, 0, (size_t)rows * sizeof(unsigned int), st) != cudaSuccess) return (int)cudaGetLastError();
-    const int seg_len = ((N + S - 1) / S + 3) / 4 * 4;
-    const dim3 grid((unsigned)rows, (unsigned)S);
-    if (seg_len <= 2048) gate_stats_seg_kernel<2><<<grid, 256, 0, st>>>(N, seg_len, S, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e, part, counter);
-    else gate_stats_seg_kernel<3><<<grid, 256, 0, st>>>(N, seg_len, S, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e, part, counter);
+    constexpr int smem = (int)sizeof(float) * kGsStages * 2 * kGsChunk + 64;
+    FRN_TRY(set_smem_once((const void*)gate_stats_bulk_kernel, smem));
+    gate_stats_bulk_kernel<<<(unsigned)rows, 256, smem, st>>>(N, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e);
     FRN_LAUNCH_CHECK();
     return FRN_OK;
   }
@@ -654,9 +670,9 @@ int adain_bwd_style(cudaStream_t st, int B, int C, int N, const float* t, const 
 
 int cast_pad_bf16(cudaStream_t st, long rows, int N, int ld, const uint16_t* src, float* dst) {
   ScopedTimer tm(st, FRN_TIME_ROWS);
-  long blocks = (rows * ld + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  cast_pad_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, ld, src, dst);
+  int gy = (ld + 1023) / 1024;
+  if (gy > 4) gy = 4;
+  cast_pad_bf16_kernel<<<dim3((unsigned)rows, (unsigned)gy), 256, 0, st>>>(rows, N, ld, src, dst);
   FRN_LAUNCH_CHECK();
   return FRN_OK;
 }

@@ -56,16 +56,30 @@ def run(name, levels, B, dtype, train, steps, warmup, peaks):
         douts.append(torch.randn(B, 2 * c, h, w, generator=g).to(dev) if train else None)
     res = torch.empty(1, dtype=torch.float32).pin_memory()
 
+    streams = [torch.cuda.Stream() for _ in levels] if len(levels) > 1 else None
+
+    def one(m, a, e, go):
+        if train:
+            a = a.detach().requires_grad_(True); e = e.detach().requires_grad_(True)
+            m(a, e).backward(go)
+            return a.grad
+        with torch.no_grad():
+            return m(a, e)
+
     def step(inputs):
+        """The independent levels on their own streams (forked from / joined into the current one), as bench.py."""
         acc = None
-        for m, (a, e), go in zip(mods, inputs, douts):
-            if train:
-                a = a.detach().requires_grad_(True); e = e.detach().requires_grad_(True)
-                m(a, e).backward(go)
-                acc = a.grad
-            else:
-                with torch.no_grad():
-                    acc = m(a, e)
+        if streams is None:
+            for m, (a, e), go in zip(mods, inputs, douts):
+                acc = one(m, a, e, go)
+            return acc
+        main = torch.cuda.current_stream()
+        for s, m, (a, e), go in zip(streams, mods, inputs, douts):
+            s.wait_stream(main)
+            with torch.cuda.stream(s):
+                acc = one(m, a, e, go)
+        for s in streams:
+            main.wait_stream(s)
         return acc
 
     def step_resident():
