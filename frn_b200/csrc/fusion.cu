@@ -817,15 +817,23 @@ const char* frn_error_string(int code) {
 }
 
 const char* frn_kernel_inventory(void) {
-  return "sgemm_kernel,tc_gemm_kernel,attn_fwd_tc_kernel,attn_dq_tc_kernel,attn_dkv_tc_kernel,pack_split_kernel,attn_bwd_prep_kernel,splitk_reduce_kernel,attn_fwd_kernel,attn_bwd_kernel,row_mean_std_kernel,"
-         "gate_stats_kernel,adain_apply_kernel,adain_bwd_reduce_kernel,adain_bwd_content_kernel,"
-         "adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,row_dot_kernel,"
-         "style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,gate_backward_kernel,"
-         "transpose_kernel,scale_rows_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
-         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,stack3_kernel,unstack3_kernel,stack_cols3_kernel,"
+  return "tc_gemm2_kernel,tc_gemm_kernel,splitk_reduce_kernel,splitk_reduce_grouped_kernel,"
+         "attn_fwd_tc_kernel,attn_dq2_tc_kernel,attn_dkv2_tc_kernel,attn_dkv3_tc_kernel,pack_split_kernel,attn_bwd_prep_kernel,"
+         "row_mean_std_kernel,gate_stats_kernel,gate_stats_bulk_kernel,adain_apply_kernel,adain_apply_bf16_kernel,"
+         "adain_bwd_reduce_kernel,adain_bwd_content_kernel,adain_bwd_style_kernel,center_rows_kernel,add_row_bias_kernel,"
+         "row_dot_kernel,cast_pad_bf16_kernel,round_tf32_kernel,gate_stats_pad_kernel,center_rows_pad_kernel,"
+         "adain_apply_bf16_pad_kernel,style_coeffs_kernel,finish_style_std_kernel,batch_row_sum_kernel,row_sum_kernel,"
+         "sum_parts_kernel,gate_backward_kernel,gate_backward_kernel4,transpose_kernel,scale_rows_kernel,scale_cols_kernel,"
+         "affine_coeffs_kernel,lateral_wgrad_combine_kernel,outer_accumulate_kernel,fill_zero_kernel,scale_sum_batch_kernel,"
+         "softmax_rows_kernel,exp_sub_lse_kernel,ds_from_p_kernel,col_partial_sum_kernel,col_center_kernel,stack3_kernel,"
+         "unstack3_kernel,stack_cols3_kernel,stack_cols3_v4_kernel,cast_bf16_to_f32_kernel,"
          "anchors_level_kernel,focal_forward_kernel,focal_finalize_kernel,focal_backward_kernel,"
          "event_bounds_kernel,event_scatter_kernel,voxel_normalize_kernel,"
-         "decode_clip_kernel,nms_keys_kernel,nms_class_kernel,nms_gather_kernel,row_sum_kernel,sum_parts_kernel";
+         "decode_clip_kernel,nms_keys_kernel,nms_class_kernel,nms_gather_kernel"
+#ifdef FRN_DEBUG_ENGINES
+         ",sgemm_kernel,attn_fwd_kernel,attn_bwd_kernel,attn_dq_tc_kernel,attn_dkv_tc_kernel"
+#endif
+      ;
 }
 
 // ---- GEMM ----------------------------------------------------------------------

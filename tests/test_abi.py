@@ -25,7 +25,8 @@ def test_library_exports_every_declared_symbol():
     for name in declared_symbols():
         assert hasattr(lib, name), name
     assert lib.frn_abi_version() == 2
-    assert b"attn_fwd_kernel" in lib.frn_kernel_inventory()
+    inv = lib.frn_kernel_inventory()
+    assert b"attn_fwd_tc_kernel" in inv and b"tc_gemm2_kernel" in inv and b"gate_stats_bulk_kernel" in inv
 
 
 def test_size_queries():
