@@ -606,7 +606,7 @@ int gate_stats(cudaStream_t st, long rows, int N, const float* r0, const float* 
   bool vec = (N % 4 == 0) && aligned16(r0) && aligned16(e0) && aligned16(r1) && aligned16(e1);
   if (vec && N >= 4096 && rows <= 2147483647L) {
     ScopedTimer tm(st, FRN_TIME_ROWS);
-    KernelTimer kt(st, "gate_stats_kernel", 16.0 * (double)rows * N);
+    KernelTimer kt(st, "gate_stats_bulk_kernel", 16.0 * (double)rows * N);
     constexpr int smem = (int)sizeof(float) * kGsStages * 2 * kGsChunk + 64;
     FRN_TRY(set_smem_once((const void*)gate_stats_bulk_kernel, smem));
     gate_stats_bulk_kernel<<<(unsigned)rows, 256, smem, st>>>(N, r0, e0, r1, e1, eps, mu_r, sd_r, mu_e, sd_e);

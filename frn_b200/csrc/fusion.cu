@@ -75,11 +75,6 @@ int run_gemm(Ctx& c, const GemmDesc& d_in) {
   }
   return gemm(c.st, d, c.splitk, c.splitk_cap);
 }
-// The materialised attention of levels 3-4 (d > 64, 1.5 % of the block's FLOPs): its logits are
-// exponentiated and its dQ sums cancel heavily, so the keys are centred over positions first (as in the
-// streaming engine); with that the split-TF32 GEMM holds the 1e-5 gate and no exact-FFMA detour is needed.
-int run_gemm_exact(Ctx& c, const GemmDesc& d) { return run_gemm(c, d); }
-
 GemmDesc desc(const float* A, const float* B, float* C, int M, int N, int K, int batch) {
   GemmDesc d{};
   d.A = A; d.B = B; d.C = C; d.M = M; d.N = N; d.K = K; d.batch = batch;
@@ -232,7 +227,9 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
   }
   int ch = chunk_for_scores(B, N, 1);
   float* S = c.ws.take<float>((size_t)ch * N * N);
-  // keys centred over positions, as in the streaming engine: softmax_j is unchanged by it
+  // The materialised attention of levels 3-4 (d > 64, 1.5 % of the block's FLOPs): its logits are exponentiated and
+  // its dQ sums cancel heavily, so the keys are centred over positions first, as in the streaming engine (softmax_j is
+  // unchanged by it); with that the split-TF32 GEMM holds the 1e-5 gate.
   float* Kz = c.ws.take<float>((size_t)B * d * N);
   float* kbar = c.ws.take<float>((size_t)B * d);
   float* ksd = c.ws.take<float>((size_t)B * d);
@@ -245,13 +242,13 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
     g.sAm = 1; g.sAk = N; g.sAb = (long)d * N;
     g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
     g.sCm = N; g.sCn = 1; g.sCb = (long)N * N;
-    FRN_TRY(run_gemm_exact(c, g));
+    FRN_TRY(run_gemm(c, g));
     RUN(c, softmax_rows(c.st, (long)nb * N, N, S, s.lse + (long)b0 * N));
     GemmDesc y = desc(S, s.Vc + o, s.Y + o, N, d, N, nb);       // Y[i][k] = sum_j P[i][j] V[k][j]
     y.sAm = N; y.sAk = 1; y.sAb = (long)N * N;
     y.sBk = 1; y.sBn = N; y.sBb = (long)d * N;
     y.sCm = d; y.sCn = 1; y.sCb = (long)N * d;
-    FRN_TRY(run_gemm_exact(c, y));
+    FRN_TRY(run_gemm(c, y));
   }
   return FRN_OK;
 }
@@ -358,29 +355,29 @@ int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* d
     g.sAm = 1; g.sAk = N; g.sAb = dn;
     g.sBk = N; g.sBn = 1; g.sBb = dn;
     g.sCm = N; g.sCn = 1; g.sCb = nn;
-    FRN_TRY(run_gemm_exact(c, g));
+    FRN_TRY(run_gemm(c, g));
     RUN(c, exp_sub_lse(c.st, (long)nb * N, N, P, s.lse + (long)b0 * N));   // P = exp(S - lse)
     GemmDesc v = desc(P, dYp + o, dVp + o, N, d, N, nb);            // dV[j][k] = sum_i P[i][j] dY[i][k]
     v.sAm = 1; v.sAk = N; v.sAb = nn;
     v.sBk = d; v.sBn = 1; v.sBb = dn;
     v.sCm = d; v.sCn = 1; v.sCb = dn;
-    FRN_TRY(run_gemm_exact(c, v));
+    FRN_TRY(run_gemm(c, v));
     GemmDesc p = desc(dYp + o, s.Vc + o, dS, N, N, d, nb);          // dP[i][j] = sum_k dY[i][k] V[k][j]
     p.sAm = d; p.sAk = 1; p.sAb = dn;
     p.sBk = N; p.sBn = 1; p.sBb = dn;
     p.sCm = N; p.sCn = 1; p.sCb = nn;
-    FRN_TRY(run_gemm_exact(c, p));
+    FRN_TRY(run_gemm(c, p));
     RUN(c, ds_from_p(c.st, (long)nb * N, N, P, dS, delta + (long)b0 * N));  // dS = P (dP - delta)
     GemmDesc q = desc(dS, Kz + o, dQp + o, N, d, N, nb);            // dQ[i][k] = sum_j dS[i][j] K[k][j]  (rows of dS sum to 0)
     q.sAm = N; q.sAk = 1; q.sAb = nn;
     q.sBk = 1; q.sBn = N; q.sBb = dn;
     q.sCm = d; q.sCn = 1; q.sCb = dn;
-    FRN_TRY(run_gemm_exact(c, q));
+    FRN_TRY(run_gemm(c, q));
     GemmDesc k = desc(dS, s.Qc + o, dKp + o, N, d, N, nb);          // dK[j][k] = sum_i dS[i][j] Q[k][i]
     k.sAm = 1; k.sAk = N; k.sAb = nn;
     k.sBk = 1; k.sBn = N; k.sBb = dn;
     k.sCm = d; k.sCn = 1; k.sCb = dn;
-    FRN_TRY(run_gemm_exact(c, k));
+    FRN_TRY(run_gemm(c, k));
   }
   return FRN_OK;
 }
