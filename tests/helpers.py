@@ -83,6 +83,9 @@ def run_module(module, a, e, dout):
     return out.detach().cpu().numpy(), a.grad.cpu().numpy(), e.grad.cpu().numpy(), grads
 
 
+PARITY_LOG = []          # (name, {quantity: l2-relative error}) of every block-level gate of this session (conftest dumps it)
+
+
 def check_against(name, got, ref, tol=RTOL_F32):
     out, da, de, grads = got
     rout, rda, rde, rgrads = ref
@@ -95,6 +98,7 @@ def check_against(name, got, ref, tol=RTOL_F32):
             errs[k] = float(np.abs(grads[k]).max()) / max(gscale, 1e-30) * (tol / ATOL_THETA_BIAS)
         else:
             errs[k] = rel_l2(grads[k], v)
+    PARITY_LOG.append((name, {k: float(v) for k, v in errs.items()}))
     bad = {k: v for k, v in errs.items() if not (v <= tol)}
     assert not bad, f"{name}: over tolerance {tol}: {bad}\nall: {errs}"
     return errs
