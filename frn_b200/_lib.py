@@ -48,6 +48,9 @@ _SIGNATURES = {
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_size_t]),
     "frn_adain_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "frn_adain_static_max_rows": (C.c_long, []),
+    "frn_adain_backward_static": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "frn_cab_saved_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "frn_cab_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "frn_cab_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,

@@ -809,6 +809,9 @@ const char* frn_error_string(int code) {
     case FRN_ERR_WORKSPACE: return "workspace or saved buffer too small";
     case FRN_ERR_UNSUPPORTED: return "unsupported configuration";
     case FRN_ERR_NO_DEVICE: return "no CUDA device";
+    case FRN_ERR_STATIC_SCRATCH:
+      return "B*C exceeds the built-in scratch of frn_adain_backward_static (FRN_ADAIN_STATIC_MAX_ROWS = 65536 rows); "
+             "use frn_adain_backward with a workspace";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
   }
 }

@@ -53,7 +53,8 @@ enum {
   FRN_ERR_NULL_POINTER = -2,
   FRN_ERR_WORKSPACE = -3,      /* ws_bytes / saved_bytes smaller than required    */
   FRN_ERR_UNSUPPORTED = -4,    /* C/8 > 256, unknown dtype ...                    */
-  FRN_ERR_NO_DEVICE = -5
+  FRN_ERR_NO_DEVICE = -5,
+  FRN_ERR_STATIC_SCRATCH = -6  /* frn_adain_backward_static: B*C > FRN_ADAIN_STATIC_MAX_ROWS */
 };
 
 enum { FRN_F32 = 0, FRN_BF16 = 1 };
@@ -112,6 +113,23 @@ int frn_adain_backward(void* stream, int B, int C, int N, int N_style, const flo
                        const float* style, const float* stats, const float* dout,
                        float* dcontent, float* dstyle, void* ws, size_t ws_bytes);
 size_t frn_adain_workspace_bytes(int B, int C, int N);
+
+/* frn_adain_backward without a workspace argument, for callers that cannot call cudaMalloc (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * The B*C-float reductions g1, g2 that frn_adain_backward keeps in `ws` live in a
+ * file-scope __device__ array of 2 * FRN_ADAIN_STATIC_MAX_ROWS floats (512 KiB, held by every GPU that loads the
+ * library until exit); the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and
+ * enqueues the same three kernels, so dcontent / dstyle are bit-identical to frn_adain_backward's.
+ *   - B*C > FRN_ADAIN_STATIC_MAX_ROWS returns FRN_ERR_STATIC_SCRATCH and enqueues nothing.
+ *   - The device that owns `stream` and the buffers must be the current device.
+ *   - All calls on a device share the one array (it keeps the last call's contents; every call overwrites the rows
+ *     it reads first, nothing needs clearing).  Calls that overlap on the GPU -- different streams, threads or
+ *     graph branches -- RACE: serialise them on one stream, or use frn_adain_backward with a workspace each. */
+#define FRN_ADAIN_STATIC_MAX_ROWS 65536
+long frn_adain_static_max_rows(void);
+int frn_adain_backward_static(void* stream, int B, int C, int N, int N_style, const float* content,
+                              const float* style, const float* stats, const float* dout,
+                              float* dcontent, float* dstyle);
 
 /* ---- CrossAttentionBlock (retinanet/Attention.py) ------------------------- */
 
