@@ -172,6 +172,7 @@ size_t tc_gemm_workspace_bytes(const GemmDesc& d);
 int tc_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);
 int tc_gemm_rowsumsq(cudaStream_t st, const GemmDesc& d, float* out_partial);
 int attn_tc_trace_read(unsigned long long* out16);
+int tc_gemm_ts_read(long long* out);                  // stage hand-over timestamps, only with -DFRN_GEMM_TS
 int tc_gemm_trace_read(unsigned long long* out16);   // role cycle counters, only with -DFRN_GEMM_TRACE
 size_t ffma_gemm_workspace_bytes(const GemmDesc& d);
 int ffma_gemm(cudaStream_t st, const GemmDesc& d, void* ws, size_t ws_bytes);

@@ -854,6 +854,7 @@ int frn_gemm_f32(void* stream, int engine, const frn_gemm_desc* g, void* ws, siz
   return engine ? tc_gemm((cudaStream_t)stream, d, ws, ws_bytes) : ffma_gemm((cudaStream_t)stream, d, ws, ws_bytes);
 }
 int frn_debug_gemm_trace(unsigned long long* out16) { return frn::tc_gemm_trace_read(out16); }
+int frn_debug_gemm_ts(long long* out) { return frn::tc_gemm_ts_read(out); }
 int frn_debug_attn_trace(unsigned long long* out16) { return frn::attn_tc_trace_read(out16); }
 void frn_set_gemm_engine(int engine) { set_gemm_engine(engine); }
 void frn_set_attn_engine(int engine) { set_attn_engine(engine); }

@@ -50,9 +50,26 @@ constexpr int kChunk = 4;     // stages per accumulation chain (K = 128)
 __device__ unsigned long long g_trace[16];
 #define TRACE_T0() const long long tr0__ = clock64()
 #define TRACE_ADD(slot) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) atomicAdd(&g_trace[slot], (unsigned long long)(clock64() - tr0__)); } while (0)
+// whole-kernel cycles (slot 13) and nanoseconds (slot 14) of CTA 0: their ratio is the SM clock under this kernel's load
+#define TRACE_KERNEL_BEGIN() const long long trk0__ = clock64(); unsigned long long trn0__; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(trn0__))
+#define TRACE_KERNEL_END() do { if (blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long n1__; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(n1__)); \
+    atomicAdd(&g_trace[13], (unsigned long long)(clock64() - trk0__)); atomicAdd(&g_trace[14], n1__ - trn0__); } } while (0)
 #else
 #define TRACE_T0() do {} while (0)
 #define TRACE_ADD(slot) do {} while (0)
+#define TRACE_KERNEL_BEGIN() do {} while (0)
+#define TRACE_KERNEL_END() do {} while (0)
+#endif
+
+// -DFRN_GEMM_TS: clock64 stamps of the hand-over points of the first 256 stages of CTA 0 (plain stores, no atomics),
+// read back with frn_debug_gemm_ts: the timeline of one stage slot through producer -> split -> MMA -> producer.
+#ifdef FRN_GEMM_TS
+__device__ long long g_ts[8][256];
+#define TS(role, it) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && (it) < 256) g_ts[role][(int)(it)] = clock64(); } while (0)
+#define TS_ANY(role, it) do { if (blockIdx.x == 0 && (it) < 256) g_ts[role][(int)(it)] = clock64(); } while (0)
+#else
+#define TS(role, it) do {} while (0)
+#define TS_ANY(role, it) do {} while (0)
 #endif
 
 template <int BN> struct TcCfg {
@@ -583,10 +600,20 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
 // accumulator, hi.hi into the main one ... except that hi.[hi | lo] and lo.[hi | lo] are issued as two N = 2 BN
 // instructions (see the MMA warp), so the column halves hold hh + lh and hl + ll.
 //
-// 18 warps: 0 = TMA producer (one lane), 1 = MMA issue, 2-9 = lo split, 10-17 = accumulator drain + epilogue.
-constexpr int kV2Threads = 18 * 32;
-constexpr int kV2SplitWarp0 = 2, kV2EpiWarp0 = 10;
-// Accumulation chain of the v2 kernel, in stages (K = 128), as in the first kernel.
+// 19 warps: 0 = TMA producer (one lane), 1 and 18 = MMA issue, 2-9 = lo split, 10-17 = accumulator drain + epilogue.
+//
+// TWO issuing warps.  Timestamps of the hand-over points (-DFRN_GEMM_TS, tools/prof_gemm.py TIMELINE) showed one
+// issuing thread spending ~900 cycles per stage on the 12 MMAs and another ~900 on the commits, the loop turn-around
+// and the next barrier wait, with the tensor pipe (1024 cycles of work per stage) running dry in between.  Issuer w
+// takes the stages i = w (mod 2) of a tile and accumulates chains of kChunk2 of ITS stages in accumulator buffer w,
+// so each issuer's bookkeeping runs under the other's MMAs, the two never touch the same accumulator, and the drain
+// warps empty buffer 0 while buffer 1 fills (and vice versa).
+constexpr int kV2Threads = 19 * 32;
+constexpr int kV2SplitWarp0 = 2, kV2EpiWarp0 = 10, kV2Issuer1 = 18;
+// Accumulation chain of the v2 kernel, in stages of ONE issuer: 4 stages = 16 truncating additions per chain, as in
+// the first kernel, and together the two buffers hold 8 stages (a whole K = 256 tile), so the issuers run on while
+// the drain warps store the previous tile.  (2 stages per chain: the tile-end store stalled both issuers, 149 -> 168 us
+// on the 256 x 19200 x 256 convolution.)
 constexpr int kChunk2 = 4;
 
 template <int BN> struct Tc2Cfg {
@@ -611,11 +638,27 @@ __device__ __forceinline__ float lo_tf32(float x) {
   return __uint_as_float((__float_as_uint(l) + 0x1000u) & 0xFFFFE000u);
 }
 
+// Every lane polls (one polling lane + __syncwarp was measured 14 % slower on the 256 x 19200 x 256 convolution).
+__device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity, int lane) {
+  (void)lane;
+#ifdef FRN_GEMM_SPIN
+  mbar_spin(bar, parity);
+#else
+  mbar_wait(bar, parity);
+#endif
+}
+
 struct V2Args {
   int ktiles, tiles_per_split, nsplit, gx, gy, gz;
   int a_mn, b_mn;            // operand is MN-major (its non-K dimension is the contiguous one)
   uint32_t mn_layout, mn_sbo;   // descriptor layout type and 4-row (or 8-row) group stride of an MN-major tile
+  int dbg;                   // -DFRN_GEMM_TRACE builds only (env FRN_GEMM_DBG): timing experiments that break the result
 };
+#if defined(FRN_GEMM_TRACE) || defined(FRN_GEMM_KNOBS)
+#define DBG(bit) ((g.dbg >> (bit)) & 1)
+#else
+#define DBG(bit) 0
+#endif
 
 template <int BN, int EPI, bool ACC>
 __global__ void __launch_bounds__(kV2Threads, 1)
@@ -623,6 +666,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
                 const __grid_constant__ CUtensorMap tmB) {
   using Cfg = Tc2Cfg<BN>;
   constexpr int HC = BN / 2;
+  TRACE_KERNEL_BEGIN();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* ctrl = smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kEpiBytes;
@@ -640,7 +684,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
 
   if (tid == 0) {
     for (int s = 0; s < Cfg::kStages; s++) { mbar_init(&raw_full[s], 1); mbar_init(&lo_full[s], 8); mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_free[s], kEpiThreads); }
+    for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_free[s], 8); }
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB);
     mbar_init_fence();
   }
@@ -664,26 +708,35 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
           const int stage = (int)(it % Cfg::kStages);
           const uint32_t phase = (uint32_t)((it / Cfg::kStages) & 1);
           { TRACE_T0();
+#ifdef FRN_GEMM_SPIN
+          mbar_spin(&empty[stage], phase ^ 1);
+#else
           mbar_wait(&empty[stage], phase ^ 1);
+#endif
           TRACE_ADD(0); }
-          mbar_expect_tx(&raw_full[stage], Cfg::kABytes + Cfg::kBBytes);
+          TS(0, it);
+          mbar_expect_tx(&raw_full[stage], (DBG(5) ? 0 : Cfg::kABytes) + (DBG(6) ? 0 : Cfg::kBBytes));
           const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes, sB = sA + 2 * Cfg::kABytes;
           const int k0 = kt * TBK, ba = p.sAb ? b : 0, bb = p.sBb ? b : 0;
-          if (!g.a_mn) tma_load_3d(sA, &tmA, k0, tl.m0, ba, &raw_full[stage]);
+          if (DBG(5)) {
+          } else if (!g.a_mn) tma_load_3d(sA, &tmA, k0, tl.m0, ba, &raw_full[stage]);
           else
 #pragma unroll
             for (int j = 0; j < TBM / 32; j++) tma_load_3d(sA + j * 4096, &tmA, tl.m0 + 32 * j, k0, ba, &raw_full[stage]);
-          if (!g.b_mn) tma_load_3d(sB, &tmB, k0, tl.n0, bb, &raw_full[stage]);
+          if (DBG(6)) {
+          } else if (!g.b_mn) tma_load_3d(sB, &tmB, k0, tl.n0, bb, &raw_full[stage]);
           else
 #pragma unroll
             for (int j = 0; j < BN / 32; j++) tma_load_3d(sB + j * 4096, &tmB, tl.n0 + 32 * j, k0, bb, &raw_full[stage]);
+          TS(1, it);
           kt++;
           if (tl.b_fixed < 0 && kt == ktiles) { kt = 0; b++; }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===== MMA issue =====
+  } else if (warp == 1 || warp == kV2Issuer1) {
+    // ===== MMA issue (issuer w: stages i = w mod 2 of every tile, accumulator buffer w) =====
+    const int w = warp == 1 ? 0 : 1;
     // [b_hi | b_lo] are adjacent in shared memory (both majors), so ONE instruction with N = 2 BN forms
     // a_hi.[b_hi | b_lo] = [hh | hl] in the column halves [main | small] of the accumulator buffer; a_lo.b_hi and
     // a_lo.b_lo follow as two N = BN instructions into the small half.  Same tensor time as four N = BN instructions
@@ -693,53 +746,78 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     // canary for truncation bias -- went from under the 1e-5 gate to 1.03e-5).
     const uint32_t majors = ((uint32_t)g.a_mn << 15) | ((uint32_t)g.b_mn << 16);
     const uint32_t idesc2 = umma_idesc_tf32(TBM, 2 * BN) | majors, idesc1 = umma_idesc_tf32(TBM, BN) | majors;
+    // Descriptors of (stage 0, K slice 0).  Every other descriptor differs only in the 14-bit start-address field
+    // (bytes >> 4; shared memory ends below 256 KB, so the additions never carry out of the field): the issuing
+    // thread spends a handful of integer additions per K slice.  (Rebuilding the four descriptors from scratch for
+    // every slice, with the major-dependent branches, was ~1000 cycles of serial scalar code per stage -- as much
+    // as the MMAs themselves, measured with the tensor work switched off: tools/prof_gemm.py SWEEP.)
+    const uint32_t sA0 = stage_base, sB0 = stage_base + 2 * Cfg::kABytes;
+    const uint64_t dA0 = g.a_mn ? umma_desc(sA0, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sA0);
+    const uint64_t dB0 = g.b_mn ? umma_desc(sB0, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sB0);
+    // K-major: + 32 bytes per K = 8 slice inside the 128-byte rows; MN-major: + 8 rows of 128 bytes
+    const uint32_t ka = (g.a_mn ? 1024u : 32u) >> 4, kb = (g.b_mn ? 1024u : 32u) >> 4;
+    const bool split = !p.fast, lolo = !p.no_lolo;
     long it = 0;
-    int gc = 0;
+    int gc = 0;                       // chains this issuer has finished (its buffer's phase counter)
     for (int id = blockIdx.x; id < total; id += gridDim.x) {
       const TcTile tl = tc_tile(p, id, g.gx, g.gy, ktiles, g.tiles_per_split, BN);
       for (int i = 0; i < tl.ntiles; i++, it++) {
         const int stage = (int)(it % Cfg::kStages);
         const uint32_t phase = (uint32_t)((it / Cfg::kStages) & 1);
-        const bool first = (i % kChunk2) == 0;
-        const bool last = (i % kChunk2) == kChunk2 - 1 || i == tl.ntiles - 1;
-        const int buf = gc & 1;
+#ifdef FRN_GEMM_ONE_ISSUER
+        if (w != 0) continue;
+        const int j = i;
+#else
+        if ((i & 1) != w) {
+          // Not this issuer's stage, but it still has to SEE the stage complete: a parity wait only works for a
+          // waiter that is at most one phase behind, and with a 3-deep ring this issuer's next stage (it + 1) is
+          // followed by it + 3 -- the same slot as `it` -- which it could otherwise reach, and pass on the stale
+          // parity of the slot's previous use, before the other issuer has consumed `it`.
+          mbar_wait_warp(split ? &lo_full[stage] : &raw_full[stage], phase, lane);
+          continue;
+        }
+        const int j = i >> 1;                                  // this issuer's stage count inside the tile
+#endif
+        const bool first = (j % kChunk2) == 0;
+#ifdef FRN_GEMM_ONE_ISSUER
+        const bool last = (j % kChunk2) == kChunk2 - 1 || i + 1 >= tl.ntiles;
+#else
+        const bool last = (j % kChunk2) == kChunk2 - 1 || i + 2 >= tl.ntiles;
+#endif
         { TRACE_T0();
-        if (first && gc >= 2) mbar_wait(&acc_free[buf], ((gc >> 1) - 1) & 1);
+        if (first && gc >= 1) mbar_wait_warp(&acc_free[w], (gc - 1) & 1, lane);
         TRACE_ADD(4); }
+        // the split warps arrive on lo_full only after they have seen raw_full complete, so lo_full covers both
         { TRACE_T0();
-        mbar_wait(&raw_full[stage], phase);
-        TRACE_ADD(5); }
-        { TRACE_T0();
-        if (!p.fast) mbar_wait(&lo_full[stage], phase);
+        mbar_wait_warp(split ? &lo_full[stage] : &raw_full[stage], phase, lane);
         TRACE_ADD(3); }
         tc_fence_after();
+        TS(4, it);
         TRACE_T0();
         if (elect_one()) {
-          const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes, sB = sA + 2 * Cfg::kABytes;
-          const uint32_t d_acc = tmem_acc + buf * 2 * BN;
+          const uint32_t d_acc = tmem_acc + w * 2 * BN;
+          const uint64_t so = (uint64_t)(((uint32_t)stage * Cfg::kStageBytes) >> 4);
+          uint64_t a_hi = dA0 + so, b_both = dB0 + so;
 #pragma unroll
-          for (int k = 0; k < TBK / 8; k++) {
-            // K-major: + 32 bytes per K = 8 slice inside the 128-byte rows; MN-major: + 8 rows of 128 bytes
-            const uint32_t oa = g.a_mn ? k * 1024 : k * 32, ob = g.b_mn ? k * 1024 : k * 32;
-            const uint64_t a_hi = g.a_mn ? umma_desc(sA + oa, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sA + oa);
-            const uint64_t a_lo = g.a_mn ? umma_desc(sA + Cfg::kABytes + oa, 4096, g.mn_sbo, g.mn_layout)
-                                         : umma_desc_sw128(sA + Cfg::kABytes + oa);
-            const uint64_t b_both = g.b_mn ? umma_desc(sB + ob, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sB + ob);
+          for (int k = 0; k < TBK / 8; k++, a_hi += ka, b_both += kb) {
             const bool acc = !(first && k == 0);
-            if (!p.fast) {
-              const uint64_t b_lo = g.b_mn ? umma_desc(sB + Cfg::kBBytes + ob, 4096, g.mn_sbo, g.mn_layout)
-                                           : umma_desc_sw128(sB + Cfg::kBBytes + ob);
-              umma_tf32_ss(d_acc, a_hi, b_both, idesc2, acc);                  // [hh | hl]
-              umma_tf32_ss(d_acc + BN, a_lo, b_both, idesc1, true);            // lh (b_both starts at b_hi)
-              if (!p.no_lolo) umma_tf32_ss(d_acc + BN, a_lo, b_lo, idesc1, true);   // ll
+            if (split) {
+              const uint64_t a_lo = a_hi + (Cfg::kABytes >> 4);
+              if (!DBG(3)) umma_tf32_ss(d_acc, a_hi, b_both, idesc2, acc);                       // [hh | hl]
+              if (!DBG(2) && !DBG(3)) umma_tf32_ss(d_acc + BN, a_lo, b_both, idesc1, true);      // lh (b_both starts at b_hi)
+              if (lolo && !DBG(1) && !DBG(2) && !DBG(3))
+                umma_tf32_ss(d_acc + BN, a_lo, b_both + (Cfg::kBBytes >> 4), idesc1, true);      // ll
             } else {
               umma_tf32_ss(d_acc, a_hi, b_both, idesc1, acc);
             }
           }
+          TS_ANY(6, it);
           umma_commit(&empty[stage]);
-          if (last) umma_commit(&acc_full[buf]);
+          if (last) umma_commit(&acc_full[w]);
+          TS_ANY(7, it);
         }
         __syncwarp();
+        TS(5, it);
         TRACE_ADD(6);
         if (last) gc++;
       }
@@ -755,12 +833,14 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
           const int stage = (int)(it % Cfg::kStages);
           const uint32_t phase = (uint32_t)((it / Cfg::kStages) & 1);
           { TRACE_T0();
-          mbar_wait(&raw_full[stage], phase);
+          mbar_wait_warp(&raw_full[stage], phase, lane);
           TRACE_ADD(1); }
+          if (warp == kV2SplitWarp0) TS(2, it);
           TRACE_T0();
           const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes + (uint32_t)t * 16u;
           const uint32_t sB = sA + 2 * Cfg::kABytes;
           float4 va[Cfg::kABytes / 4096], vb[Cfg::kBBytes / 4096];
+          if (!DBG(0)) {
 #pragma unroll
           for (int q = 0; q < Cfg::kABytes / 4096; q++) va[q] = lds128(sA + q * 4096);
 #pragma unroll
@@ -771,9 +851,11 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
 #pragma unroll
           for (int q = 0; q < Cfg::kBBytes / 4096; q++)
             sts128(sB + Cfg::kBBytes + q * 4096, lo_tf32(vb[q].x), lo_tf32(vb[q].y), lo_tf32(vb[q].z), lo_tf32(vb[q].w));
-          fence_proxy_async_smem();
+          }
+          if (!DBG(8)) fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&lo_full[stage]);
+          if (warp == kV2SplitWarp0) TS(3, it);
           TRACE_ADD(2);
         }
       }
@@ -784,44 +866,57 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     const int quad = warp & 3, half = e >> 2;
     const uint32_t tlane = ((uint32_t)(quad * 32)) << 16;
     const uint32_t tile = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes) + (uint32_t)e * 4096u;
-    int gc = 0;
+    int gcb[2] = {0, 0};              // chains drained from each buffer
     for (int id = blockIdx.x; id < total; id += gridDim.x) {
       const TcTile tl = tc_tile(p, id, g.gx, g.gy, ktiles, g.tiles_per_split, BN);
       float acc[HC];
 #pragma unroll
       for (int j = 0; j < HC; j++) acc[j] = 0.f;
-      const int nchunks = (tl.ntiles + kChunk2 - 1) / kChunk2;
-      for (int chunk = 0; chunk < nchunks; chunk++, gc++) {
-        const int buf = gc & 1;
-        { TRACE_T0();
-        mbar_wait(&acc_full[buf], (gc >> 1) & 1);
-        TRACE_ADD(7); }
-        tc_fence_after();
-        const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
+      // chains of this tile in the order they finish: issuer 0's c-th, issuer 1's c-th, issuer 0's (c + 1)-th ...
+#ifdef FRN_GEMM_ONE_ISSUER
+      const int own0 = tl.ntiles, own1 = 0;
+#else
+      const int own0 = (tl.ntiles + 1) >> 1, own1 = tl.ntiles >> 1;          // stages of issuer 0 / 1
+#endif
+      const int nch0 = (own0 + kChunk2 - 1) / kChunk2, nch1 = (own1 + kChunk2 - 1) / kChunk2;
+      for (int chunk = 0; chunk < nch0; chunk++) {
 #pragma unroll
-        for (int c0 = 0; c0 < HC; c0 += 16) {
-          float v[16], w[16];
-          tmem_ld16(taddr + c0, v);
-          if (!p.fast) {
-            tmem_ld16(taddr + BN + c0, w);
-          } else {
+        for (int buf = 0; buf < 2; buf++) {
+          if (buf == 1 && chunk >= nch1) break;
+          { TRACE_T0();
+          mbar_wait_warp(&acc_full[buf], (uint32_t)(gcb[buf] & 1), lane);
+          TRACE_ADD(7); }
+          gcb[buf]++;
+          tc_fence_after();
+          const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
+          if (!DBG(7))
 #pragma unroll
-            for (int j = 0; j < 16; j++) w[j] = 0.f;
+          for (int c0 = 0; c0 < HC; c0 += 16) {
+            float v[16], w[16];
+            tmem_ld16(taddr + c0, v);
+            if (!p.fast) {
+              tmem_ld16(taddr + BN + c0, w);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; j++) w[j] = 0.f;
+            }
+            tmem_wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
           }
-          tmem_wait_ld();
-#pragma unroll
-          for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_free[buf]);
         }
-        tc_fence_before();
-        mbar_arrive(&acc_free[buf]);
       }
       TRACE_T0();
-      tc_epilogue<BN, EPI, ACC>(p, aux, tl, acc, tile, red, g.nsplit, g.gx, quad, half, lane);
+      if (!DBG(4)) tc_epilogue<BN, EPI, ACC>(p, aux, tl, acc, tile, red, g.nsplit, g.gx, quad, half, lane);
       TRACE_ADD(8);
     }
   }
   tc_fence_before();
   __syncthreads();
+  TRACE_KERNEL_END();
   if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_acc);
 }
 
@@ -842,10 +937,27 @@ struct TcPlan { int bn, ktiles, nsplit, tiles_per_split; bool swapped; GemmDesc 
 
 // The UMMA M dimension is fixed at 128: problems with few rows and many columns (the C/8-row
 // projections) are run as C^T = B^T A^T, which is only a relabelling of strides.
+struct GemmEnv { int tma, v2; uint32_t mn_layout, mn_sbo; CUtensorMapSwizzle mn_swizzle; int lolo; };
+const GemmEnv& gemm_env() {
+  static const GemmEnv env = [] {
+    GemmEnv e{1, 2, 1u, 512u, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, -1};
+    if (const char* s = getenv("FRN_GEMM_LOLO")) e.lolo = s[0] != '0';       // 0 / 1: drop / keep lo.lo everywhere (study)
+    if (const char* s = getenv("FRN_GEMM_TMA")) e.tma = s[0] != '0';
+    if (const char* s = getenv("FRN_GEMM_V2")) e.v2 = s[0] == '0' ? 0 : (s[0] == 'k' ? 1 : 2);
+    if (const char* s = getenv("FRN_GEMM_MN")) {
+      unsigned a = 1, b = 512, c = 4;
+      if (sscanf(s, "%u,%u,%u", &a, &b, &c) >= 2) { e.mn_layout = a; e.mn_sbo = b; e.mn_swizzle = (CUtensorMapSwizzle)c; }
+    }
+    return e;
+  }();
+  return env;
+}
+
 TcPlan tc_plan(const GemmDesc& in, bool allow_swap) {
   TcPlan pl;
   pl.d = in;
   pl.swapped = false;
+  if (gemm_env().lolo >= 0) pl.d.no_lolo = !gemm_env().lolo;
   if (allow_swap && in.M <= 64 && in.N > in.M && in.group_m == 0) {
     GemmDesc& d = pl.d;
     d.A = in.B; d.sAm = in.sBn; d.sAk = in.sBk; d.sAb = in.sBb;
@@ -943,20 +1055,6 @@ bool make_operand_map_v2(CUtensorMap* tm, const float* base, int rows, int K, in
 //   FRN_GEMM_TMA=0   cp.async staging in the first kernel (debug / comparison)
 //   FRN_GEMM_V2=0    never use the v2 kernel;  FRN_GEMM_V2=k  v2 for K-major operands only
 //   FRN_GEMM_MN=layout,sbo,swizzle   MN-major descriptor parameters of the v2 kernel (probing)
-struct GemmEnv { int tma, v2; uint32_t mn_layout, mn_sbo; CUtensorMapSwizzle mn_swizzle; };
-const GemmEnv& gemm_env() {
-  static const GemmEnv env = [] {
-    GemmEnv e{1, 2, 1u, 512u, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B};
-    if (const char* s = getenv("FRN_GEMM_TMA")) e.tma = s[0] != '0';
-    if (const char* s = getenv("FRN_GEMM_V2")) e.v2 = s[0] == '0' ? 0 : (s[0] == 'k' ? 1 : 2);
-    if (const char* s = getenv("FRN_GEMM_MN")) {
-      unsigned a = 1, b = 512, c = 4;
-      if (sscanf(s, "%u,%u,%u", &a, &b, &c) >= 2) { e.mn_layout = a; e.mn_sbo = b; e.mn_swizzle = (CUtensorMapSwizzle)c; }
-    }
-    return e;
-  }();
-  return env;
-}
 
 template <int BN, int EPI, bool ACC>
 int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
@@ -978,9 +1076,21 @@ int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
     using Cfg2 = Tc2Cfg<BN>;
     auto kern2 = tc_gemm2_kernel<BN, EPI, ACC>;
     FRN_TRY(set_smem_once((const void*)kern2, Cfg2::kSmem));
-    V2Args g{pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz, a_mn ? 1 : 0, b_mn ? 1 : 0, env.mn_layout, env.mn_sbo};
+    V2Args g{pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz, a_mn ? 1 : 0, b_mn ? 1 : 0, env.mn_layout, env.mn_sbo, 0};
+#if defined(FRN_GEMM_TRACE) || defined(FRN_GEMM_KNOBS)
+    if (const char* s = getenv("FRN_GEMM_DBG")) g.dbg = atoi(s);      // read per launch: tools/prof_gemm.py sweeps it
+#endif
     kern2<<<ctas, kV2Threads, Cfg2::kSmem, st>>>(d, aux, g, tmA, tmB);
     FRN_LAUNCH_CHECK();
+#if defined(FRN_GEMM_KNOBS)
+    if (getenv("FRN_GEMM_SYNC")) {          // debugging: name the launch that faults
+      cudaError_t e = cudaStreamSynchronize(st);
+      fprintf(stderr, "v2 BN=%d EPI=%d ACC=%d M=%d N=%d K=%d batch=%d a_mn=%d b_mn=%d fast=%d reduce=%d pbs=%d group_m=%d ktiles=%d tps=%d nsplit=%d grid=%d: %s\n",
+              BN, EPI, (int)ACC, d.M, d.N, d.K, d.batch, (int)a_mn, (int)b_mn, d.fast, d.reduce_batch, d.per_batch_split,
+              d.group_m, pl.ktiles, pl.tiles_per_split, pl.nsplit, ctas, cudaGetErrorString(e));
+      if (e != cudaSuccess) return (int)e;
+    }
+#endif
     return FRN_OK;
   }
   using Cfg = TcCfg<BN>;
@@ -1020,6 +1130,16 @@ int tc_gemm_trace_read(unsigned long long* out16) {
   return 1;
 #else
   (void)out16;
+  return 0;
+#endif
+}
+
+int tc_gemm_ts_read(long long* out) {      // 8 x 256 stamps
+#ifdef FRN_GEMM_TS
+  cudaMemcpyFromSymbol(out, g_ts, sizeof(long long) * 8 * 256);
+  return 1;
+#else
+  (void)out;
   return 0;
 #endif
 }

@@ -16,7 +16,7 @@ DEV = "cuda:0"
 
 
 def run_gemm(engine, A, B, Cout, M, N, K, batch, sA, sB, sC, bias_m=None, bias_n=None, accumulate=0,
-             reduce_batch=0):
+             reduce_batch=0, repeat=1, sync=True):
     lib = _lib.load()
     d = _lib.GemmDesc()
     d.A, d.B, d.C = A.data_ptr(), B.data_ptr(), Cout.data_ptr()
@@ -29,9 +29,11 @@ def run_gemm(engine, A, B, Cout, M, N, K, batch, sA, sB, sC, bias_m=None, bias_n
     d.accumulate, d.reduce_batch = accumulate, reduce_batch
     nbytes = lib.frn_gemm_workspace_bytes(C.byref(d))
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=DEV)
-    rc = lib.frn_gemm_f32(C.c_void_p(torch.cuda.current_stream().cuda_stream), engine, C.byref(d),
-                          C.c_void_p(ws.data_ptr()), nbytes)
-    torch.cuda.synchronize()
+    for _ in range(repeat):
+        rc = lib.frn_gemm_f32(C.c_void_p(torch.cuda.current_stream().cuda_stream), engine, C.byref(d),
+                              C.c_void_p(ws.data_ptr()), nbytes)
+    if sync:
+        torch.cuda.synchronize()
     assert rc == 0, lib.frn_error_string(rc)
 
 
