@@ -75,17 +75,24 @@ int run_gemm(Ctx& c, const GemmDesc& d_in) {
   }
   return gemm(c.st, d, c.splitk, c.splitk_cap);
 }
-GemmDesc desc(const float* A, const float* B, float* C, int M, int N, int K, int batch) {
+// Products of the block run as hi.hi + hi.lo + lo.hi (3 tensor-core products, like the attention kernels); the
+// fourth, lo.lo (2^-22 of the product on average, one-sided), is kept where it can matter: conv0 (a near-constant
+// input map -- RGB blanking, model.py:279-280 -- keeps all of its variation in `lo`, and the result is normalised by
+// its own variance), the materialised attention scores (exp amplifies absolute errors) and the stand-alone GEMM /
+// conv entry points of the C ABI.  Measured with FRN_GEMM_LOLO=0 (dropped everywhere): worst parity error 6.6e-6
+// against 5.4e-6 with it everywhere; one product less is ~10 % of every large GEMM.
+GemmDesc desc(const float* A, const float* B, float* C, int M, int N, int K, int batch, int keep_lolo = 0) {
   GemmDesc d{};
   d.A = A; d.B = B; d.C = C; d.M = M; d.N = N; d.K = K; d.batch = batch;
   d.alpha = 1.f;
+  d.no_lolo = keep_lolo ? 0 : 1;
   return d;
 }
 
 // out (batch, M, N) = W (M, K) @ x (batch, K, N) + bias
 int conv1x1(Ctx& c, const float* W, const float* bias, const float* x, float* out, int batch, int M,
-            int K, int N) {
-  GemmDesc d = desc(W, x, out, M, N, K, batch);
+            int K, int N, int keep_lolo = 0) {
+  GemmDesc d = desc(W, x, out, M, N, K, batch, keep_lolo);
   d.sAm = K; d.sAk = 1; d.sAb = 0;
   d.sBk = N; d.sBn = 1; d.sBb = (long)K * N;
   d.sCm = N; d.sCn = 1; d.sCb = (long)M * N;
@@ -114,7 +121,7 @@ int proj3(Ctx& c, const float* w0, const float* b0, const float* w1, const float
 }
 // dx (batch, K, N) (+)= W^T (K, M) @ dy (batch, M, N), dy element (m, n) at dy[m*sm + n*sn]
 int conv1x1_dgrad(Ctx& c, const float* W, const float* dy, long sm, long sn, long sb, float* dx,
-                  int batch, int M, int K, int N, int accumulate, int no_lolo = 0) {
+                  int batch, int M, int K, int N, int accumulate, int no_lolo = 1) {
   GemmDesc d = desc(W, dy, dx, K, N, M, batch);
   d.no_lolo = no_lolo;
   d.sAm = 1; d.sAk = K; d.sAb = 0;
@@ -125,7 +132,7 @@ int conv1x1_dgrad(Ctx& c, const float* W, const float* dy, long sm, long sn, lon
 }
 // dW (M, K) = sum_b dy_b (M, N) @ x_b^T (N, K);  db (M) = sum_b sum_n dy_b
 int conv1x1_wgrad(Ctx& c, const float* dy, long sm, long sn, long sb, const float* x, float* dW,
-                  float* db, int batch, int M, int K, int N, int no_lolo = 0) {
+                  float* db, int batch, int M, int K, int N, int no_lolo = 1) {
   GemmDesc d = desc(dy, x, dW, M, K, N, batch);
   d.no_lolo = no_lolo;
   d.sAm = sm; d.sAk = sn; d.sAb = sb;
@@ -238,7 +245,7 @@ int attention_fwd(Ctx& c, int B, int N, int d, const CabSaved& s) {
   for (int b0 = 0; b0 < B; b0 += ch) {
     int nb = std::min(ch, B - b0);
     long o = (long)b0 * d * N;
-    GemmDesc g = desc(s.Qc + o, Kz + o, S, N, N, d, nb);        // S[i][j] = sum_c Q[c][i] K[c][j]
+    GemmDesc g = desc(s.Qc + o, Kz + o, S, N, N, d, nb, 1);     // S[i][j] = sum_c Q[c][i] K[c][j]
     g.sAm = 1; g.sAk = N; g.sAb = (long)d * N;
     g.sBk = N; g.sBn = 1; g.sBb = (long)d * N;
     g.sCm = N; g.sCn = 1; g.sCb = (long)N * N;
@@ -351,7 +358,7 @@ int attention_bwd(Ctx& c, int B, int N, int d, const CabSaved& s, const float* d
   for (int b0 = 0; b0 < B; b0 += ch) {
     int nb = std::min(ch, B - b0);
     long o = (long)b0 * dn;
-    GemmDesc g = desc(s.Qc + o, Kz + o, P, N, N, d, nb);            // S = Q K
+    GemmDesc g = desc(s.Qc + o, Kz + o, P, N, N, d, nb, 1);         // S = Q K
     g.sAm = 1; g.sAk = N; g.sAb = dn;
     g.sBk = N; g.sBn = 1; g.sBb = dn;
     g.sCm = N; g.sCn = 1; g.sCb = nn;
@@ -590,8 +597,8 @@ FusionSaved fusion_saved_layout(void* base, int B, int C, int N) {
 int refusion_forward(Ctx& c, int B, int C, int N, const float* a, const float* e,
                      const frn_refusion_params& p, float* out, const FusionSaved& s) {
   NvtxRange nv("frn.refusion.fwd");
-  FRN_TRY(conv1x1(c, p.conv0_rgb_w, p.conv0_rgb_b, a, s.R0, B, C, C, N));   // fusion.py:23
-  FRN_TRY(conv1x1(c, p.conv0_evt_w, p.conv0_evt_b, e, s.E0, B, C, C, N));   // fusion.py:24
+  FRN_TRY(conv1x1(c, p.conv0_rgb_w, p.conv0_rgb_b, a, s.R0, B, C, C, N, 1));   // fusion.py:23
+  FRN_TRY(conv1x1(c, p.conv0_evt_w, p.conv0_evt_b, e, s.E0, B, C, C, N, 1));   // fusion.py:24
   // fusion.py:26-28 fused with the content statistics both AdaINs need (AdaIN.py:23)
   {
     size_t m0 = c.ws.off;
@@ -1203,12 +1210,12 @@ int frn_refusion_lateral_backward(void* stream, int B, int C, int N, int Cout, c
 // ---- 1x1 convolution (FPN laterals, model.py:28-40) ---------------------------------
 static int conv1x1_fwd_body(Ctx& c, int B, int Cin, int Cout, int N, const float* x, const float* w,
                             const float* bias, float* y) {
-  return conv1x1(c, w, bias, x, y, B, Cout, Cin, N);
+  return conv1x1(c, w, bias, x, y, B, Cout, Cin, N, 1);
 }
 static int conv1x1_bwd_body(Ctx& c, int B, int Cin, int Cout, int N, const float* x, const float* w,
                             const float* dy, float* dx, float* dw, float* db) {
-  if (dx) FRN_TRY(conv1x1_dgrad(c, w, dy, N, 1, (long)Cout * N, dx, B, Cout, Cin, N, 0));
-  return conv1x1_wgrad(c, dy, N, 1, (long)Cout * N, x, dw, db, B, Cout, Cin, N);
+  if (dx) FRN_TRY(conv1x1_dgrad(c, w, dy, N, 1, (long)Cout * N, dx, B, Cout, Cin, N, 0, 0));
+  return conv1x1_wgrad(c, dy, N, 1, (long)Cout * N, x, dw, db, B, Cout, Cin, N, 0);
 }
 size_t frn_conv1x1_workspace_bytes(int B, int Cin, int Cout, int N) {
   if (B <= 0 || Cin <= 0 || Cout <= 0 || N <= 0) return 0;
