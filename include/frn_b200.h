@@ -22,7 +22,7 @@
  *     the side streams and fork / join events on which independent halves of a call run (block A / block B of
  *     REFusion, dQ / dK,dV of the attention backward) -- they always rejoin the caller's stream before the call
  *     returns; (2) the set of kernels whose shared-memory limit has been raised; (3) switches read ONCE from the
- *     environment at first use (FRN_GEMM_TMA, FRN_GEMM_V2, FRN_NO_PROJ3, FRN_NO_F4, FRN_NO_FORK, FRN_INFER_V1: debug
+ *     environment at first use (FRN_GEMM_TMA, FRN_GEMM_V2, FRN_GEMM_LOLO, FRN_NO_PROJ3, FRN_NO_F4, FRN_NO_FORK, FRN_INFER_V1: debug
  *     and comparison only); (4) the launch counter and, when enabled, the measurement hooks at the end of this file.
  *     The engine switches (frn_set_*_engine) only have an effect in a -DFRN_DEBUG_ENGINES build.
  *   - The caller owns every buffer, including `saved` (forward state kept for
