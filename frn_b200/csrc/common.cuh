@@ -146,8 +146,9 @@ struct GemmDesc {
                          // already hold tf32-exact values (their producers rounded them): v2 kernel, no staging at all
   // tcgen05 v2 kernel only: drop the lo*lo product (3 tensor-core products instead of 4).  lo*lo is 2^-22 of the
   // product on average (one-sided); it only matters when an operand is near-constant AND the result is normalised
-  // by its own variance afterwards (conv0 of a blanked RGB map, model.py:279-280), so the gradient GEMMs of conv0
-  // skip it.
+  // by its own variance afterwards (conv0 of a blanked RGB map, model.py:279-280) or exponentiated (attention
+  // scores).  fusion.cu's desc() sets it for every other product of the block; the C ABI's stand-alone GEMM and
+  // conv entry points keep all four.
   int no_lolo;
   // tcgen05 engine only, plain stores (no reduce_batch / accumulate): rows [g * group_m, (g + 1) * group_m) of the
   // product go to the g-th of up to three output matrices (C, C1, C2; same strides) -- one GEMM for the three 1x1

@@ -605,7 +605,7 @@ tc_gemm_kernel(GemmDesc p, float* __restrict__ aux, int ktiles, int tiles_per_sp
 // TWO issuing warps.  Timestamps of the hand-over points (-DFRN_GEMM_TS, tools/prof_gemm.py TIMELINE) showed one
 // issuing thread spending ~900 cycles per stage on the 12 MMAs and another ~900 on the commits, the loop turn-around
 // and the next barrier wait, with the tensor pipe (1024 cycles of work per stage) running dry in between.  Issuer w
-// takes the stages i = w (mod 2) of a tile and accumulates chains of kChunk2 of ITS stages in accumulator buffer w,
+// takes the stages it = w (mod 2) of the CTA's global stage sequence and accumulates chains of kChunk2 of ITS stages in accumulator buffer w,
 // so each issuer's bookkeeping runs under the other's MMAs, the two never touch the same accumulator, and the drain
 // warps empty buffer 0 while buffer 1 fills (and vice versa).
 constexpr int kV2Threads = 19 * 32;
@@ -735,7 +735,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
       }
     }
   } else if (warp == 1 || warp == kV2Issuer1) {
-    // ===== MMA issue (issuer w: stages i = w mod 2 of every tile, accumulator buffer w) =====
+    // ===== MMA issue (issuer w: global stages it = w mod 2, accumulator buffer w) =====
     const int w = warp == 1 ? 0 : 1;
     // [b_hi | b_lo] are adjacent in shared memory (both majors), so ONE instruction with N = 2 BN forms
     // a_hi.[b_hi | b_lo] = [hh | hl] in the column halves [main | small] of the accumulator buffer; a_lo.b_hi and
@@ -759,31 +759,25 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     const bool split = !p.fast, lolo = !p.no_lolo;
     long it = 0;
     int gc = 0;                       // chains this issuer has finished (its buffer's phase counter)
+    int cnt = 0;                      // stages in this issuer's open chain
     for (int id = blockIdx.x; id < total; id += gridDim.x) {
       const TcTile tl = tc_tile(p, id, g.gx, g.gy, ktiles, g.tiles_per_split, BN);
       for (int i = 0; i < tl.ntiles; i++, it++) {
         const int stage = (int)(it % Cfg::kStages);
         const uint32_t phase = (uint32_t)((it / Cfg::kStages) & 1);
-#ifdef FRN_GEMM_ONE_ISSUER
-        if (w != 0) continue;
-        const int j = i;
-#else
-        if ((i & 1) != w) {
+        if ((int)(it & 1) != w) {
           // Not this issuer's stage, but it still has to SEE the stage complete: a parity wait only works for a
-          // waiter that is at most one phase behind, and with a 3-deep ring this issuer's next stage (it + 1) is
-          // followed by it + 3 -- the same slot as `it` -- which it could otherwise reach, and pass on the stale
-          // parity of the slot's previous use, before the other issuer has consumed `it`.
+          // waiter that is at most one phase behind.  Stages are owned by the parity of the GLOBAL stage counter, so
+          // every issuer owns every other stage whatever the tiles' K is, the in-order producer can never get more
+          // than a ring ahead of either issuer's last commit, and neither can miss a phase of any slot.  (Without
+          // these waits the second issuer passed a slot's stale parity in the 3-deep ring and consumed a stage that
+          // had not been loaded: a launch failure in the single-product mode.)
           mbar_wait_warp(split ? &lo_full[stage] : &raw_full[stage], phase, lane);
           continue;
         }
-        const int j = i >> 1;                                  // this issuer's stage count inside the tile
-#endif
-        const bool first = (j % kChunk2) == 0;
-#ifdef FRN_GEMM_ONE_ISSUER
-        const bool last = (j % kChunk2) == kChunk2 - 1 || i + 1 >= tl.ntiles;
-#else
-        const bool last = (j % kChunk2) == kChunk2 - 1 || i + 2 >= tl.ntiles;
-#endif
+        const bool first = cnt == 0;
+        const bool last = cnt == kChunk2 - 1 || i + 2 >= tl.ntiles;    // chain full, or this issuer's last stage of the tile
+        cnt = last ? 0 : cnt + 1;
         { TRACE_T0();
         if (first && gc >= 1) mbar_wait_warp(&acc_free[w], (gc - 1) & 1, lane);
         TRACE_ADD(4); }
@@ -867,48 +861,45 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     const uint32_t tlane = ((uint32_t)(quad * 32)) << 16;
     const uint32_t tile = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes) + (uint32_t)e * 4096u;
     int gcb[2] = {0, 0};              // chains drained from each buffer
+    int cnt[2] = {0, 0};              // stages in each issuer's open chain
+    long it = 0;                      // global stage counter at the start of the tile
     for (int id = blockIdx.x; id < total; id += gridDim.x) {
       const TcTile tl = tc_tile(p, id, g.gx, g.gy, ktiles, g.tiles_per_split, BN);
       float acc[HC];
 #pragma unroll
       for (int j = 0; j < HC; j++) acc[j] = 0.f;
-      // chains of this tile in the order they finish: issuer 0's c-th, issuer 1's c-th, issuer 0's (c + 1)-th ...
-#ifdef FRN_GEMM_ONE_ISSUER
-      const int own0 = tl.ntiles, own1 = 0;
-#else
-      const int own0 = (tl.ntiles + 1) >> 1, own1 = tl.ntiles >> 1;          // stages of issuer 0 / 1
-#endif
-      const int nch0 = (own0 + kChunk2 - 1) / kChunk2, nch1 = (own1 + kChunk2 - 1) / kChunk2;
-      for (int chunk = 0; chunk < nch0; chunk++) {
+      // the chains of this tile in the order they finish, by the issuers' own rule
+      for (int i = 0; i < tl.ntiles; i++) {
+        const int buf = (int)((it + i) & 1);
+        const bool last = cnt[buf] == kChunk2 - 1 || i + 2 >= tl.ntiles;
+        cnt[buf] = last ? 0 : cnt[buf] + 1;
+        if (!last) continue;
+        { TRACE_T0();
+        mbar_wait_warp(&acc_full[buf], (uint32_t)(gcb[buf] & 1), lane);
+        TRACE_ADD(7); }
+        gcb[buf]++;
+        tc_fence_after();
+        const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
+        if (!DBG(7))
 #pragma unroll
-        for (int buf = 0; buf < 2; buf++) {
-          if (buf == 1 && chunk >= nch1) break;
-          { TRACE_T0();
-          mbar_wait_warp(&acc_full[buf], (uint32_t)(gcb[buf] & 1), lane);
-          TRACE_ADD(7); }
-          gcb[buf]++;
-          tc_fence_after();
-          const uint32_t taddr = tmem_acc + tlane + buf * 2 * BN + half * HC;
-          if (!DBG(7))
+        for (int c0 = 0; c0 < HC; c0 += 16) {
+          float v[16], w[16];
+          tmem_ld16(taddr + c0, v);
+          if (!p.fast) {
+            tmem_ld16(taddr + BN + c0, w);
+          } else {
 #pragma unroll
-          for (int c0 = 0; c0 < HC; c0 += 16) {
-            float v[16], w[16];
-            tmem_ld16(taddr + c0, v);
-            if (!p.fast) {
-              tmem_ld16(taddr + BN + c0, w);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; j++) w[j] = 0.f;
-            }
-            tmem_wait_ld();
-#pragma unroll
-            for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
+            for (int j = 0; j < 16; j++) w[j] = 0.f;
           }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_free[buf]);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 16; j++) acc[c0 + j] += v[j] + w[j];
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_free[buf]);
       }
+      it += tl.ntiles;
       TRACE_T0();
       if (!DBG(4)) tc_epilogue<BN, EPI, ACC>(p, aux, tl, acc, tile, red, g.nsplit, g.gx, quad, half, lane);
       TRACE_ADD(8);
