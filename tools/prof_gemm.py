@@ -2,6 +2,10 @@
   conv   C (8, 256, 19200) = W (256, 256) @ x (8, 256, 19200)          retinanet/fusion.py:23
   wgrad  dW (256, 256) = sum_b dy_b (256, 19200) @ x_b^T (19200, 256)
   proj   V (8, 32, 19200) = Wg (32, 256) @ x                            retinanet/Attention.py:24
+
+Instrumented builds (frn_b200/csrc/Makefile: GEMM_KNOBS / GEMM_TS / GEMM_TRACE), loaded with FRN_B200_LIB=...:
+  SWEEP=1      the v2 kernel with parts switched off (FRN_GEMM_DBG bits), 20 back-to-back launches per setting
+  TIMELINE=n   clock64 stamps of the first n stage hand-overs of CTA 0
 """
 import os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
