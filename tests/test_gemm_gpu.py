@@ -62,6 +62,13 @@ CASES = [
     ("v2_bn32_posmajor", 2, 320, 32, 128, "km", "nk", "nm"),
     ("v2_long_k", 1, 128, 128, 4096, "mk", "nk", "mn"),
     ("v2_swapped_small_M", 2, 96, 1200, 512, "mk", "kn", "mn"),
+    # persistent CTAs walking MANY tiles (more tiles than SMs) with 1, 3 and 5 stages per tile: the two MMA-issuing
+    # warps own stages by the parity of the CTA's global stage counter, so with an odd stage count per tile the owner of
+    # a tile's first stage alternates, chains of both issuers end inside one tile, and every ring slot changes hands
+    ("v2_many_tiles_k32", 16, 128, 4096, 32, "mk", "kn", "mn"),
+    ("v2_many_tiles_k96", 8, 256, 5120, 96, "mk", "kn", "mn"),
+    ("v2_many_tiles_k160_kB", 4, 384, 3000, 160, "mk", "nk", "mn"),
+    ("v2_many_tiles_bn32", 24, 1024, 32, 96, "mk", "kn", "mn"),
 ]
 
 
