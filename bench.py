@@ -285,12 +285,14 @@ def run_ours(args):
     norm_host = [torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(2)]
 
     copy_stream = torch.cuda.Stream(device=dev)
-    order = sorted(range(len(levels)), key=lambda k: host_a[k].numel())      # smallest level first
+    # largest level first: level 1 is half of the step's compute, so its inputs should not queue behind the others
+    # (this only matters for the first step of a run -- later steps' inputs arrive while the previous step computes)
+    order = sorted(range(len(levels)), key=lambda k: -host_a[k].numel())
 
     out_host = [torch.empty((B, 2 * c, h, w), dtype=torch.float32).pin_memory() for c, h, w in levels] if args.e2e_full else None
 
     def run_e2e(steps, full=False):
-        """`steps` steps of: host inputs -> H2D (pinned, on a copy stream, smallest level first) -> fwd+bwd through
+        """`steps` steps of: host inputs -> H2D (pinned, on a copy stream, largest level first) -> fwd+bwd through
         the public modules -> allreduce -> D2H of the result.  Software-pipelined the way a training loop is: step
         i + 1's inputs are copied into the other staging set while step i computes, and the host reads step i's
         result while step i + 1 is already enqueued (so launch latency is hidden too).  All `steps` copies and

@@ -616,11 +616,14 @@ constexpr int kV2SplitWarp0 = 2, kV2EpiWarp0 = 10, kV2Issuer1 = 18;
 // on the 256 x 19200 x 256 convolution.)
 constexpr int kChunk2 = 4;
 
-template <int BN> struct Tc2Cfg {
-  static constexpr int kStages = BN == 128 ? 3 : 4;
+// FAST (single product on tf32-exact operands, the bf16 inference path): no lo tiles, so a stage is half the size and
+// the ring twice as deep -- this mode has nothing but the TMA latency to hide (4 MMAs per stage).
+template <int BN, bool FAST> struct Tc2Cfg {
+  static constexpr int kPlanes = FAST ? 1 : 2;
+  static constexpr int kStages = FAST ? (BN == 128 ? 6 : 8) : (BN == 128 ? 3 : 4);
   static constexpr int kABytes = TBM * TBK * 4;            // hi or lo
   static constexpr int kBBytes = BN * TBK * 4;
-  static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;     // A hi | A lo | B hi | B lo
+  static constexpr int kStageBytes = kPlanes * (kABytes + kBBytes);     // A hi | A lo | B hi | B lo  (FAST: A | B)
   static constexpr int kEpiBytes = 8 * 4096;
   static constexpr int kSmem = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 1024 /*barriers, scratch*/;
   static constexpr int kTmemCols = 4 * BN;
@@ -660,11 +663,11 @@ struct V2Args {
 #define DBG(bit) 0
 #endif
 
-template <int BN, int EPI, bool ACC>
+template <int BN, int EPI, bool ACC, bool FAST>
 __global__ void __launch_bounds__(kV2Threads, 1)
 tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_constant__ CUtensorMap tmA,
                 const __grid_constant__ CUtensorMap tmB) {
-  using Cfg = Tc2Cfg<BN>;
+  using Cfg = Tc2Cfg<BN, FAST>;
   constexpr int HC = BN / 2;
   TRACE_KERNEL_BEGIN();
   extern __shared__ uint8_t smem_raw[];
@@ -716,7 +719,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
           TRACE_ADD(0); }
           TS(0, it);
           mbar_expect_tx(&raw_full[stage], (DBG(5) ? 0 : Cfg::kABytes) + (DBG(6) ? 0 : Cfg::kBBytes));
-          const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes, sB = sA + 2 * Cfg::kABytes;
+          const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes, sB = sA + Cfg::kPlanes * Cfg::kABytes;
           const int k0 = kt * TBK, ba = p.sAb ? b : 0, bb = p.sBb ? b : 0;
           if (DBG(5)) {
           } else if (!g.a_mn) tma_load_3d(sA, &tmA, k0, tl.m0, ba, &raw_full[stage]);
@@ -751,12 +754,13 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     // thread spends a handful of integer additions per K slice.  (Rebuilding the four descriptors from scratch for
     // every slice, with the major-dependent branches, was ~1000 cycles of serial scalar code per stage -- as much
     // as the MMAs themselves, measured with the tensor work switched off: tools/prof_gemm.py SWEEP.)
-    const uint32_t sA0 = stage_base, sB0 = stage_base + 2 * Cfg::kABytes;
+    const uint32_t sA0 = stage_base, sB0 = stage_base + Cfg::kPlanes * Cfg::kABytes;
     const uint64_t dA0 = g.a_mn ? umma_desc(sA0, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sA0);
     const uint64_t dB0 = g.b_mn ? umma_desc(sB0, 4096, g.mn_sbo, g.mn_layout) : umma_desc_sw128(sB0);
     // K-major: + 32 bytes per K = 8 slice inside the 128-byte rows; MN-major: + 8 rows of 128 bytes
     const uint32_t ka = (g.a_mn ? 1024u : 32u) >> 4, kb = (g.b_mn ? 1024u : 32u) >> 4;
-    const bool split = !p.fast, lolo = !p.no_lolo;
+    constexpr bool split = !FAST;
+    const bool lolo = !p.no_lolo;
     long it = 0;
     int gc = 0;                       // chains this issuer has finished (its buffer's phase counter)
     int cnt = 0;                      // stages in this issuer's open chain
@@ -818,7 +822,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
     }
   } else if (warp < kV2EpiWarp0) {
     // ===== lo split: same byte offsets as the raw tile, whatever its layout =====
-    if (!p.fast) {
+    if (!FAST) {
       const int t = tid - kV2SplitWarp0 * 32;          // 0..255
       long it = 0;
       for (int id = blockIdx.x; id < total; id += gridDim.x) {
@@ -832,7 +836,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
           if (warp == kV2SplitWarp0) TS(2, it);
           TRACE_T0();
           const uint32_t sA = stage_base + (uint32_t)stage * Cfg::kStageBytes + (uint32_t)t * 16u;
-          const uint32_t sB = sA + 2 * Cfg::kABytes;
+          const uint32_t sB = sA + Cfg::kPlanes * Cfg::kABytes;
           float4 va[Cfg::kABytes / 4096], vb[Cfg::kBBytes / 4096];
           if (!DBG(0)) {
 #pragma unroll
@@ -885,7 +889,7 @@ tc_gemm2_kernel(GemmDesc p, float* __restrict__ aux, V2Args g, const __grid_cons
         for (int c0 = 0; c0 < HC; c0 += 16) {
           float v[16], w[16];
           tmem_ld16(taddr + c0, v);
-          if (!p.fast) {
+          if (!FAST) {
             tmem_ld16(taddr + BN + c0, w);
           } else {
 #pragma unroll
@@ -1064,14 +1068,15 @@ int tc_launch_acc(cudaStream_t st, const TcPlan& pl, float* aux) {
   if (env.tma && env.v2 && d.fast != 1 && (env.v2 == 2 || (!a_mn && !b_mn)) &&
       make_operand_map_v2(&tmA, d.A, d.M, d.K, d.batch, d.sAm, d.sAk, d.sAb, TBM, env.mn_swizzle) &&
       make_operand_map_v2(&tmB, d.B, d.N, d.K, d.batch, d.sBn, d.sBk, d.sBb, BN, env.mn_swizzle)) {
-    using Cfg2 = Tc2Cfg<BN>;
-    auto kern2 = tc_gemm2_kernel<BN, EPI, ACC>;
-    FRN_TRY(set_smem_once((const void*)kern2, Cfg2::kSmem));
+    const bool fast = d.fast != 0;
+    auto kern2 = fast ? tc_gemm2_kernel<BN, EPI, ACC, true> : tc_gemm2_kernel<BN, EPI, ACC, false>;
+    const int smem2 = fast ? Tc2Cfg<BN, true>::kSmem : Tc2Cfg<BN, false>::kSmem;
+    FRN_TRY(set_smem_once((const void*)kern2, smem2));
     V2Args g{pl.ktiles, pl.tiles_per_split, pl.nsplit, gx, gy, gz, a_mn ? 1 : 0, b_mn ? 1 : 0, env.mn_layout, env.mn_sbo, 0};
 #if defined(FRN_GEMM_TRACE) || defined(FRN_GEMM_KNOBS)
     if (const char* s = getenv("FRN_GEMM_DBG")) g.dbg = atoi(s);      // read per launch: tools/prof_gemm.py sweeps it
 #endif
-    kern2<<<ctas, kV2Threads, Cfg2::kSmem, st>>>(d, aux, g, tmA, tmB);
+    kern2<<<ctas, kV2Threads, smem2, st>>>(d, aux, g, tmA, tmB);
     FRN_LAUNCH_CHECK();
 #if defined(FRN_GEMM_KNOBS)
     if (getenv("FRN_GEMM_SYNC")) {          // debugging: name the launch that faults
