@@ -10,7 +10,9 @@ features, fp32 on 1xB200").  N > 1: one process per GPU (torchrun), the batch is
 (weak scaling: 8 samples per GPU) and the fusion-parameter gradients are all-reduced over NCCL.
 
 Prints ONE JSON line (rank 0).  `value` is device-resident throughput, `e2e` includes the H2D copy
-of every step's inputs from pinned host memory and a D2H read of the step's gradient norm.
+of every step's inputs from pinned host memory and a D2H read of the step's gradient norm (software
+pipelined as a training loop is: step i + 1's inputs travel while step i computes; every step's
+copies are inside the timed region).
 `--impl reference` times the reference's own CPU arithmetic (oracle/fusion_torch.py: the same ATen
 call sequence as retinanet/fusion.py, since /root/reference does not exist on the GPU box).
 """
