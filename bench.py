@@ -287,6 +287,7 @@ def run_ours(args):
     norm_host = [torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(2)]
 
     copy_stream = torch.cuda.Stream(device=dev)
+    d2h_stream = torch.cuda.Stream(device=dev)
     # largest level first: level 1 is half of the step's compute, so its inputs should not queue behind the others
     # (this only matters for the first step of a run -- later steps' inputs arrive while the previous step computes)
     order = sorted(range(len(levels)), key=lambda k: -host_a[k].numel())
@@ -332,14 +333,21 @@ def run_ours(args):
                 with torch.cuda.stream(st):
                     a = stage_a[s][k].detach().requires_grad_(True); e = stage_e[s][k].detach().requires_grad_(True)
                     out = mods[k](a, e)
+                    if full:                    # the 2C map goes home on its own stream, under this level's backward
+                        fwd_done = torch.cuda.Event()
+                        fwd_done.record(st)
+                        d2h_stream.wait_event(fwd_done)
+                        with torch.cuda.stream(d2h_stream):
+                            out_host[k].copy_(out.detach(), non_blocking=True)
+                        out.record_stream(d2h_stream)
                     out.backward(douts[k])
                     bucket.allreduce_level(k)
-                    if full:
-                        out_host[k].copy_(out.detach(), non_blocking=True)
             if lvl_streams is not None:
                 for k in order:
                     main.wait_stream(lvl_streams[k])
             bucket.wait()
+            if full:
+                main.wait_stream(d2h_stream)    # the step's outputs are on the host before its result is reported
             norm_host[s].copy_(bucket.grad_norm().reshape(1), non_blocking=True)   # D2H result
             ev = torch.cuda.Event()
             ev.record(main)
